@@ -1,0 +1,99 @@
+// Shared device/host helpers for the aha_b200 sm_100a kernels.
+//
+// Rounding convention: PyTorch evaluates every bf16 tensor op in
+// fp32 and rounds the result to bf16 (RNE) before the next op.  `bf16r()` is that rounding
+// step; kernels that must be bit-faithful to the reference's op order call it after every
+// reference-level op.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string>
+
+typedef __nv_bfloat16 bf16;
+
+// ---- status codes of the C-ABI (include/aha_b200.h) ----
+#define AHA_OK 0
+#define AHA_ERR_VALUE (-1)    // reference would raise ValueError (bad geometry / shape)
+#define AHA_ERR_RUNTIME (-2)  // reference would raise RuntimeError (CUDA failure)
+
+void aha_set_error(const std::string& msg);
+int aha_cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define AHA_CUDA(expr)                                                        \
+  do {                                                                        \
+    cudaError_t _e = (expr);                                                  \
+    if (_e != cudaSuccess) return aha_cuda_fail(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define AHA_CHECK_LAUNCH() AHA_CUDA(cudaGetLastError())
+
+#define AHA_REQUIRE(cond, msg)                         \
+  do {                                                 \
+    if (!(cond)) {                                     \
+      aha_set_error(std::string("ValueError: ") + msg); \
+      return AHA_ERR_VALUE;                            \
+    }                                                  \
+  } while (0)
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+__device__ __forceinline__ float b2f(bf16 x) { return __bfloat162float(x); }
+__device__ __forceinline__ bf16 f2b(float x) { return __float2bfloat16_rn(x); }
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
+  __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
+  return __bfloat1622float2(v);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024 (multiple of 32); `red` is >= 32 floats of smem.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  float r = (lane < nw) ? red[lane] : 0.f;
+  r = warp_sum(r);
+  return r;
+}
+
+// 128-bit streaming load / store (read-once data: keep it out of L1).
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_v4(void* p, const uint4& v) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// Activation functions in fp32, written the way ATen evaluates them.
+__device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gelu_tanh_f(float x) {
+  const float kBeta = 0.79788456080286535588f;  // sqrt(2/pi)
+  const float kKappa = 0.044715f;
+  float inner = kBeta * (x + kKappa * x * x * x);
+  return 0.5f * x * (1.f + tanhf(inner));
+}
+__device__ __forceinline__ float silu_f(float x) { return x / (1.f + expf(-x)); }
+
+#endif  // __CUDACC__

@@ -1,0 +1,53 @@
+// Host-side interface of the tcgen05 GEMM (gemm_tcgen05.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+enum GemmAct { GEMM_ACT_NONE = 0, GEMM_ACT_GELU_TANH = 1, GEMM_ACT_GELU_ERF = 2, GEMM_ACT_SILU_MUL = 3 };
+
+// Device-visible parameter block (passed by value).
+struct GemmParams {
+  int Ma, Nb, K;        // rows of A, rows of B, shared inner dimension
+  int swap;             // 0: A = tokens, B = features ; 1: A = features (weights), B = tokens
+  int splits;           // split-K factor (gridDim.z)
+  int kb_per_split;     // 64-wide k-blocks per split
+  void* out;            // out[token * ldo + feature]; bf16 unless out_f32
+  int ldo;
+  int out_f32;
+  int round_bf16;       // with out_f32: round the sum to bf16 first (reference: bf16 Linear then .float())
+  int act;              // GemmAct
+  const __nv_bfloat16* bias;      // [features] or null
+  const __nv_bfloat16* residual;  // residual[(token % res_mod) * ldr + feature] or null
+  int ldr;
+  int res_mod;          // 0 = no modulo
+  float* ws;            // split-K workspace
+  int* tickets;         // split-K tile tickets (zero-initialised, self re-arming)
+};
+
+// Description of one GEMM call as the model layers see it:  out[tokens, features] = X[tokens, K] . W[features, K]^T
+struct GemmCall {
+  const __nv_bfloat16* x; int tokens; int ldx;    // activations, row stride in elements
+  const __nv_bfloat16* w; int features; int ldw;  // weights
+  int K;
+  void* out; int ldo; int out_f32; int round_bf16;
+  int act;
+  const __nv_bfloat16* bias;
+  const __nv_bfloat16* residual; int ldr; int res_mod;
+  int force_swap;    // -1 auto, 0 tall, 1 skinny
+  int force_bn;      // 0 auto
+  int force_splits;  // 0 auto
+};
+
+struct GemmWorkspace {
+  float* ws = nullptr; size_t ws_bytes = 0;
+  int* tickets = nullptr; int n_tickets = 0;
+  int sm_count = 148;
+};
+
+int gemm_workspace_create(GemmWorkspace* w, int device);
+void gemm_workspace_destroy(GemmWorkspace* w);
+// Enqueues the GEMM on `stream`. Returns AHA_OK or a negative error code.
+int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream);
+// Launch counters (bench.py's gpu_launches claim).
+extern unsigned long long g_aha_launch_count;

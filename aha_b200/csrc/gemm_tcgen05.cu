@@ -1,0 +1,435 @@
+// bf16 GEMM on the 5th-gen tensor cores (tcgen05.mma, accumulator in TMEM, operands staged by TMA).
+//
+//   D[i, j] = sum_k A[i, k] * B[j, k]        A: [Ma, K] row-major bf16, B: [Nb, K] row-major bf16
+//
+// One CTA computes one 128 x BN tile of D (optionally one K-split of it).  Warp roles:
+//   warp 0 : TMA producer (one elected lane) - fills a kStages ring of {A 128x64, B BNx64} bf16 tiles,
+//            128-byte swizzled, signalling `full[s]` via mbarrier complete_tx
+//   warp 1 : MMA issuer (one elected lane) - 4 x tcgen05.mma (K=16 each) per stage, tcgen05.commit -> `empty[s]`,
+//            final commit -> `accum_full`
+//   warp 2 : TMEM allocator / deallocator
+//   warps 4-7 : epilogue - tcgen05.ld (lane = tile row), bias / activation / residual, bf16 or fp32 store
+//
+// The same kernel serves two orientations (GemmParams::swap):
+//   swap = 0 ("tall"): A = activations [tokens, K], B = weights [features, K]   (SigLIP tower, projector)
+//   swap = 1 ("skinny"): A = weights [features, K], B = activations [tokens, K] (Qwen2 prefill with
+//            49..256 tokens: the 128-wide MMA M dimension is filled with weight rows, the token count
+//            becomes the MMA N dimension, so no tensor work is wasted on padding and every CTA streams a
+//            distinct slab of weights - the skinny GEMMs are HBM-bound on weight bytes)
+// Output is always out[token * ldo + feature].
+//
+// Split-K: gridDim.z splits write fp32 partial tiles to a workspace; the last CTA to arrive at the
+// tile's ticket sums the partials in split order (deterministic) and runs the epilogue.
+//
+// Replaces the cuBLAS calls behind nn.Linear in the reference: SigLIP q/k/v/out/fc1/fc2
+// (LLaVA_NeXT/llava/model/multimodal_encoder/siglip_encoder.py:197-255), mm_projector
+// (multimodal_projector/builder.py:42-48), Qwen2 q/k/v/o/gate/up/down + lm_head
+// (transformers 4.49 modeling_qwen2.py, called at models/live_llava/video_head_live_llava_qwen.py:160-175).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "gemm.h"
+
+#include <cuda.h>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+using namespace sm100;
+
+namespace {
+
+constexpr int kBlockM = 128;  // rows of A per tile == TMEM lanes
+constexpr int kBlockK = 64;   // bf16 elements per stage row == one 128-byte swizzle atom
+constexpr int kUmmaK = 16;
+constexpr int kThreads = 256;
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = (BN <= 32) ? 5 : (BN <= 64) ? 4 : (BN <= 128) ? 3 : 4;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBBytes = BN * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTmemCols = BN < 32 ? 32 : BN;  // power of two >= 32
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// Applies bias / activation / residual to 16 consecutive accumulator columns (j = jc .. jc+15) of
+// tile row i and stores them.  `acc` are fp32 sums.
+__device__ __forceinline__ void epilogue_store16(const GemmParams& p, int a0, int b0, int i, int jc, float (&acc)[16]) {
+  const int ai = a0 + i;  // global A row
+  if (!p.swap) {
+    // token = A row (fixed for this thread); features = B rows jc..jc+15 (contiguous in memory)
+    const int token = ai;
+    if (token >= p.Ma) return;
+    const int f0 = b0 + jc;
+    if (f0 >= p.Nb) return;
+    const int nvalid = min(16, p.Nb - f0);
+    float v[16];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      float x = acc[t];
+      if (p.bias && t < nvalid) x += b2f(p.bias[f0 + t]);
+      if (!p.out_f32 || p.round_bf16) x = bf16r(x);
+      if (p.act == GEMM_ACT_GELU_TANH) x = bf16r(gelu_tanh_f(x));
+      else if (p.act == GEMM_ACT_GELU_ERF) x = bf16r(gelu_erf_f(x));
+      v[t] = x;
+    }
+    if (p.residual) {
+      const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
+      const bf16* r = p.residual + (size_t)rrow * p.ldr + f0;
+#pragma unroll
+      for (int t = 0; t < 16; ++t)
+        if (t < nvalid) v[t] = bf16r(b2f(r[t]) + v[t]);
+    }
+    if (p.out_f32) {
+      float* o = reinterpret_cast<float*>(p.out) + (size_t)token * p.ldo + f0;
+#pragma unroll
+      for (int t = 0; t < 16; ++t)
+        if (t < nvalid) o[t] = v[t];
+    } else {
+      bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + f0;
+      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+        uint4 w0, w1;
+        w0.x = pack_bf16x2(v[0], v[1]);   w0.y = pack_bf16x2(v[2], v[3]);
+        w0.z = pack_bf16x2(v[4], v[5]);   w0.w = pack_bf16x2(v[6], v[7]);
+        w1.x = pack_bf16x2(v[8], v[9]);   w1.y = pack_bf16x2(v[10], v[11]);
+        w1.z = pack_bf16x2(v[12], v[13]); w1.w = pack_bf16x2(v[14], v[15]);
+        st_v4(o, w0);
+        st_v4(o + 8, w1);
+      } else {
+#pragma unroll
+        for (int t = 0; t < 16; ++t)
+          if (t < nvalid) o[t] = f2b(v[t]);
+      }
+    }
+  } else {
+    // feature = A row (fixed for this thread); tokens = B rows jc..jc+15
+    const int feat = ai;
+    const bool fvalid = feat < p.Ma;
+    const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      const int token = b0 + jc + t;
+      float x = acc[t] + bias;
+      if (!p.out_f32 || p.round_bf16) x = bf16r(x);
+      if (p.act == GEMM_ACT_SILU_MUL) {
+        // rows interleaved: even A row = gate feature f, odd A row = up feature f
+        float other = __shfl_down_sync(0xffffffffu, x, 1);
+        float s = bf16r(silu_f(x));
+        x = bf16r(s * other);
+        if ((i & 1) == 0 && fvalid && token < p.Nb) {
+          reinterpret_cast<bf16*>(p.out)[(size_t)token * p.ldo + (feat >> 1)] = f2b(x);
+        }
+        continue;
+      }
+      if (p.act == GEMM_ACT_GELU_TANH) x = bf16r(gelu_tanh_f(x));
+      else if (p.act == GEMM_ACT_GELU_ERF) x = bf16r(gelu_erf_f(x));
+      if (!fvalid || token >= p.Nb) continue;
+      if (p.residual) {
+        const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
+        x = bf16r(b2f(p.residual[(size_t)rrow * p.ldr + feat]) + x);
+      }
+      if (p.out_f32) reinterpret_cast<float*>(p.out)[(size_t)token * p.ldo + feat] = x;
+      else reinterpret_cast<bf16*>(p.out)[(size_t)token * p.ldo + feat] = f2b(x);
+    }
+  }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const GemmParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles need 1024-byte alignment.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + C::kStages * C::kABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* accum_bar = empty_bar + C::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  int* flag_slot = reinterpret_cast<int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int a0 = blockIdx.x * kBlockM;
+  const int b0 = blockIdx.y * BN;
+  const int split = blockIdx.z;
+  const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  const int kb_begin = split * p.kb_per_split;
+  const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
+  const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(accum_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (elect_one()) {
+      const uint64_t pol_a = p.swap ? l2_policy_evict_first() : l2_policy_evict_last();
+      const uint64_t pol_b = p.swap ? l2_policy_evict_last() : l2_policy_evict_first();
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % C::kStages;
+        const uint32_t ph = (kb / C::kStages) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full_bar[s], C::kStageBytes);
+        const int kc = (kb_begin + kb) * kBlockK;
+        tma_load_2d_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kc, a0, pol_a);
+        tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kc, b0, pol_b);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % C::kStages;
+        const uint32_t ph = (kb / C::kStages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + s * C::kABytes));
+        const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + s * C::kBBytes));
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // advance 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
+          umma_f16_ss(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+        }
+        umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+      }
+      umma_commit(accum_bar);  // accumulator complete
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 =====
+    const int ew = warp & 3;
+    const int i = ew * 32 + lane;  // tile row
+    mbar_wait(accum_bar, 0);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
+    if (p.splits == 1) {
+#pragma unroll 1
+      for (int jc = 0; jc < BN; jc += 16) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(taddr + jc, r);
+        tmem_ld_wait();
+        float acc[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
+        epilogue_store16(p, a0, b0, i, jc, acc);
+      }
+    } else {
+      // write this split's partial tile: ws[((tile * splits + split) * BN + j) * 128 + i]
+      const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+      float* wsp = p.ws + ((size_t)tile * p.splits + split) * (size_t)(BN * kBlockM);
+#pragma unroll 1
+      for (int jc = 0; jc < BN; jc += 16) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(taddr + jc, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 16; ++t) wsp[(size_t)(jc + t) * kBlockM + i] = __uint_as_float(r[t]);
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 128) {
+        const int old = atomicAdd(&p.tickets[tile], 1);
+        const int last = (old == p.splits - 1);
+        if (last) p.tickets[tile] = 0;  // re-arm for the next launch on this stream
+        *flag_slot = last;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*flag_slot) {
+        __threadfence();
+        const float* wst = p.ws + (size_t)tile * p.splits * (size_t)(BN * kBlockM);
+#pragma unroll 1
+        for (int jc = 0; jc < BN; jc += 16) {
+          float acc[16];
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+          for (int s = 0; s < p.splits; ++s) {
+            const float* q = wst + (size_t)s * (BN * kBlockM) + (size_t)jc * kBlockM + i;
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] += __ldcg(q + t * kBlockM);
+          }
+          epilogue_store16(p, a0, b0, i, jc, acc);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
+}
+
+}  // namespace
+
+// =====================================================================================
+// Host side: tensor-map cache, tiling heuristics, launch.
+// =====================================================================================
+unsigned long long g_aha_launch_count = 0;
+
+namespace {
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+struct TmapKey {
+  const void* ptr; int rows; int K; int ld; int box_rows;
+  bool operator<(const TmapKey& o) const {
+    return std::tie(ptr, rows, K, ld, box_rows) < std::tie(o.ptr, o.rows, o.K, o.ld, o.box_rows);
+  }
+};
+std::map<TmapKey, CUtensorMap> g_tmaps;
+std::mutex g_tmap_mu;
+
+// K-major [rows, K] bf16 matrix, box = 64 (K) x box_rows, 128-byte swizzle, OOB reads return zero.
+int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap* out) {
+  TmapKey key{ptr, rows, K, ld, box_rows};
+  std::lock_guard<std::mutex> lk(g_tmap_mu);
+  auto it = g_tmaps.find(key);
+  if (it != g_tmaps.end()) { *out = it->second; return AHA_OK; }
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) { aha_set_error("RuntimeError: cuTensorMapEncodeTiled not available from the driver"); return AHA_ERR_RUNTIME; }
+  AHA_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "GEMM operand base must be 16-byte aligned");
+  AHA_REQUIRE(((size_t)ld * 2) % 16 == 0, "GEMM operand row stride must be a multiple of 8 elements");
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    aha_set_error("RuntimeError: cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return AHA_ERR_RUNTIME;
+  }
+  if (g_tmaps.size() > 65536) g_tmaps.clear();
+  g_tmaps[key] = m;
+  *out = m;
+  return AHA_OK;
+}
+
+template <int BN>
+int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_done = true;
+  }
+  gemm_tcgen05_kernel<BN><<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, p);
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
+}  // namespace
+
+int gemm_workspace_create(GemmWorkspace* w, int device) {
+  cudaDeviceProp prop;
+  AHA_CUDA(cudaGetDeviceProperties(&prop, device));
+  w->sm_count = prop.multiProcessorCount;
+  w->ws_bytes = (size_t)96 << 20;
+  w->n_tickets = 8192;
+  AHA_CUDA(cudaMalloc(&w->ws, w->ws_bytes));
+  AHA_CUDA(cudaMalloc(&w->tickets, w->n_tickets * sizeof(int)));
+  AHA_CUDA(cudaMemset(w->tickets, 0, w->n_tickets * sizeof(int)));
+  return AHA_OK;
+}
+
+void gemm_workspace_destroy(GemmWorkspace* w) {
+  if (w->ws) cudaFree(w->ws);
+  if (w->tickets) cudaFree(w->tickets);
+  w->ws = nullptr; w->tickets = nullptr;
+}
+
+int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
+  AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
+  int swap = c.force_swap >= 0 ? c.force_swap : (c.tokens <= 256 ? 1 : 0);
+  if (c.act == GEMM_ACT_SILU_MUL) {
+    AHA_REQUIRE(swap == 1, "SiLU*mul epilogue needs the skinny (swap) orientation");
+    AHA_REQUIRE(!c.out_f32 && !c.residual, "SiLU*mul epilogue writes bf16 without residual");
+  }
+  GemmParams p{};
+  p.K = c.K; p.swap = swap;
+  p.out = c.out; p.ldo = c.ldo; p.out_f32 = c.out_f32; p.round_bf16 = c.round_bf16; p.act = c.act;
+  p.bias = c.bias; p.residual = c.residual; p.ldr = c.ldr; p.res_mod = c.res_mod;
+  const void* a; const void* b; int lda, ldb;
+  if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
+  else      { p.Ma = c.tokens; p.Nb = c.features; a = c.x; lda = c.ldx; b = c.w; ldb = c.ldw; }
+
+  int bn = c.force_bn;
+  if (bn == 0) {
+    if (swap) bn = p.Nb <= 32 ? 32 : p.Nb <= 64 ? 64 : p.Nb <= 128 ? 128 : 256;
+    else bn = p.Nb <= 32 ? 32 : p.Nb <= 64 ? 64 : 128;
+  }
+  AHA_REQUIRE(bn == 32 || bn == 64 || bn == 128 || bn == 256, "unsupported GEMM BN tile");
+  const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM;
+  const int tiles_b = (p.Nb + bn - 1) / bn;
+  const int tiles = tiles_a * tiles_b;
+  const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  int splits = c.force_splits;
+  if (splits == 0) {
+    splits = 1;
+    const int target = 2 * w->sm_count;
+    if (tiles < target) {
+      splits = (target + tiles - 1) / tiles;
+      const int max_by_k = kb_total / 4 > 0 ? kb_total / 4 : 1;  // at least 4 k-blocks per split
+      if (splits > max_by_k) splits = max_by_k;
+      if (splits > 16) splits = 16;
+    }
+  }
+  if (splits > kb_total) splits = kb_total;
+  int kb_per = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per - 1) / kb_per;  // no empty splits
+  p.splits = splits; p.kb_per_split = kb_per;
+  if (splits > 1) {
+    size_t need = (size_t)tiles * splits * bn * kBlockM * sizeof(float);
+    AHA_REQUIRE(need <= w->ws_bytes && tiles <= w->n_tickets, "split-K workspace too small for this GEMM");
+    p.ws = w->ws; p.tickets = w->tickets;
+  }
+  CUtensorMap ta, tb;
+  int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
+  rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
+  dim3 grid(tiles_a, tiles_b, splits);
+  switch (bn) {
+    case 32: return launch_bn<32>(ta, tb, p, grid, stream);
+    case 64: return launch_bn<64>(ta, tb, p, grid, stream);
+    case 128: return launch_bn<128>(ta, tb, p, grid, stream);
+    default: return launch_bn<256>(ta, tb, p, grid, stream);
+  }
+}

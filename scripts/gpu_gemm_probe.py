@@ -1,0 +1,104 @@
+"""GPU probe for the tcgen05 GEMM: compares against torch.matmul over a shape/epilogue sweep and times it.
+Run on the B200 box: python scripts/gpu_gemm_probe.py  (writes gpurun_out/gemm_probe.json)."""
+import ctypes, json, os, sys, time
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+lib = ctypes.CDLL(os.path.join(ROOT, "aha_b200", "lib", "libaha_b200.so"))
+lib.aha_last_error.restype = ctypes.c_char_p
+P = ctypes.c_void_p
+
+
+def gemm(x, w, out, act=0, bias=None, residual=None, res_mod=0, out_f32=0, round_bf16=0, swap=-1, bn=0, splits=0):
+    tokens, K = x.shape
+    feats = w.shape[0]
+    rc = lib.aha_gemm_bf16(P(x.data_ptr()), tokens, x.stride(0), P(w.data_ptr()), feats, w.stride(0), K,
+                           P(out.data_ptr()), out.stride(0), out_f32, round_bf16, act,
+                           P(bias.data_ptr()) if bias is not None else None,
+                           P(residual.data_ptr()) if residual is not None else None,
+                           residual.stride(0) if residual is not None else 0, res_mod, swap, bn, splits,
+                           P(torch.cuda.current_stream().cuda_stream))
+    if rc != 0:
+        raise RuntimeError(lib.aha_last_error().decode())
+
+
+def main():
+    torch.manual_seed(0)
+    dev = "cuda"
+    res = []
+    ok_all = True
+    cases = [
+        # tokens, feats, K, swap, bn, splits, act, bias, residual
+        (128, 128, 64, 0, 128, 1, 0, False, False),
+        (128, 128, 256, 0, 128, 1, 0, False, False),
+        (64, 128, 128, 1, 64, 1, 0, False, False),
+        (49, 256, 896, 1, 0, 0, 0, True, False),
+        (49, 3584, 3584, 1, 0, 0, 0, True, True),
+        (53, 4608, 3584, 1, 0, 0, 0, True, False),
+        (85, 3584, 18944, 1, 0, 0, 0, False, True),
+        (49, 37888, 3584, 1, 0, 0, 3, False, False),
+        (200, 1152, 896, 1, 0, 0, 0, True, False),
+        (729, 1152, 1152, 0, 0, 0, 0, True, True),
+        (729, 4304, 1152, 0, 0, 0, 1, True, False),
+        (729, 1152, 4304, 0, 0, 0, 0, True, True),
+        (729, 3584, 1152, 0, 0, 0, 2, True, False),
+        (1458, 1152, 592, 0, 0, 0, 0, True, True),
+        (729, 1152, 4304, 0, 64, 3, 0, True, False),
+        (729, 1152, 4304, 0, 32, 0, 0, True, False),
+        (300, 4304, 1152, 0, 256, 1, 0, True, False),
+        (49, 151936, 896, 1, 0, 0, 0, False, False),
+    ]
+    for (T, F, K, swap, bn, splits, act, has_bias, has_res) in cases:
+        x = (torch.randn(T, K, device=dev) * 0.5).bfloat16()
+        w = (torch.randn(F, K, device=dev) * (1.0 / K ** 0.5)).bfloat16()
+        bias = (torch.randn(F, device=dev) * 0.1).bfloat16() if has_bias else None
+        Fo = F // 2 if act == 3 else F
+        resid = (torch.randn(T, Fo, device=dev)).bfloat16() if has_res else None
+        out = torch.full((T, Fo), float("nan"), device=dev, dtype=torch.bfloat16)
+        entry = dict(T=T, F=F, K=K, swap=swap, bn=bn, splits=splits, act=act)
+        try:
+            gemm(x, w, out, act=act, bias=bias, residual=resid, swap=swap, bn=bn, splits=splits)
+            torch.cuda.synchronize()
+            ref = x.float() @ w.float().t()
+            if bias is not None:
+                ref = ref + bias.float()
+            ref = ref.bfloat16().float()
+            if act == 1:
+                ref = torch.nn.functional.gelu(ref, approximate="tanh").bfloat16().float()
+            elif act == 2:
+                ref = torch.nn.functional.gelu(ref).bfloat16().float()
+            elif act == 3:
+                g, u = ref[:, 0::2], ref[:, 1::2]
+                ref = (torch.nn.functional.silu(g).bfloat16().float() * u).bfloat16().float()
+            if resid is not None:
+                ref = (resid.float() + ref).bfloat16().float()
+            err = (out.float() - ref).abs().max().item()
+            scale = ref.abs().max().item()
+            nan = bool(torch.isnan(out.float()).any().item())
+            ok = (not nan) and err <= 0.02 * max(scale, 1.0)
+            # timing
+            for _ in range(3):
+                gemm(x, w, out, act=act, bias=bias, residual=resid, swap=swap, bn=bn, splits=splits)
+            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            e0.record()
+            n = 20
+            for _ in range(n):
+                gemm(x, w, out, act=act, bias=bias, residual=resid, swap=swap, bn=bn, splits=splits)
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / n
+            entry.update(err=err, scale=scale, nan=nan, ok=ok, us=us, tflops=2.0 * T * F * K / us / 1e6,
+                         w_gbs=F * K * 2 / us / 1e3)
+        except Exception as ex:  # noqa
+            entry.update(ok=False, error=str(ex))
+        ok_all &= bool(entry.get("ok"))
+        print(json.dumps(entry), flush=True)
+        res.append(entry)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    json.dump(res, open(os.path.join(ROOT, "gpurun_out", "gemm_probe.json"), "w"), indent=1)
+    print("ALL_OK" if ok_all else "SOME_FAILED")
+    return 0 if ok_all else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
