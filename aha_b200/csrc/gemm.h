@@ -10,7 +10,7 @@ enum GemmAct { GEMM_ACT_NONE = 0, GEMM_ACT_GELU_TANH = 1, GEMM_ACT_GELU_ERF = 2,
 struct GemmParams {
   int Ma, Nb, K;        // rows of A, rows of B, shared inner dimension
   int swap;             // 0: A = tokens, B = features ; 1: A = features (weights), B = tokens
-  int splits;           // split-K factor (gridDim.z)
+  int splits;           // split-K factor (gridDim.z == cluster size, <= 8)
   int kb_per_split;     // 64-wide k-blocks per split
   void* out;            // out[token * ldo + feature]; bf16 unless out_f32
   int ldo;
@@ -21,8 +21,6 @@ struct GemmParams {
   const __nv_bfloat16* residual;  // residual[(token % res_mod) * ldr + feature] or null
   int ldr;
   int res_mod;          // 0 = no modulo
-  float* ws;            // split-K workspace
-  int* tickets;         // split-K tile tickets (zero-initialised, self re-arming)
 };
 
 // Description of one GEMM call as the model layers see it:  out[tokens, features] = X[tokens, K] . W[features, K]^T
@@ -40,8 +38,6 @@ struct GemmCall {
 };
 
 struct GemmWorkspace {
-  float* ws = nullptr; size_t ws_bytes = 0;
-  int* tickets = nullptr; int n_tickets = 0;
   int sm_count = 148;
 };
 

@@ -18,8 +18,9 @@
 //            distinct slab of weights - the skinny GEMMs are HBM-bound on weight bytes)
 // Output is always out[token * ldo + feature].
 //
-// Split-K: gridDim.z splits write fp32 partial tiles to a workspace; the last CTA to arrive at the
-// tile's ticket sums the partials in split order (deterministic) and runs the epilogue.
+// Split-K: the gridDim.z K-splits of a tile form one thread-block cluster; partial tiles are parked in
+// shared memory and reduced in rank order through distributed shared memory (deterministic, no HBM
+// workspace, no atomics).
 //
 // Replaces the cuBLAS calls behind nn.Linear in the reference: SigLIP q/k/v/out/fc1/fc2
 // (LLaVA_NeXT/llava/model/multimodal_encoder/siglip_encoder.py:197-255), mm_projector
@@ -30,11 +31,13 @@
 #include "gemm.h"
 
 #include <cuda.h>
+#include <cooperative_groups.h>
 #include <map>
 #include <mutex>
 #include <tuple>
 
 using namespace sm100;
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -149,7 +152,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* accum_bar = empty_bar + C::kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
-  int* flag_slot = reinterpret_cast<int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -233,44 +235,47 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         epilogue_store16(p, a0, b0, i, jc, acc);
       }
     } else {
-      // write this split's partial tile: ws[((tile * splits + split) * BN + j) * 128 + i]
-      const int tile = blockIdx.y * gridDim.x + blockIdx.x;
-      float* wsp = p.ws + ((size_t)tile * p.splits + split) * (size_t)(BN * kBlockM);
+      // Split-K over a thread-block cluster (cluster dims 1 x 1 x splits): every CTA parks its fp32 partial
+      // tile in its own shared memory (the operand ring is idle by now), then 16-column chunks are
+      // reduced through distributed shared memory in rank order (deterministic) by CTA (chunk % splits).
+      float* stage = reinterpret_cast<float*>(smem);  // [BN][128] fp32, column-major: conflict-free per warp
 #pragma unroll 1
       for (int jc = 0; jc < BN; jc += 16) {
         uint32_t r[16];
         tmem_ld_32x32b_x16(taddr + jc, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int t = 0; t < 16; ++t) wsp[(size_t)(jc + t) * kBlockM + i] = __uint_as_float(r[t]);
-      }
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (threadIdx.x == 128) {
-        const int old = atomicAdd(&p.tickets[tile], 1);
-        const int last = (old == p.splits - 1);
-        if (last) p.tickets[tile] = 0;  // re-arm for the next launch on this stream
-        *flag_slot = last;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*flag_slot) {
-        __threadfence();
-        const float* wst = p.ws + (size_t)tile * p.splits * (size_t)(BN * kBlockM);
-#pragma unroll 1
-        for (int jc = 0; jc < BN; jc += 16) {
-          float acc[16];
-#pragma unroll
-          for (int t = 0; t < 16; ++t) acc[t] = 0.f;
-          for (int s = 0; s < p.splits; ++s) {
-            const float* q = wst + (size_t)s * (BN * kBlockM) + (size_t)jc * kBlockM + i;
-#pragma unroll
-            for (int t = 0; t < 16; ++t) acc[t] += __ldcg(q + t * kBlockM);
-          }
-          epilogue_store16(p, a0, b0, i, jc, acc);
-        }
+        for (int t = 0; t < 16; ++t) stage[(jc + t) * kBlockM + i] = __uint_as_float(r[t]);
       }
     }
     tc_fence_before();
+  }
+
+  if (p.splits > 1) {
+    cg::cluster_group cluster = cg::this_cluster();
+    __syncwarp();
+    cluster.sync();  // all partial tiles are visible cluster-wide
+    if (warp >= 4) {
+      const int ew = warp & 3;
+      const int i = ew * 32 + lane;
+      const int rank = (int)cluster.block_rank();
+      float* stage = reinterpret_cast<float*>(smem);
+#pragma unroll 1
+      for (int c = rank; c < BN / 16; c += p.splits) {
+        const int jc = c * 16;
+        float acc[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+        for (int s = 0; s < p.splits; ++s) {
+          const float* peer = cluster.map_shared_rank(stage, s) + jc * kBlockM + i;
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] += peer[t * kBlockM];
+        }
+        epilogue_store16(p, a0, b0, i, jc, acc);
+      }
+    }
+    __syncwarp();
+    cluster.sync();  // nobody leaves while peers still read its shared memory
   }
 
   __syncthreads();
@@ -351,7 +356,13 @@ int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
     AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_done = true;
   }
-  gemm_tcgen05_kernel<BN><<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, p);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN>, ta, tb, p));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;
@@ -363,19 +374,10 @@ int gemm_workspace_create(GemmWorkspace* w, int device) {
   cudaDeviceProp prop;
   AHA_CUDA(cudaGetDeviceProperties(&prop, device));
   w->sm_count = prop.multiProcessorCount;
-  w->ws_bytes = (size_t)96 << 20;
-  w->n_tickets = 8192;
-  AHA_CUDA(cudaMalloc(&w->ws, w->ws_bytes));
-  AHA_CUDA(cudaMalloc(&w->tickets, w->n_tickets * sizeof(int)));
-  AHA_CUDA(cudaMemset(w->tickets, 0, w->n_tickets * sizeof(int)));
   return AHA_OK;
 }
 
-void gemm_workspace_destroy(GemmWorkspace* w) {
-  if (w->ws) cudaFree(w->ws);
-  if (w->tickets) cudaFree(w->tickets);
-  w->ws = nullptr; w->tickets = nullptr;
-}
+void gemm_workspace_destroy(GemmWorkspace*) {}
 
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
@@ -410,18 +412,14 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
       splits = (target + tiles - 1) / tiles;
       const int max_by_k = kb_total / 4 > 0 ? kb_total / 4 : 1;  // at least 4 k-blocks per split
       if (splits > max_by_k) splits = max_by_k;
-      if (splits > 16) splits = 16;
+      if (splits > 8) splits = 8;
     }
   }
   if (splits > kb_total) splits = kb_total;
   int kb_per = (kb_total + splits - 1) / splits;
   splits = (kb_total + kb_per - 1) / kb_per;  // no empty splits
   p.splits = splits; p.kb_per_split = kb_per;
-  if (splits > 1) {
-    size_t need = (size_t)tiles * splits * bn * kBlockM * sizeof(float);
-    AHA_REQUIRE(need <= w->ws_bytes && tiles <= w->n_tickets, "split-K workspace too small for this GEMM");
-    p.ws = w->ws; p.tickets = w->tickets;
-  }
+  AHA_REQUIRE(splits <= 8, "split-K factor above the portable cluster size (8)");
   CUtensorMap ta, tb;
   int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
