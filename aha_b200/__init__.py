@@ -1,0 +1,14 @@
+"""aha_b200: B200-native (sm_100a) implementation of Aha!'s per-frame streaming ingest-and-score step.
+Importing the package does not need a GPU; every compute call goes through libaha_b200.so and raises without it."""
+from . import _lib
+from .config import AhaConfig, VisionConfig, config_preset
+from .caches import SinkCache, SlidingWindowCache, TrulyStaticCache, make_cache
+from .model import VideoHeadLiveLlavaQwenForCausalLM, VideoHeadCausalLMOutputWithPast, build_model_from_state_dict
+from .postproc import find_ticks, find_ticks_batched
+from .live_infer import LiveInferForBenchmark, LiveInferForDemo, round_numbers
+from .weights import random_init_state_dict, synthetic_frames
+
+__all__ = ["AhaConfig", "VisionConfig", "config_preset", "SinkCache", "SlidingWindowCache", "TrulyStaticCache",
+           "make_cache", "VideoHeadLiveLlavaQwenForCausalLM", "VideoHeadCausalLMOutputWithPast",
+           "build_model_from_state_dict", "find_ticks", "find_ticks_batched", "LiveInferForBenchmark", "LiveInferForDemo",
+           "round_numbers", "random_init_state_dict", "synthetic_frames"]

@@ -12,10 +12,9 @@
 
 typedef __nv_bfloat16 bf16;
 
-// ---- status codes of the C-ABI (include/aha_b200.h) ----
-#define AHA_OK 0
-#define AHA_ERR_VALUE (-1)    // reference would raise ValueError (bad geometry / shape)
-#define AHA_ERR_RUNTIME (-2)  // reference would raise RuntimeError (CUDA failure)
+#include "aha_b200.h"  // status codes of the C-ABI
+
+extern unsigned long long g_aha_launch_count;  // every kernel launch of this library bumps it
 
 void aha_set_error(const std::string& msg);
 int aha_cuda_fail(cudaError_t e, const char* what, const char* file, int line);

@@ -45,5 +45,8 @@ int gemm_workspace_create(GemmWorkspace* w, int device);
 void gemm_workspace_destroy(GemmWorkspace* w);
 // Enqueues the GEMM on `stream`. Returns AHA_OK or a negative error code.
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream);
+// Cached TMA descriptor of a row-major [rows, K] bf16 matrix (row stride ld elements): box = 64 x box_rows, 128B swizzle.
+#include <cuda.h>
+int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap* out);
 // Launch counters (bench.py's gpu_launches claim).
 extern unsigned long long g_aha_launch_count;

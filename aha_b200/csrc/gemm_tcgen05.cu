@@ -68,6 +68,26 @@ __device__ __forceinline__ void epilogue_store16(const GemmParams& p, int a0, in
     if (f0 >= p.Nb) return;
     const int nvalid = min(16, p.Nb - f0);
     float v[16];
+    if (p.act == GEMM_ACT_SILU_MUL) {
+      // features interleaved: even = gate f, odd = up f  ->  out[token, f0/2 + t] = bf16(bf16(silu(gate)) * up)
+      bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + (f0 >> 1);
+      float w[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        float g = acc[2 * t], u = acc[2 * t + 1];
+        if (p.bias && 2 * t + 1 < nvalid) { g += b2f(p.bias[f0 + 2 * t]); u += b2f(p.bias[f0 + 2 * t + 1]); }
+        g = bf16r(g); u = bf16r(u);
+        w[t] = bf16r(bf16r(silu_f(g)) * u);
+      }
+      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+        st_v4(o, make_uint4(pack_bf16x2(w[0], w[1]), pack_bf16x2(w[2], w[3]), pack_bf16x2(w[4], w[5]), pack_bf16x2(w[6], w[7])));
+      } else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (2 * t + 1 < nvalid) o[t] = f2b(w[t]);
+      }
+      return;
+    }
 #pragma unroll
     for (int t = 0; t < 16; ++t) {
       float x = acc[t];
@@ -320,6 +340,8 @@ struct TmapKey {
 std::map<TmapKey, CUtensorMap> g_tmaps;
 std::mutex g_tmap_mu;
 
+}  // namespace
+
 // K-major [rows, K] bf16 matrix, box = 64 (K) x box_rows, 128-byte swizzle, OOB reads return zero.
 int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap* out) {
   TmapKey key{ptr, rows, K, ld, box_rows};
@@ -347,6 +369,8 @@ int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap
   *out = m;
   return AHA_OK;
 }
+
+namespace {
 
 template <int BN>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
@@ -383,7 +407,6 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
   int swap = c.force_swap >= 0 ? c.force_swap : (c.tokens <= 256 ? 1 : 0);
   if (c.act == GEMM_ACT_SILU_MUL) {
-    AHA_REQUIRE(swap == 1, "SiLU*mul epilogue needs the skinny (swap) orientation");
     AHA_REQUIRE(!c.out_f32 && !c.residual, "SiLU*mul epilogue writes bf16 without residual");
   }
   GemmParams p{};

@@ -1,0 +1,532 @@
+// KV-cache policies of the reference on a device ring buffer: SinkCache (test/sink_cache.py:7-164),
+// SlidingWindowCache (test/sliding_window_cache.py:5-53), TrulyStaticCache (test/static_cache.py:5-47).
+// Integer semantics (lengths, positions, which token lives where) are decided on the host in cache_plan_update();
+// the kernels below only move / rotate bytes: coalesced 128-bit accesses, one pass over every byte they touch.
+#include "kvcache.h"
+#include <algorithm>
+
+namespace {
+
+// physical slot of chunk token t under plan geometry
+__device__ __forceinline__ int store_slot(int t, int store_begin, int store_phys0, int wrap_end, int R) {
+  int x = store_phys0 + (t - store_begin);
+  if (x >= wrap_end) x -= R;
+  return x;
+}
+
+// ---- store: copy already-rotated k / v chunk rows into their slots.  One thread per 16 bytes. ----
+__global__ void cache_store_kernel(const bf16* __restrict__ k, const bf16* __restrict__ v, long long k_hs, long long k_ts,
+                                   long long v_hs, long long v_ts, bf16* __restrict__ K, bf16* __restrict__ V, int kvh,
+                                   int d, int cap, int store_begin, int store_end, int store_phys0, int wrap_end, int R) {
+  const int dv = d >> 3;
+  const int n = store_end - store_begin;
+  const long long total = (long long)kvh * n * dv * 2;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % dv);
+    long long r = idx / dv;
+    const int t = store_begin + (int)(r % n); r /= n;
+    const int h = (int)(r % kvh);
+    const int which = (int)(r / kvh);
+    const int slot = store_slot(t, store_begin, store_phys0, wrap_end, R);
+    const bf16* src = which ? (v + h * v_hs + t * v_ts) : (k + h * k_hs + t * k_ts);
+    bf16* dst = (which ? V : K) + ((size_t)h * cap + slot) * d;
+    // sources coming from a transposed view may be only 2-byte aligned per row; rows themselves are contiguous
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+      reinterpret_cast<uint4*>(dst)[c] = reinterpret_cast<const uint4*>(src)[c];
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) dst[c * 8 + e] = src[c * 8 + e];
+    }
+  }
+}
+
+__global__ void ids_store_kernel(int32_t* __restrict__ ids, long long fed, int store_begin, int store_end, int store_phys0,
+                                 int wrap_end, int R) {
+  const int t = store_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < store_end) ids[store_slot(t, store_begin, store_phys0, wrap_end, R)] = (int32_t)(fed + t);
+}
+
+// ---- sink re-rotation table (sink_cache.py:35-55), each fp32 op rounded separately exactly as torch evaluates
+//      original_cos * shifted_cos + original_sin * shifted_sin  and  -original_sin * shifted_cos + original_cos * shifted_sin
+__global__ void rerot_table_kernel(const bf16* __restrict__ cos_t, const bf16* __restrict__ sin_t, bf16* __restrict__ out,
+                                   int S, int q, int keep, int d) {
+  const int total = keep * d;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int r = idx / d, c = idx % d;
+    const float oc = b2f(cos_t[(size_t)(S + q + r) * d + c]), sc = b2f(cos_t[(size_t)(S + r) * d + c]);
+    const float os = b2f(sin_t[(size_t)(S + q + r) * d + c]), ss = b2f(sin_t[(size_t)(S + r) * d + c]);
+    const float rc = __fadd_rn(__fmul_rn(oc, sc), __fmul_rn(os, ss));
+    const float rs = __fadd_rn(__fmul_rn(-os, sc), __fmul_rn(oc, ss));
+    out[idx] = f2b(rc);
+    out[(size_t)total + idx] = f2b(rs);
+  }
+}
+
+// ---- in-place re-rotation of the kept keys: k' = (k * c) + (rotate_half(k) * s), every op rounded to bf16
+//      (sink_cache.py:27-33).  Thread = 8 elements of the low half + the matching 8 of the high half of one key.
+//      Algorithmic bytes per key: 2*d read + 2*d written (+ the shared table rows, which stay in L2).
+struct RerotLayers { bf16* k[64]; };
+
+__global__ void __launch_bounds__(256) rerotate_kernel(RerotLayers ls, const bf16* __restrict__ rerot, int kvh, int d,
+                                                       int cap, int S, int R, int base, int keep) {
+  const int tpk = d >> 4;  // threads per key
+  const long long total = (long long)kvh * keep * tpk;
+  bf16* K = ls.k[blockIdx.y];
+  const bf16* rc = rerot;
+  const bf16* rs = rerot + (size_t)keep * d;
+  const int half = d >> 1;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % tpk);
+    long long t = idx / tpk;
+    const int r = (int)(t % keep);
+    const int h = (int)(t / keep);
+    int slot = base + r;
+    if (slot >= R) slot -= R;
+    slot += S;
+    bf16* row = K + ((size_t)h * cap + slot) * d;
+    const uint4 lo = *reinterpret_cast<const uint4*>(row + c * 8);
+    const uint4 hi = *reinterpret_cast<const uint4*>(row + half + c * 8);
+    const uint4 clo = *reinterpret_cast<const uint4*>(rc + (size_t)r * d + c * 8);
+    const uint4 chi = *reinterpret_cast<const uint4*>(rc + (size_t)r * d + half + c * 8);
+    const uint4 slo = *reinterpret_cast<const uint4*>(rs + (size_t)r * d + c * 8);
+    const uint4 shi = *reinterpret_cast<const uint4*>(rs + (size_t)r * d + half + c * 8);
+    const uint32_t l[4] = {lo.x, lo.y, lo.z, lo.w}, hh[4] = {hi.x, hi.y, hi.z, hi.w};
+    const uint32_t cl[4] = {clo.x, clo.y, clo.z, clo.w}, ch[4] = {chi.x, chi.y, chi.z, chi.w};
+    const uint32_t sl[4] = {slo.x, slo.y, slo.z, slo.w}, sh[4] = {shi.x, shi.y, shi.z, shi.w};
+    uint32_t ol[4], oh[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 a = unpack_bf16x2(l[e]), b = unpack_bf16x2(hh[e]);
+      const float2 ca = unpack_bf16x2(cl[e]), cb = unpack_bf16x2(ch[e]);
+      const float2 sa = unpack_bf16x2(sl[e]), sb = unpack_bf16x2(sh[e]);
+      // low half: rotate_half = -high ; high half: rotate_half = low
+      const float lx = bf16r(bf16r(a.x * ca.x) + bf16r(-b.x * sa.x));
+      const float ly = bf16r(bf16r(a.y * ca.y) + bf16r(-b.y * sa.y));
+      const float hx = bf16r(bf16r(b.x * cb.x) + bf16r(a.x * sb.x));
+      const float hy = bf16r(bf16r(b.y * cb.y) + bf16r(a.y * sb.y));
+      ol[e] = pack_bf16x2(lx, ly);
+      oh[e] = pack_bf16x2(hx, hy);
+    }
+    *reinterpret_cast<uint4*>(row + c * 8) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+    *reinterpret_cast<uint4*>(row + half + c * 8) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+  }
+}
+
+// ---- logical-order export (what Cache.update() returns): out[h][j][:] = buf[h][phys(j)][:] ----
+__global__ void export_kernel(const bf16* __restrict__ buf, bf16* __restrict__ out, int kvh, int d, int cap, int len,
+                              int S, int R, int base) {
+  const int dv = d >> 3;
+  const long long total = (long long)kvh * len * dv;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % dv);
+    long long t = idx / dv;
+    const int j = (int)(t % len);
+    const int h = (int)(t / len);
+    int p = j;
+    if (R > 0 && j >= S) { p = base + (j - S); if (p >= R) p -= R; p += S; }
+    reinterpret_cast<uint4*>(out + ((size_t)h * len + j) * d)[c] =
+        reinterpret_cast<const uint4*>(buf + ((size_t)h * cap + p) * d)[c];
+  }
+}
+__global__ void export_ids_kernel(const int32_t* __restrict__ ids, int32_t* __restrict__ out, int len, int S, int R,
+                                  int base) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= len) return;
+  int p = j;
+  if (R > 0 && j >= S) { p = base + (j - S); if (p >= R) p -= R; p += S; }
+  out[j] = ids[p];
+}
+
+// compaction helpers: gather rows [from, from+n) of every head into scratch, then scatter to [to, to+n)
+__global__ void move_rows_kernel(const bf16* __restrict__ src, int src_cap, int src_row0, bf16* __restrict__ dst,
+                                 int dst_cap, int dst_row0, int kvh, int d, int n) {
+  const int dv = d >> 3;
+  const long long total = (long long)kvh * n * dv;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % dv);
+    long long t = idx / dv;
+    const int r = (int)(t % n);
+    const int h = (int)(t / n);
+    reinterpret_cast<uint4*>(dst + ((size_t)h * dst_cap + dst_row0 + r) * d)[c] =
+        reinterpret_cast<const uint4*>(src + ((size_t)h * src_cap + src_row0 + r) * d)[c];
+  }
+}
+__global__ void move_ids_kernel(const int32_t* __restrict__ src, int32_t* __restrict__ dst, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[i];
+}
+
+// ---- fused RoPE + append for the prefill engine ----
+// Qwen2 apply_rotary_pos_emb (transformers 4.49): x' = (x * cos) + (rotate_half(x) * sin), each op rounded to bf16.
+// Thread = (stream, token, head slot, 16-element pair of 8-chunks).  Head slots: [0, heads) = q heads,
+// [heads, heads+kvh) = k heads, [heads+kvh, heads+2kvh) = v heads (the packed projection's column blocks).
+__global__ void __launch_bounds__(256) rope_append_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ cos,
+                                                          const bf16* __restrict__ sin, bf16* __restrict__ qbuf,
+                                                          RopeAppendArgs a, int q, int heads, int kvh, int d, int cap) {
+  const int tph = d >> 4;                 // threads per head row
+  const int slots = heads + 2 * kvh;
+  const int ld = slots * d;
+  const int s = blockIdx.y;
+  const int group = heads / kvh;
+  const int half = d >> 1;
+  const RopeAppendStream& st = a.s[s];
+  const long long total = (long long)q * slots * tph;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % tph);
+    long long t2 = idx / tph;
+    const int slot = (int)(t2 % slots);
+    const int t = (int)(t2 / slots);
+    const bf16* src = qkv + ((size_t)s * q + t) * ld + (size_t)slot * d;
+    const uint4 lo = *reinterpret_cast<const uint4*>(src + c * 8);
+    const uint4 hi = *reinterpret_cast<const uint4*>(src + half + c * 8);
+    bf16* dst;
+    bool rotate = true;
+    if (slot < heads) {
+      const int g = slot / group, r = slot % group;
+      dst = qbuf + ((((size_t)s * kvh + g) * q + t) * group + r) * d;
+    } else {
+      if (t < st.store_begin || t >= st.store_end) continue;
+      const int phys = store_slot(t, st.store_begin, st.store_phys0, st.wrap_end, st.R);
+      if (slot < heads + kvh) {
+        dst = st.k + ((size_t)(slot - heads) * cap + phys) * d;
+      } else {
+        dst = st.v + ((size_t)(slot - heads - kvh) * cap + phys) * d;
+        rotate = false;
+      }
+    }
+    if (!rotate) {
+      *reinterpret_cast<uint4*>(dst + c * 8) = lo;
+      *reinterpret_cast<uint4*>(dst + half + c * 8) = hi;
+      continue;
+    }
+    const bf16* cr = cos + ((size_t)s * q + t) * d;
+    const bf16* sr = sin + ((size_t)s * q + t) * d;
+    const uint4 clo = *reinterpret_cast<const uint4*>(cr + c * 8), chi = *reinterpret_cast<const uint4*>(cr + half + c * 8);
+    const uint4 slo = *reinterpret_cast<const uint4*>(sr + c * 8), shi = *reinterpret_cast<const uint4*>(sr + half + c * 8);
+    const uint32_t l[4] = {lo.x, lo.y, lo.z, lo.w}, hh[4] = {hi.x, hi.y, hi.z, hi.w};
+    const uint32_t cl[4] = {clo.x, clo.y, clo.z, clo.w}, ch[4] = {chi.x, chi.y, chi.z, chi.w};
+    const uint32_t sl[4] = {slo.x, slo.y, slo.z, slo.w}, sh[4] = {shi.x, shi.y, shi.z, shi.w};
+    uint32_t ol[4], oh[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(l[e]), y = unpack_bf16x2(hh[e]);
+      const float2 ca = unpack_bf16x2(cl[e]), cb = unpack_bf16x2(ch[e]);
+      const float2 sa = unpack_bf16x2(sl[e]), sb = unpack_bf16x2(sh[e]);
+      ol[e] = pack_bf16x2(bf16r(bf16r(x.x * ca.x) + bf16r(-y.x * sa.x)), bf16r(bf16r(x.y * ca.y) + bf16r(-y.y * sa.y)));
+      oh[e] = pack_bf16x2(bf16r(bf16r(y.x * cb.x) + bf16r(x.x * sb.x)), bf16r(bf16r(y.y * cb.y) + bf16r(x.y * sb.y)));
+    }
+    *reinterpret_cast<uint4*>(dst + c * 8) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+    *reinterpret_cast<uint4*>(dst + half + c * 8) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+  }
+}
+
+inline int grid_for(long long items, int threads, int cap = 148 * 8) {
+  long long g = (items + threads - 1) / threads;
+  return (int)std::max<long long>(1, std::min<long long>(g, cap));
+}
+
+}  // namespace
+
+// =====================================================================================
+// host side
+// =====================================================================================
+int cache_plan_update(const aha_cache_s* c, const CacheLayer& ly, int q, UpdatePlan* plan) {
+  UpdatePlan p;
+  AHA_REQUIRE(q > 0, "cache update with an empty chunk");
+  p.q = q; p.S = c->S; p.R = c->R; p.L = ly.populated ? ly.len : 0;
+  p.new_base = ly.ring_base;
+  const int W = c->W, S = c->S, R = c->R;
+  if (c->policy == AHA_POLICY_STATIC) {
+    if (!ly.populated) {            // static_cache.py:26-33: first call stores k[:, :, :W]
+      p.store_begin = 0; p.store_end = std::min(q, W); p.store_phys0 = 0; p.klen = p.store_end;
+    } else {                        // :34-36: later calls are ignored, the frozen prefix is returned
+      p.store_begin = p.store_end = 0; p.klen = ly.len;
+    }
+    *plan = p;
+    return AHA_OK;
+  }
+  if (!ly.populated) {              // sink_cache.py:124-127 / sliding_window_cache.py:27-30: stored whole, even if q > W
+    AHA_REQUIRE(q <= c->cap, "first chunk is larger than the cache capacity (max(window, max_chunk))");
+    p.store_begin = 0; p.store_end = q; p.store_phys0 = 0; p.klen = q; p.new_base = 0;
+    *plan = p;
+    return AHA_OK;
+  }
+  const int len = ly.len;
+  const bool oversize = len > W;    // linear layout left behind by an oversize first chunk
+  if (c->policy == AHA_POLICY_SLIDING) {
+    const long long total = (long long)len + q;
+    if (total <= W) {               // sliding_window_cache.py:33-42 with nothing to drop
+      p.store_begin = 0; p.store_end = q; p.store_phys0 = (ly.ring_base + len) % R; p.wrap_end = W; p.klen = (int)total;
+    } else if (q >= W) {            // cat(old, new)[-W:] keeps only the last W new tokens
+      p.store_begin = q - W; p.store_end = q; p.store_phys0 = 0; p.new_base = 0; p.klen = W; p.evicted = len;
+    } else if (oversize) {
+      p.keep_copy = W - q; p.compact_from = len - p.keep_copy; p.new_base = 0;
+      p.store_begin = 0; p.store_end = q; p.store_phys0 = p.keep_copy; p.klen = W; p.evicted = len - p.keep_copy;
+    } else {
+      const int e = (int)(total - W);
+      p.evicted = e;
+      p.new_base = (ly.ring_base + e) % R;
+      p.store_begin = 0; p.store_end = q; p.store_phys0 = (ly.ring_base + len) % R; p.wrap_end = W; p.klen = W;
+    }
+    *plan = p;
+    return AHA_OK;
+  }
+  // ---- sink ----
+  if ((long long)q + len < W) {     // sink_cache.py:129-132 growing (only ever reached with ring_base == 0)
+    p.store_begin = 0; p.store_end = q; p.store_phys0 = len; p.klen = len + q;
+    *plan = p;
+    return AHA_OK;
+  }
+  const int keep = W - S - q;       // sink_cache.py:134-162 shifting
+  AHA_REQUIRE(keep > 0, "chunk does not fit behind the sinks: q >= window_length - num_sink_tokens");
+  p.keep = keep;
+  p.evicted = len + q - W;
+  p.klen = W;
+  p.store_begin = 0; p.store_end = q;
+  if (oversize) {
+    p.keep_copy = keep; p.compact_from = len - keep; p.new_base = 0;
+    p.store_phys0 = S + keep;
+  } else {
+    p.new_base = (ly.ring_base + p.evicted) % R;
+    p.store_phys0 = S + (p.new_base + keep) % R;
+    p.wrap_end = W;
+  }
+  *plan = p;
+  return AHA_OK;
+}
+
+int cache_ensure_layer(aha_cache_s* c, int layer) {
+  AHA_REQUIRE(layer >= 0 && layer < 4096, "layer index out of range");
+  if ((int)c->layers.size() <= layer) c->layers.resize(layer + 1);
+  CacheLayer& ly = c->layers[layer];
+  if (!ly.k) {
+    const size_t bytes = (size_t)c->kvh * c->cap * c->d * sizeof(bf16);
+    AHA_CUDA(cudaMalloc(&ly.k, bytes));
+    AHA_CUDA(cudaMalloc(&ly.v, bytes));
+  }
+  if (layer + 1 > c->n_layers) c->n_layers = layer + 1;
+  return AHA_OK;
+}
+
+int cache_layer0_bookkeeping(aha_cache_s* c, const UpdatePlan& p, const bf16* cos, const bf16* sin, cudaStream_t st) {
+  const int q = p.q;
+  if (c->policy == AHA_POLICY_SINK) {
+    c->seen_tokens += q;                                          // sink_cache.py:105-106
+    c->have_rope = (cos != nullptr && sin != nullptr);
+    if (c->have_rope) {
+      if (c->cos_rows == 0 || c->cos_rows < c->W) {               // sink_cache.py:116-121
+        AHA_REQUIRE(c->cos_rows + q <= c->W + c->max_chunk, "cos/sin table overflow (chunk larger than max_chunk)");
+        const size_t bytes = (size_t)q * c->d * sizeof(bf16);
+        AHA_CUDA(cudaMemcpyAsync(c->cos_table + (size_t)c->cos_rows * c->d, cos, bytes, cudaMemcpyDeviceToDevice, st));
+        AHA_CUDA(cudaMemcpyAsync(c->sin_table + (size_t)c->cos_rows * c->d, sin, bytes, cudaMemcpyDeviceToDevice, st));
+        c->cos_rows += q;
+      }
+      if (p.keep > 0 && !c->rerot.count(q)) {                     // sink_cache.py:38-55, once per distinct q
+        AHA_REQUIRE(c->cos_rows >= c->W, "re-rotation requested before the cos/sin table covers the window");
+        bf16* t = nullptr;
+        AHA_CUDA(cudaMalloc(&t, (size_t)2 * p.keep * c->d * sizeof(bf16)));
+        c->rerot[q] = t;
+        rerot_table_kernel<<<grid_for((long long)p.keep * c->d, 256), 256, 0, st>>>(c->cos_table, c->sin_table, t, c->S, q,
+                                                                                    p.keep, c->d);
+        ++g_aha_launch_count;
+        AHA_CHECK_LAUNCH();
+      }
+    }
+  }
+  // provenance ids
+  if (p.compact_from >= 0 && p.keep_copy > 0) {
+    int32_t* tmp = nullptr;
+    AHA_CUDA(cudaMallocAsync(&tmp, (size_t)p.keep_copy * 4, st));
+    move_ids_kernel<<<(p.keep_copy + 255) / 256, 256, 0, st>>>(c->ids + p.compact_from, tmp, p.keep_copy);
+    move_ids_kernel<<<(p.keep_copy + 255) / 256, 256, 0, st>>>(tmp, c->ids + c->S, p.keep_copy);
+    g_aha_launch_count += 2;
+    AHA_CUDA(cudaFreeAsync(tmp, st));
+  }
+  if (p.store_end > p.store_begin) {
+    const int n = p.store_end - p.store_begin;
+    ids_store_kernel<<<(n + 127) / 128, 128, 0, st>>>(c->ids, c->fed, p.store_begin, p.store_end, p.store_phys0,
+                                                      p.wrap_end, p.R);
+    ++g_aha_launch_count;
+    AHA_CHECK_LAUNCH();
+  }
+  c->fed += q;
+  return AHA_OK;
+}
+
+int cache_compact(aha_cache_s* c, int layer, const UpdatePlan& p, cudaStream_t st) {
+  if (p.compact_from < 0 || p.keep_copy <= 0) return AHA_OK;
+  const size_t half = (size_t)c->kvh * c->W * c->d;
+  if (!c->scratch) AHA_CUDA(cudaMalloc(&c->scratch, half * sizeof(bf16)));
+  CacheLayer& ly = c->layers[layer];
+  const int dst_row0 = c->policy == AHA_POLICY_SINK ? c->S : 0;
+  bf16* bufs[2] = {ly.k, ly.v};
+  for (int i = 0; i < 2; ++i) {
+    const long long items = (long long)c->kvh * p.keep_copy * (c->d / 8);
+    move_rows_kernel<<<grid_for(items, 256), 256, 0, st>>>(bufs[i], c->cap, p.compact_from, c->scratch, c->W, 0, c->kvh,
+                                                          c->d, p.keep_copy);
+    move_rows_kernel<<<grid_for(items, 256), 256, 0, st>>>(c->scratch, c->W, 0, bufs[i], c->cap, dst_row0, c->kvh, c->d,
+                                                          p.keep_copy);
+    g_aha_launch_count += 2;
+  }
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
+int cache_rerotate(aha_cache_s* c, int layer0, int n, const UpdatePlan& p, cudaStream_t st) {
+  if (p.keep <= 0 || !c->have_rope) return AHA_OK;
+  auto it = c->rerot.find(p.q);
+  AHA_REQUIRE(it != c->rerot.end(), "re-rotation table missing for this chunk length (layer 0 must be updated first)");
+  for (int l0 = 0; l0 < n; l0 += 64) {
+    const int cnt = std::min(64, n - l0);
+    RerotLayers ls;
+    for (int i = 0; i < cnt; ++i) ls.k[i] = c->layers[layer0 + l0 + i].k;
+    const long long items = (long long)c->kvh * p.keep * (c->d / 16);
+    // enough CTAs per layer to put ~2 waves on 148 SMs across all layers of the launch
+    int gx = (int)std::min<long long>((items + 255) / 256, std::max(1, (148 * 8 + cnt - 1) / cnt));
+    dim3 grid(gx, cnt);
+    rerotate_kernel<<<grid, 256, 0, st>>>(ls, it->second, c->kvh, c->d, c->cap, c->S, c->R, p.new_base, p.keep);
+    ++g_aha_launch_count;
+  }
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
+int cache_store(aha_cache_s* c, int layer, const UpdatePlan& p, const bf16* k, const bf16* v, long long k_hs,
+                long long k_ts, long long v_hs, long long v_ts, cudaStream_t st) {
+  const int n = p.store_end - p.store_begin;
+  if (n <= 0) return AHA_OK;
+  CacheLayer& ly = c->layers[layer];
+  const long long items = (long long)c->kvh * n * (c->d / 8) * 2;
+  cache_store_kernel<<<grid_for(items, 256), 256, 0, st>>>(k, v, k_hs, k_ts, v_hs, v_ts, ly.k, ly.v, c->kvh, c->d, c->cap,
+                                                           p.store_begin, p.store_end, p.store_phys0, p.wrap_end, p.R);
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
+void cache_commit(aha_cache_s* c, int layer, const UpdatePlan& p) {
+  CacheLayer& ly = c->layers[layer];
+  if (c->policy == AHA_POLICY_STATIC) {
+    if (!ly.populated) { ly.populated = true; ly.len = p.klen; }
+    return;
+  }
+  ly.populated = true;
+  ly.len = p.klen;
+  ly.ring_base = p.new_base;
+}
+
+int op_rope_append(const bf16* qkv, const bf16* cos, const bf16* sin, bf16* qbuf, const RopeAppendArgs& a, int n_streams,
+                   int q, int heads, int kvh, int d, int cap, cudaStream_t st) {
+  AHA_REQUIRE(n_streams > 0 && n_streams <= 16 && d % 16 == 0 && heads % kvh == 0, "rope_append: bad shape");
+  const long long items = (long long)q * (heads + 2 * kvh) * (d / 16);
+  dim3 grid(grid_for(items, 256), n_streams);
+  rope_append_kernel<<<grid, 256, 0, st>>>(qkv, cos, sin, qbuf, a, q, heads, kvh, d, cap);
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
+// =====================================================================================
+// C-ABI
+// =====================================================================================
+extern "C" {
+
+int aha_cache_create(int n_layers, int kv_heads, int head_dim, int policy, int window, int sinks, int max_chunk,
+                     int device, aha_cache_t* out) {
+  AHA_REQUIRE(out != nullptr, "aha_cache_create: out is NULL");
+  AHA_REQUIRE(policy >= 0 && policy <= 2, "unknown cache policy");
+  AHA_REQUIRE(kv_heads > 0 && head_dim > 0 && head_dim % 16 == 0, "head_dim must be a positive multiple of 16");
+  AHA_REQUIRE(window > 0, "window_length must be positive");
+  if (policy != AHA_POLICY_SINK) sinks = 0;
+  AHA_REQUIRE(sinks >= 0 && sinks < window, "num_sink_tokens must be in [0, window_length)");
+  AHA_REQUIRE(n_layers >= 0 && n_layers <= 4096, "bad layer count");
+  AHA_CUDA(cudaSetDevice(device));
+  aha_cache_s* c = new aha_cache_s();
+  c->device = device; c->kvh = kv_heads; c->d = head_dim; c->policy = policy; c->W = window; c->S = sinks;
+  c->R = window - sinks;
+  c->max_chunk = std::max(max_chunk, 1);
+  c->cap = std::max(window, c->max_chunk);
+  cudaError_t e = cudaMalloc(&c->ids, (size_t)c->cap * sizeof(int32_t));
+  if (e == cudaSuccess && policy == AHA_POLICY_SINK) {
+    const size_t rows = (size_t)window + c->max_chunk;
+    e = cudaMalloc(&c->cos_table, rows * head_dim * sizeof(bf16));
+    if (e == cudaSuccess) e = cudaMalloc(&c->sin_table, rows * head_dim * sizeof(bf16));
+  }
+  if (e != cudaSuccess) { aha_cache_destroy(c); return aha_cuda_fail(e, "cudaMalloc(cache)", __FILE__, __LINE__); }
+  for (int l = 0; l < n_layers; ++l) {
+    int rc = cache_ensure_layer(c, l);
+    if (rc) { aha_cache_destroy(c); return rc; }
+  }
+  *out = c;
+  return AHA_OK;
+}
+
+int aha_cache_reset(aha_cache_t c) {
+  AHA_REQUIRE(c != nullptr, "aha_cache_reset: NULL handle");
+  for (auto& ly : c->layers) { ly.populated = false; ly.len = 0; ly.ring_base = 0; }
+  c->seen_tokens = 0; c->fed = 0; c->cos_rows = 0; c->have_rope = false;
+  for (auto& kv : c->rerot) cudaFree(kv.second);
+  c->rerot.clear();
+  return AHA_OK;
+}
+
+int aha_cache_destroy(aha_cache_t c) {
+  if (!c) return AHA_OK;
+  for (auto& ly : c->layers) { cudaFree(ly.k); cudaFree(ly.v); }
+  for (auto& kv : c->rerot) cudaFree(kv.second);
+  cudaFree(c->ids); cudaFree(c->cos_table); cudaFree(c->sin_table); cudaFree(c->scratch);
+  delete c;
+  return AHA_OK;
+}
+
+int aha_cache_update(aha_cache_t c, int layer, const void* k, const void* v, long long k_hs, long long k_ts,
+                     long long v_hs, long long v_ts, const void* cos, const void* sin, int q, void* stream) {
+  AHA_REQUIRE(c != nullptr && k != nullptr && v != nullptr, "aha_cache_update: NULL argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = cache_ensure_layer(c, layer); if (rc) return rc;
+  UpdatePlan p;
+  rc = cache_plan_update(c, c->layers[layer], q, &p); if (rc) return rc;
+  if (layer == 0) { rc = cache_layer0_bookkeeping(c, p, (const bf16*)cos, (const bf16*)sin, st); if (rc) return rc; }
+  else if (c->policy == AHA_POLICY_SINK) c->have_rope = (cos != nullptr && sin != nullptr);
+  rc = cache_compact(c, layer, p, st); if (rc) return rc;
+  rc = cache_rerotate(c, layer, 1, p, st); if (rc) return rc;
+  rc = cache_store(c, layer, p, (const bf16*)k, (const bf16*)v, k_hs, k_ts, v_hs, v_ts, st); if (rc) return rc;
+  cache_commit(c, layer, p);
+  return AHA_OK;
+}
+
+int aha_cache_seq_length(aha_cache_t c, int layer, int* out) {
+  AHA_REQUIRE(c != nullptr && out != nullptr, "aha_cache_seq_length: NULL argument");
+  *out = (layer >= 0 && layer < (int)c->layers.size() && c->layers[layer].populated) ? c->layers[layer].len : 0;
+  return AHA_OK;
+}
+
+int aha_cache_seen_tokens(aha_cache_t c, long long* out) {
+  AHA_REQUIRE(c != nullptr && out != nullptr, "aha_cache_seen_tokens: NULL argument");
+  *out = c->seen_tokens;
+  return AHA_OK;
+}
+
+int aha_cache_export(aha_cache_t c, int layer, void* K_out, void* V_out, int32_t* prov, void* stream) {
+  AHA_REQUIRE(c != nullptr, "aha_cache_export: NULL handle");
+  AHA_REQUIRE(layer >= 0 && layer < (int)c->layers.size() && c->layers[layer].populated, "layer not populated");
+  cudaStream_t st = (cudaStream_t)stream;
+  const CacheLayer& ly = c->layers[layer];
+  const int len = ly.len;
+  if (len == 0) return AHA_OK;
+  const bool ring = (c->policy != AHA_POLICY_STATIC) && len <= c->W;
+  const int R = ring ? c->R : 0;
+  const long long items = (long long)c->kvh * len * (c->d / 8);
+  if (K_out) { export_kernel<<<grid_for(items, 256), 256, 0, st>>>(ly.k, (bf16*)K_out, c->kvh, c->d, c->cap, len, c->S, R, ly.ring_base); ++g_aha_launch_count; }
+  if (V_out) { export_kernel<<<grid_for(items, 256), 256, 0, st>>>(ly.v, (bf16*)V_out, c->kvh, c->d, c->cap, len, c->S, R, ly.ring_base); ++g_aha_launch_count; }
+  if (prov) { export_ids_kernel<<<(len + 255) / 256, 256, 0, st>>>(c->ids, prov, len, c->S, R, ly.ring_base); ++g_aha_launch_count; }
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+"""Host-side mirror of the reference's live drivers, restricted to ingest-and-score:
+
+    LiveInferForBenchmark      test/inference.py:38-348   (reset / set_fps / input_video_stream / input_query_stream /
+                                                            _encode_frame / _encode_query / inference)
+    LiveInferForDemo           test/live_infer_for_video.py:80-229 (load_one_frame / input_one_frame / find_ticks)
+
+Differences that are the point of the rewrite: frame embeddings stay on the device (the reference parks them in host
+RAM, test/inference.py:185,213); the three per-frame scores are written by the heads kernel into a device score buffer
+and read back once per stream instead of three `.item()` syncs per frame (:222-227) - unless a response threshold is
+active, in which case one read per frame is needed, exactly where the reference needs its decision.
+Response generation (fast_greedy_generate) is outside this path ("next" row N1): when a threshold fires the frame is
+recorded in `response_needed` and the stream goes on.
+"""
+from __future__ import annotations
+
+from collections import deque
+from typing import List, Optional
+
+import torch
+
+from .model import VideoHeadLiveLlavaQwenForCausalLM
+from .postproc import find_ticks as _find_ticks
+
+
+def round_numbers(data, n):
+    """test/inference.py:365-375."""
+    if isinstance(data, list):
+        return [round_numbers(d, n) for d in data]
+    if isinstance(data, dict):
+        return {k: round_numbers(v, n) for k, v in data.items()}
+    if isinstance(data, float):
+        return round(data, n)
+    return data
+
+
+class LiveInferForBenchmark:
+    def __init__(self, model: VideoHeadLiveLlavaQwenForCausalLM, start_ids: torch.Tensor,
+                 added_stream_prompt_ids: Optional[torch.Tensor] = None, sink_cache: bool = False,
+                 alt_cache: str = "default_sink", window_length: int = 2048, num_sink_tokens: int = 32,
+                 frame_fps: float = 2.0, score_heads=("relevance_score", "informative_score"),
+                 stream_end_prob_threshold: Optional[float] = None, stream_end_score_sum_threshold: Optional[float] = None,
+                 running_list_length: int = 20, max_frames: int = 4096):
+        self.model = model
+        self.model.eval()
+        cfg = model.config
+        self.hidden_size = cfg.hidden_size
+        self.frame_fps = frame_fps
+        self.frame_interval = 1 / frame_fps
+        self.frame_resolution = cfg.frame_resolution
+        self.frame_num_tokens = cfg.frame_num_tokens
+        self.score_heads = list(score_heads)
+        self.stream_end_prob_threshold = stream_end_prob_threshold
+        self.stream_end_score_sum_threshold = stream_end_score_sum_threshold
+        self.running_list_length = running_list_length
+        self._start_ids = start_ids.reshape(1, -1).to(model.device)
+        self._added_stream_prompt_ids = None if added_stream_prompt_ids is None else \
+            added_stream_prompt_ids.reshape(1, -1).to(model.device)
+        self._cache_args = dict(alt_cache=alt_cache, window_length=window_length, num_sink_tokens=num_sink_tokens,
+                                sink_cache=sink_cache, n_sys=self._start_ids.shape[1])
+        self._max_frames = max_frames
+        self._score_buf = torch.zeros(max_frames, 3, dtype=torch.float32, device=model.device)
+        self.reset()
+
+    # ---- state (test/inference.py:112-155) ----
+    def _init_cache(self):
+        max_chunk = max(self._start_ids.shape[1] + self.frame_num_tokens + 8, 256)
+        self.past_key_values = self.model.new_cache(max_chunk=max_chunk, **self._cache_args)
+
+    def reset(self):
+        self.query_queue = deque()
+        self.frame_embeds_queue = deque()
+        self.video_time = 0
+        self.last_frame_idx = -1
+        self.video_tensor = None
+        self.last_ids = torch.tensor([[]], device=self.model.device, dtype=torch.long)
+        self._init_cache()
+        self.debug_data_list = []
+        self.generated_token_ids = []
+        self.num_frames_no_reply = 0
+        self.stream_end_prob_list = []
+        self.stream_end_score_sum = 0
+        self.consec_frames = 0
+        self.init_vision_time = False
+        self.response_needed = []
+        self._n_scored = 0
+        self._times = []
+
+    def set_fps(self, fps=None, frame_interval=None):
+        assert fps is not None or frame_interval is not None
+        self.frame_fps = fps or 1 / frame_interval
+        self.frame_interval = 1 / self.frame_fps
+
+    # ---- vision (test/inference.py:169-187, test/live_infer_for_video.py:98-128) ----
+    def input_video_stream(self, video_frames: torch.Tensor, batch_size: int = 32):
+        """uint8 [T, 3, S, S]; embeds stay on the device."""
+        for b in range(0, len(video_frames), batch_size):
+            emb = self.model.visual_embed(video_frames[b:b + batch_size]).split(self.frame_num_tokens)
+            for r, f in enumerate(emb):
+                self.frame_embeds_queue.append(((r + b) / self.frame_fps, f))
+
+    def load_one_frame(self, frame: torch.Tensor):
+        emb = self.model.visual_embed(frame.reshape(1, *frame.shape[-3:]))
+        self.frame_embeds_queue.append((self.video_time if not self.frame_embeds_queue else
+                                        self.frame_embeds_queue[-1][0] + self.frame_interval, emb))
+
+    def input_query_stream(self, query_ids: torch.Tensor, video_time: float = 0.0):
+        """The reference tokenises a chat turn (test/inference.py:157-167); without a tokenizer the ids are given."""
+        self.query_queue.append((video_time, query_ids.reshape(1, -1).to(self.model.device)))
+
+    # ---- one chunk (test/inference.py:196-262) ----
+    def _encode_frame(self):
+        video_time, frame_embeds = self.frame_embeds_queue.popleft()
+        if not self.init_vision_time:
+            self.last_ids = self._start_ids
+            self.init_vision_time = True
+        elif self.last_ids is None:
+            self.last_ids = torch.tensor([[]], device=self.model.device, dtype=torch.long)
+        x = self.model.assemble_chunk(self.last_ids, frame_embeds)
+        if self._n_scored >= self._max_frames:
+            raise RuntimeError("score buffer full: raise max_frames")
+        slot = self._score_buf[self._n_scored:self._n_scored + 1]
+        out = self.model(inputs_embeds=x, use_cache=True, past_key_values=self.past_key_values, return_dict=True,
+                         scores_out=slot)
+        self.past_key_values = out.past_key_values
+        self.last_ids = None
+        self._times.append(video_time)
+        self._n_scored += 1
+        return out
+
+    def _encode_query(self):
+        _, ids = self.query_queue.popleft()
+        x = self.model.assemble_chunk(ids, None)
+        out = self.model(inputs_embeds=x, use_cache=True, past_key_values=self.past_key_values, return_dict=True)
+        self.past_key_values = out.past_key_values
+        self.last_query_output = out
+        return out
+
+    def input_one_frame(self):
+        """One iteration of the loop (test/live_infer_for_video.py:135-176)."""
+        if self.query_queue and self.video_time >= self.query_queue[0][0]:
+            self._encode_query()
+        self._encode_frame()
+        if self.stream_end_prob_threshold is not None or self.stream_end_score_sum_threshold is not None:
+            inf, rel, unc = self._score_buf[self._n_scored - 1].tolist()       # one sync, only when a decision is due
+            scores = dict(informative_score=inf, relevance_score=rel)
+            stream_end_score = sum(v for k, v in scores.items() if k in self.score_heads)
+            self.stream_end_prob_list.append(stream_end_score)
+            self.stream_end_score_sum += stream_end_score
+            if isinstance(self.running_list_length, int) and self.running_list_length > 0:
+                self.stream_end_prob_list = self.stream_end_prob_list[-self.running_list_length:]
+            need = False
+            if self.stream_end_score_sum_threshold is not None and self.stream_end_score_sum > self.stream_end_score_sum_threshold:
+                need = True
+                self.stream_end_score_sum = 0
+            if self.stream_end_prob_threshold is not None and stream_end_score > self.stream_end_prob_threshold:
+                need = True
+            if need:
+                self.response_needed.append(self.video_time)
+        self.video_time += 1 / self.frame_fps
+
+    def inference(self):
+        """test/inference.py:283-334; fills `debug_data_list` with one dict per frame."""
+        while self.frame_embeds_queue:
+            self.input_one_frame()
+        self._flush_scores()
+        return self.debug_data_list
+
+    def _flush_scores(self):
+        n0 = len(self.debug_data_list)
+        if self._n_scored > n0:
+            host = self._score_buf[n0:self._n_scored].cpu().tolist()          # the single device->host read
+            for t, (inf, rel, unc) in zip(self._times[n0:self._n_scored], host):
+                self.debug_data_list.append(dict(time=t, informative_score=inf, relevance_score=rel, uncertainty_score=unc))
+
+    # ---- post-processing (test/live_infer_for_video.py:195-228) ----
+    def find_ticks(self, scores, fps, min_separation=10, prominence=0.02, thresh=False, verbose=False):
+        return _find_ticks(scores, fps, min_separation, prominence, thresh, verbose, device=self.model.device)
+
+
+LiveInferForDemo = LiveInferForBenchmark

@@ -1,0 +1,155 @@
+/* aha_b200.h - C-ABI of libaha_b200.so: the B200-native (sm_100a) implementation of Aha!'s per-frame streaming
+ * ingest-and-score step.
+ *
+ * The reference (aiden200/Aha-) has no FFI: the path is reached through three Python surfaces.
+ * Every entry point below states the reference interface it replaces (file:line relative to the reference repo);
+ * aha_b200/*.py are thin ctypes wrappers that keep the reference's class / method names on top of these calls.
+ *
+ * Conventions
+ *   - plain C types only: device pointers, sizes, CUDA stream as void* (cudaStream_t); no torch types.
+ *   - every function returns 0 on success, AHA_ERR_VALUE (-1) where the reference would raise ValueError
+ *     (bad geometry / shape), AHA_ERR_RUNTIME (-2) where it would raise RuntimeError (CUDA failure);
+ *     aha_last_error() returns the thread-local message.
+ *   - all work is enqueued on the caller's stream; no hidden synchronisation, no host callbacks.
+ *   - handles are bound to one device and are not thread-safe; one process (or thread + handle set) per GPU.
+ *   - bf16 tensors are passed as const void* (uint16 storage).
+ */
+#ifndef AHA_B200_H_
+#define AHA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AHA_OK 0
+#define AHA_ERR_VALUE (-1)
+#define AHA_ERR_RUNTIME (-2)
+
+#define AHA_POLICY_SINK 0    /* test/sink_cache.py:7-164 */
+#define AHA_POLICY_SLIDING 1 /* test/sliding_window_cache.py:5-53 */
+#define AHA_POLICY_STATIC 2  /* test/static_cache.py:5-47 */
+
+#define AHA_MASK_SDPA 0 /* allowed(i,j) <=> j <= L + i           (transformers 4.49 sdpa/eager mask sliced to Klen) */
+#define AHA_MASK_FA2 1  /* allowed(i,j) <=> j <= i + (Klen - q)  (flash-attn bottom-right causal) */
+
+#define AHA_LOGITS_NONE 0
+#define AHA_LOGITS_LAST 1 /* lm_head on the last token of every stream's chunk only */
+#define AHA_LOGITS_ALL 2  /* video_head_live_llava_qwen.py:175 (all q positions) */
+
+#define AHA_POOL_BILINEAR 0 /* video_head_live_llava_qwen.py:128-131 */
+#define AHA_POOL_AVERAGE 1  /* :124-125 */
+#define AHA_POOL_MAX 2      /* :126-127 */
+#define AHA_POOL_ADAPTIVE 3 /* models/vision_live.py:21-26 (adaptive_avg_pool2d) */
+
+typedef struct aha_model_s* aha_model_t;
+typedef struct aha_cache_s* aha_cache_t;
+
+/* Shapes of VideoHeadLiveLlavaQwenConfig (models/live_llava/video_head_live_llava_qwen.py:43-47) + SigLipVisionConfig
+ * (LLaVA_NeXT/llava/model/multimodal_encoder/siglip_encoder.py:70-115). */
+typedef struct {
+  int hidden, inter, layers, heads, kv_heads, head_dim, vocab;
+  float rope_theta, rms_eps;
+  int v_hidden, v_inter, v_layers /* layers actually run: 26 */, v_heads, v_patch, v_image;
+  float v_eps;
+  int pool_stride, pool_mode;
+  int max_tokens; /* largest streams*q one aha_prefill_chunk call will see (workspace sizing) */
+  int max_frames; /* largest n_frames one aha_vision_embed call will see */
+} aha_model_desc;
+
+/* One state-dict entry, named exactly as in the reference checkpoint ("model.layers.0.self_attn.q_proj.weight", ...). */
+typedef struct {
+  const char* name;
+  const void* ptr; /* device pointer, bf16, contiguous */
+} aha_weight_entry;
+
+const char* aha_last_error(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+unsigned long long aha_launch_count(void);
+
+/* ---- model: replaces build_model_and_tokenizer()'s from_pretrained result as far as the hot path needs it
+ *      (models/modeling_live.py:96-181).  Packs the weights it is given into its own device layouts (fused QKV,
+ *      interleaved gate/up, padded vision heads); the caller may free its copies afterwards. ---- */
+int aha_model_create(const aha_model_desc* desc, const aha_weight_entry* weights, int n_weights, int device,
+                     aha_model_t* out);
+int aha_model_destroy(aha_model_t m);
+
+/* ---- KV caches: SinkCache(window_length, num_sink_tokens) test/sink_cache.py:10, SlidingWindowCache(window_length)
+ *      test/sliding_window_cache.py:10, TrulyStaticCache(window_size) test/static_cache.py:11.
+ *      Storage is a device ring buffer; eviction never moves surviving tokens. ---- */
+int aha_cache_create(int n_layers, int kv_heads, int head_dim, int policy, int window, int sinks, int max_chunk,
+                     int device, aha_cache_t* out);
+int aha_cache_reset(aha_cache_t c);
+int aha_cache_destroy(aha_cache_t c);
+/* Cache.update(key_states, value_states, layer_idx, {"cos","sin"}): k/v are [1, kv_heads, q, d] bf16 with the given
+ * element strides; k is already rotated at positions [L, L+q).  cos/sin are [q, d] bf16 (may be NULL: no re-rotation,
+ * sink_cache.py:101).  test/sink_cache.py:74-164, test/sliding_window_cache.py:18-44, test/static_cache.py:18-38. */
+int aha_cache_update(aha_cache_t c, int layer, const void* k, const void* v, long long k_head_stride,
+                     long long k_token_stride, long long v_head_stride, long long v_token_stride, const void* cos,
+                     const void* sin, int q, void* stream);
+/* get_seq_length(layer_idx): sink_cache.py:57-62, sliding_window_cache.py:46-49, static_cache.py:43-47 */
+int aha_cache_seq_length(aha_cache_t c, int layer, int* out);
+/* SinkCache._seen_tokens (sink_cache.py:105-106) */
+int aha_cache_seen_tokens(aha_cache_t c, long long* out);
+/* Logical-order materialisation of what update() returns: K_out/V_out [kv_heads, len, d] bf16, provenance_out [len]
+ * int32 global token ids (may each be NULL). */
+int aha_cache_export(aha_cache_t c, int layer, void* K_out, void* V_out, int32_t* provenance_out, void* stream);
+
+/* ---- vision: LiveMixin.visual_embed (models/modeling_live.py:31-37) = SigLipVisionTower.forward
+ *      (siglip_encoder.py:576-589) -> connector (video_head_live_llava_qwen.py:107-108) -> post_projector_pooling
+ *      (:117-136).  Give either uint8 frames [n,3,S,S] (preprocess of siglip_encoder.py:47-67 is fused in) or bf16
+ *      pixel_values [n,3,S,S]; the other pointer NULL.  out: [n * frame_num_tokens, hidden] bf16. ---- */
+int aha_vision_embed(aha_model_t m, const uint8_t* frames_u8, const void* pixel_values_bf16, int n_frames, void* out,
+                     void* stream);
+
+/* ---- chunk assembly: _encode_frame's torch.cat([embed_tokens(last_ids), frame_embeds]) (test/inference.py:204-214).
+ *      ids: [n_ids] int64 device (may be NULL when n_ids == 0); frame_embeds [n_frame_tokens, hidden] bf16. ---- */
+int aha_assemble_chunk(aha_model_t m, const int64_t* ids, int n_ids, const void* frame_embeds, int n_frame_tokens,
+                       void* out, void* stream);
+
+/* ---- the per-frame step: VideoHeadLiveLlavaQwenForCausalLM.forward(inputs_embeds=[1,q,H], past_key_values=cache,
+ *      use_cache=True) (video_head_live_llava_qwen.py:138-188, inference branch) for n_streams independent streams at
+ *      once: inputs_embeds [n_streams*q, H] bf16 (stream-major), one cache per stream, all with the same q.
+ *      Outputs (each may be NULL): logits fp32 [n_streams*q, V] (ALL) or [n_streams, V] (LAST); informative fp32
+ *      [n*q, 2]; relevance fp32 [n*q, 1] (post-sigmoid); uncertainty fp32 [n*q, 1] (log-variance); scores3 fp32
+ *      [n_streams, 3] = (softmax(informative[-1])[1], relevance[-1], exp(uncertainty[-1])) (test/inference.py:222-227);
+ *      hidden_out bf16 [n*q, H] = final-norm output. ---- */
+int aha_prefill_chunk(aha_model_t m, const aha_cache_t* caches, int n_streams, const void* inputs_embeds, int q,
+                      int mask_mode, int logits_mode, float* logits, float* informative, float* relevance,
+                      float* uncertainty, float* scores3, void* hidden_out, void* stream);
+
+/* ---- post-processing: find_ticks (test/live_infer_for_video.py:195-228, test/live_video/infer_live_video.py:70-91):
+ *      savgol_filter(15,3,'interp') -> thresh = mean + 0.5*std (unless thresh[s] given, NaN = auto) -> find_peaks(height,
+ *      prominence, distance).  scores: [n_streams, T] f64 device.  peaks: [n_streams, max_peaks] int32, n_peaks
+ *      [n_streams] int32 (n_peaks[s] > max_peaks signals truncation); smoothed_out [n_streams, T] f64 and thresh_out
+ *      [n_streams] f64 optional.  T >= 15 (scipy raises otherwise -> AHA_ERR_VALUE). ---- */
+int aha_find_ticks(const double* scores, int n_streams, int T, double prominence, int distance,
+                   const double* thresh_or_null, int32_t* peaks, int max_peaks, int32_t* n_peaks, double* smoothed_out,
+                   double* thresh_out, void* stream);
+
+/* ---- single operators, exported for the parity tests and for callers that run their own layer loop ---- */
+/* out[tokens, features] = X[tokens, K] . W[features, K]^T (+bias) (activation) (+residual); nn.Linear replacement. */
+int aha_gemm_bf16(const void* x, int tokens, int ldx, const void* w, int features, int ldw, int K, void* out, int ldo,
+                  int out_f32, int round_bf16, int act, const void* bias, const void* residual, int ldr, int res_mod,
+                  int force_swap, int force_bn, int force_splits, void* stream);
+/* Qwen2RMSNorm (transformers 4.49 modeling_qwen2.py) */
+int aha_rmsnorm(const void* x, const void* weight, void* out, int rows, int cols, float eps, void* stream);
+/* nn.LayerNorm (siglip_encoder.py:265,267) */
+int aha_layernorm(const void* x, const void* weight, const void* bias, void* out, int rows, int cols, float eps,
+                  void* stream);
+/* SigLipImageProcessor.preprocess (siglip_encoder.py:47-67) + .to(bf16): uint8 [n] -> bf16 [n] */
+int aha_preprocess(const uint8_t* frames_u8, void* out_bf16, long long n, void* stream);
+/* post_projector_pooling (video_head_live_llava_qwen.py:117-136): [frames, side*side, C] -> [frames, out*out, C] */
+int aha_pool(const void* x, void* out, int frames, int side, int channels, int stride, int mode, void* stream);
+/* Qwen2RotaryEmbedding: cos/sin [q, d] bf16 for positions pos0 .. pos0+q-1 */
+int aha_rope_table(int pos0, int q, int head_dim, float theta, void* cos_out, void* sin_out, void* stream);
+/* attention of a chunk against explicit K/V: q [kv_heads, nq, group, d], k/v [kv_heads, klen, d] bf16 contiguous, out
+ * [nq, heads*d]; allowed(i,j) <=> j <= off + i (pass off >= klen for no mask).  Used by the parity tests. */
+int aha_attention(const void* q, const void* k, const void* v, void* out, int heads, int kv_heads, int nq, int klen,
+                  int head_dim, int off, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AHA_B200_H_ */
