@@ -348,7 +348,7 @@ int op_preprocess(const uint8_t* in, bf16* out, long long n, cudaStream_t st) {
 int op_patchify(const uint8_t* frames_u8, const bf16* pixels, bf16* out, int n, int image, int patch, int kpad,
                 cudaStream_t st) {
   AHA_REQUIRE((frames_u8 != nullptr) != (pixels != nullptr), "patchify: give exactly one of frames_u8 / pixel_values");
-  AHA_REQUIRE(n > 0 && image % patch == 0 && kpad >= 3 * patch * patch, "patchify: bad geometry");
+  AHA_REQUIRE(n > 0 && image >= patch && kpad >= 3 * patch * patch, "patchify: bad geometry");
   const int side = image / patch;
   const long long total = (long long)n * side * side * (3 * patch + 1);
   if (frames_u8) patchify_kernel<true><<<grid_for(total, 256, 148 * 32), 256, 0, st>>>(frames_u8, nullptr, out, n, image, patch, kpad);

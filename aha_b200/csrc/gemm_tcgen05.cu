@@ -32,6 +32,7 @@
 
 #include <cuda.h>
 #include <cooperative_groups.h>
+#include <deque>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -372,6 +373,27 @@ int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap
 
 namespace {
 
+struct ProfSlot { cudaEvent_t e0, e1; int cls; double bytes, flops; };
+std::deque<ProfSlot> g_prof;
+std::mutex g_prof_mu;
+bool g_prof_enabled = false;
+
+ProfSlot* prof_begin(int cls, cudaStream_t st) {
+  if (!g_prof_enabled) return nullptr;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (g_prof.size() >= 200000) return nullptr;
+  ProfSlot s{};
+  s.cls = cls;
+  if (cudaEventCreate(&s.e0) != cudaSuccess || cudaEventCreate(&s.e1) != cudaSuccess) return nullptr;
+  cudaEventRecord(s.e0, st);
+  g_prof.push_back(s);
+  return &g_prof.back();
+}
+void prof_end(ProfSlot* s, cudaStream_t st, double bytes, double flops) {
+  s->bytes = bytes; s->flops = flops;
+  cudaEventRecord(s->e1, st);
+}
+
 template <int BN>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
   using C = Cfg<BN>;
@@ -447,10 +469,40 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
   dim3 grid(tiles_a, tiles_b, splits);
+  ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);
   switch (bn) {
-    case 32: return launch_bn<32>(ta, tb, p, grid, stream);
-    case 64: return launch_bn<64>(ta, tb, p, grid, stream);
-    case 128: return launch_bn<128>(ta, tb, p, grid, stream);
-    default: return launch_bn<256>(ta, tb, p, grid, stream);
+    case 32: rc = launch_bn<32>(ta, tb, p, grid, stream); break;
+    case 64: rc = launch_bn<64>(ta, tb, p, grid, stream); break;
+    case 128: rc = launch_bn<128>(ta, tb, p, grid, stream); break;
+    default: rc = launch_bn<256>(ta, tb, p, grid, stream); break;
   }
+  if (slot) {
+    const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * (c.out_f32 ? 4 : 2);
+    prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,
+             2.0 * c.tokens * (double)c.features * c.K);
+  }
+  return rc;
+}
+
+// ---- optional per-launch CUDA-event timing of the GEMM launches (bench.py's roofline leg) ----
+extern "C" int aha_profile_gemm(int enable) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (auto& s : g_prof) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
+  g_prof.clear();
+  g_prof_enabled = enable != 0;
+  return AHA_OK;
+}
+// cls 0 = skinny (weight-streaming, tokens <= 256), 1 = tall.  Synchronises the recorded events.
+extern "C" int aha_profile_gemm_read(int cls, double* ms, long long* launches, double* bytes, double* flops) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  double t = 0, b = 0, f = 0; long long n = 0;
+  for (auto& s : g_prof) {
+    if (s.cls != cls) continue;
+    AHA_CUDA(cudaEventSynchronize(s.e1));
+    float e = 0.f;
+    AHA_CUDA(cudaEventElapsedTime(&e, s.e0, s.e1));
+    t += e; b += s.bytes; f += s.flops; ++n;
+  }
+  if (ms) *ms = t; if (launches) *launches = n; if (bytes) *bytes = b; if (flops) *flops = f;
+  return AHA_OK;
 }

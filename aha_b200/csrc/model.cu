@@ -365,7 +365,7 @@ int aha_model_create(const aha_model_desc* desc, const aha_weight_entry* weights
   AHA_REQUIRE(d.head_dim == 64 || d.head_dim == 128, "decoder head_dim must be 64 or 128");
   AHA_REQUIRE(d.v_hidden % d.v_heads == 0 && d.v_hidden % 8 == 0 && d.v_inter % 8 == 0, "bad vision shape");
   AHA_REQUIRE((d.v_hidden / d.v_heads) % 8 == 0 && d.v_hidden / d.v_heads <= 128, "vision head_dim must be a multiple of 8, <= 128");
-  AHA_REQUIRE(d.v_image % d.v_patch == 0, "image size must be a multiple of the patch size");
+  AHA_REQUIRE(d.v_image >= d.v_patch && d.v_patch > 0, "image smaller than one patch");  // conv stride = patch: trailing pixels are ignored
   AHA_REQUIRE(d.max_tokens > 0 && d.max_frames > 0, "max_tokens / max_frames must be positive");
   AHA_REQUIRE(d.pool_mode >= 0 && d.pool_mode <= 3, "Unexpected mm_spatial_pool_mode");
   AHA_CUDA(cudaSetDevice(device));

@@ -68,6 +68,11 @@ const char* aha_last_error(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 unsigned long long aha_launch_count(void);
 
+/* Optional CUDA-event timing of every GEMM launch (bench.py's roofline leg): enable, run, then read the summed launch
+ * durations [ms], launch count, algorithmic bytes and FLOPs of class 0 (weight-streaming, tokens <= 256) or 1 (tall). */
+int aha_profile_gemm(int enable);
+int aha_profile_gemm_read(int cls, double* ms, long long* launches, double* bytes, double* flops);
+
 /* ---- model: replaces build_model_and_tokenizer()'s from_pretrained result as far as the hot path needs it
  *      (models/modeling_live.py:96-181).  Packs the weights it is given into its own device layouts (fused QKV,
  *      interleaved gate/up, padded vision heads); the caller may free its copies afterwards. ---- */

@@ -182,6 +182,17 @@ def synthetic_frames(n: int, image: int = 384, seed: int = 1, smooth: int = 4) -
     return ((up * 0.8 + noise).clamp(0, 1) * 255).to(torch.uint8)
 
 
+def synthetic_frames_varied(n: int, image: int = 384, seed: int = 5) -> torch.Tensor:
+    """uint8 frames whose brightness and coarse pattern change from frame to frame, so that the per-frame scores
+    spread far more than one bf16 step (rank correlation is meaningless on a flat score stream)."""
+    g = torch.Generator().manual_seed(seed)
+    a = torch.rand(n, 1, 1, 1, generator=g)
+    base = torch.rand(n, 3, image, image, generator=g)
+    pat = torch.rand(n, 3, 6, 6, generator=g)
+    up = F.interpolate(pat, size=(image, image), mode="nearest")
+    return ((0.15 + 0.85 * a) * (0.6 * up + 0.4 * base) * 255).clamp(0, 255).to(torch.uint8)
+
+
 # ----------------------------------------------------------------------------------------------
 # A1 preprocess (siglip_encoder.py:47-67; frames are already 384x384 so the bicubic resize is the identity)
 # ----------------------------------------------------------------------------------------------
