@@ -6,10 +6,11 @@
 //     per (stream, kv head) the q*group query rows (GQA heads folded into the M dimension) against the cache's
 //     physical ring slots; the reference's mask rule allowed(i, j) <=> logical(j) <= off + i is
 //     evaluated from the ring geometry, so keys are streamed in PHYSICAL order (softmax is order independent) and an
-//     eviction never has to move them.
+//     eviction never has to move them.  A chunk has only a few query tiles, so the key axis is split over a thread-block
+//     cluster (flash-decoding style) and the partial (O, m, l) are merged through distributed shared memory in rank order.
 //   * SigLIP self-attention (siglip_encoder.py:197-239): per (frame, head) 729 x 729, head_dim 72 padded to 80 columns.
 //
-// CTA = one 128-row query tile of one (segment, head block).  Warp roles:
+// CTA = one 128-row query tile of one (segment, head block, key split).  Warp roles:
 //   warp 0    TMA producer: Q once, then a 2-stage ring of {K tile, V tile} (128 keys each)
 //   warp 1    MMA issuer (one elected lane): S[b] = Q.K^T for tile kt+1 is issued before P.V of tile kt, so the
 //             tensor pipe works on the next scores while the softmax warps are busy with the current ones
@@ -20,10 +21,12 @@
 #include "ops.h"
 #include "gemm.h"
 #include "ptx_sm100.cuh"
-#include <cstdlib>
+#include <cooperative_groups.h>
 #include <cstdio>
+#include <cstdlib>
 
 using namespace sm100;
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -44,10 +47,32 @@ struct AttnSmem {
   static __host__ __device__ int total(int DB) { return bar_off(DB) + 256 + 1024; }
 };
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// bit t of the result: key slot p0 + t is visible to a query whose logical limit is `limit`
+__device__ __noinline__ uint32_t visible_mask32(const AttnSeg& seg, int p0, int limit) {
+  uint32_t vm = 0;
+#pragma unroll 1
+  for (int t = 0; t < 32; ++t) {
+    const int pslot = p0 + t;
+    int j = pslot;
+    if (seg.ring_R > 0 && pslot >= seg.ring_S) {
+      j = pslot - seg.ring_S - seg.ring_base;
+      if (j < 0) j += seg.ring_R;
+      j += seg.ring_S;
+    }
+    if (pslot < seg.klen && j <= limit) vm |= 1u << t;
+  }
+  return vm;
+}
+
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
-                 const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ AttnProblem p, const uint32_t v_lbo,
-                 const uint32_t v_sbo) {
+                 const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ AttnProblem p, const int splits) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int DB = (p.d_pad + 63) >> 6;
@@ -65,10 +90,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const AttnSeg& seg = p.segs[blockIdx.z];
+  const int seg_idx = blockIdx.z / splits, split = blockIdx.z % splits;
+  const AttnSeg& seg = p.segs[seg_idx];
   const int blk = blockIdx.y;
   const int qt = blockIdx.x;
-  const int nkt = (seg.klen + kTile - 1) / kTile;
+  const int nkt_all = (seg.klen + kTile - 1) / kTile;
+  const int per = (nkt_all + splits - 1) / splits;
+  const int kt0 = split * per;
+  const int nkt = max(0, min(nkt_all, kt0 + per) - kt0);   // key tiles of this CTA: kt0 .. kt0 + nkt - 1
   const int stage_bytes = DB * kAtomBytes;
 
   if (warp == 0 && lane == 0) { prefetch_tensormap(&tmap_q); prefetch_tensormap(&tmap_k); prefetch_tensormap(&tmap_v); }
@@ -86,6 +115,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // softmax-thread state (meaningful in warps 4-7)
+  const int ew = warp & 3;
+  const int row = ew * 32 + lane;            // tile row == TMEM lane
+  const int m = qt * kTile + row;            // query row inside the (segment, block)
+  const bool row_valid = m < p.nq_rows;
+  const int tok = m / p.group;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
+  float m_used = -INFINITY, l_sum = 0.f;
+
   if (nkt > 0) {
     if (warp == 0) {
       // ===================== TMA producer =====================
@@ -96,14 +134,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int b = 0; b < DB; ++b) tma_load_2d(sQ + b * kAtomBytes, &tmap_q, q_full, q_col + b * 64, q_row);
         const int k_row = seg.k_row0 + blk * p.k_head_rows, k_col = p.k_col0 + blk * p.k_col_step;
         const int v_row = seg.v_row0 + blk * p.k_head_rows, v_col = p.v_col0 + blk * p.v_col_step;
-        for (int kt = 0; kt < nkt; ++kt) {
-          const int s = kt % kStagesKV;
-          const uint32_t ph = (kt / kStagesKV) & 1;
+        for (int it = 0; it < nkt; ++it) {
+          const int s = it % kStagesKV;
+          const uint32_t ph = (it / kStagesKV) & 1;
           mbar_wait(&kv_empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&kv_full[s], 2 * stage_bytes);
+          const int key0 = (kt0 + it) * kTile;
           for (int b = 0; b < DB; ++b) {
-            tma_load_2d(sK + s * stage_bytes + b * kAtomBytes, &tmap_k, &kv_full[s], k_col + b * 64, k_row + kt * kTile);
-            tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, &tmap_v, &kv_full[s], v_col + b * 64, v_row + kt * kTile);
+            tma_load_2d(sK + s * stage_bytes + b * kAtomBytes, &tmap_k, &kv_full[s], k_col + b * 64, k_row + key0);
+            tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, &tmap_v, &kv_full[s], v_col + b * 64, v_row + key0);
           }
         }
       }
@@ -113,88 +152,77 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const uint32_t idesc_qk = make_idesc_bf16_f32(kTile, kTile);
         const uint32_t idesc_pv = make_idesc_bf16_f32_bmn(kTile, (uint32_t)p.d_pad);
         const int ksteps = p.d_pad >> 4;
-        auto issue_qk = [&](int kt) {
-          const int s = kt % kStagesKV;
-          mbar_wait(&kv_full[s], (kt / kStagesKV) & 1);
+        auto issue_qk = [&](int it) {
+          const int s = it % kStagesKV;
+          mbar_wait(&kv_full[s], (it / kStagesKV) & 1);
           tc_fence_after();
           const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + s * stage_bytes);
           for (int ks = 0; ks < ksteps; ++ks) {
             const uint32_t o = (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32;
-            umma_f16_ss(tmem_base + ((kt & 1) ? kColS1 : kColS0), make_kmajor_sw128_desc(qa + o),
+            umma_f16_ss(tmem_base + ((it & 1) ? kColS1 : kColS0), make_kmajor_sw128_desc(qa + o),
                         make_kmajor_sw128_desc(ka + o), idesc_qk, ks != 0);
           }
-          umma_commit(&s_full[kt & 1]);
+          umma_commit(&s_full[it & 1]);
         };
         mbar_wait(q_full, 0);
         issue_qk(0);
-        for (int kt = 0; kt < nkt; ++kt) {
-          if (kt + 1 < nkt) issue_qk(kt + 1);
-          mbar_wait(p_full, kt & 1);
+        for (int it = 0; it < nkt; ++it) {
+          if (it + 1 < nkt) issue_qk(it + 1);
+          mbar_wait(p_full, it & 1);
           tc_fence_after();
-          const int s = kt % kStagesKV;
+          const int s = it % kStagesKV;
           const uint32_t pa = smem_u32(sP), va = smem_u32(sV + s * stage_bytes);
           for (int ks = 0; ks < kTile / 16; ++ks) {
             const uint64_t da = make_kmajor_sw128_desc(pa + (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32);
-            const uint64_t db = make_mnmajor_sw128_desc(va + (uint32_t)ks * 2048, v_lbo, v_sbo);
-            umma_f16_ss(tmem_base + kColO, da, db, idesc_pv, (kt | ks) != 0);
+            // V tile is MN-major: 64-column blocks kAtomBytes apart (LBO), 8-key groups 1024 B apart (SBO)
+            const uint64_t db = make_mnmajor_sw128_desc(va + (uint32_t)ks * 2048, kAtomBytes, 1024);
+            umma_f16_ss(tmem_base + kColO, da, db, idesc_pv, (it | ks) != 0);
           }
           umma_commit(&kv_empty[s]);
           umma_commit(pv_done);
         }
       }
     } else if (warp >= 4) {
-      // ===================== softmax / correction / epilogue =====================
-      const int ew = warp & 3;
-      const int row = ew * 32 + lane;            // tile row == TMEM lane
-      const int m = qt * kTile + row;            // query row inside the (segment, block)
-      const bool row_valid = m < p.nq_rows;
-      const int tok = m / p.group;
+      // ===================== softmax / correction =====================
       const int limit = seg.off + tok;           // logical key index must be <= limit
-      const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
       const float sl2 = p.scale * 1.4426950408889634f;
       const bool all_visible = seg.off >= seg.klen - 1;
-      float m_used = -INFINITY, l_sum = 0.f;
       uint8_t* prow = sP + row * 128;
-      for (int kt = 0; kt < nkt; ++kt) {
-        mbar_wait(&s_full[kt & 1], (kt >> 1) & 1);
+      for (int it = 0; it < nkt; ++it) {
+        const int kt = kt0 + it;
+        mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
-        const uint32_t s_addr = lane_addr + ((kt & 1) ? kColS1 : kColS0);
-        const bool need_mask = !(all_visible && (kt * kTile + kTile <= seg.klen));
-        auto visible = [&](int c) -> bool {
-          const int pslot = kt * kTile + c;
-          if (pslot >= seg.klen) return false;
-          int j = pslot;
-          if (seg.ring_R > 0 && pslot >= seg.ring_S) {
-            j = pslot - seg.ring_S - seg.ring_base;
-            if (j < 0) j += seg.ring_R;
-            j += seg.ring_S;
-          }
-          return j <= limit;
-        };
-        // pass 1: tile maximum of this row
-        float tmax = -INFINITY;
-#pragma unroll 1
-        for (int cc = 0; cc < kTile; cc += 32) {
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(s_addr + cc, r);
-          tmem_ld_wait();
+        const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0);
+        uint32_t sv[kTile];
+        tmem_ld_32x32b_x32p(s_addr, sv);
+        tmem_ld_32x32b_x32p(s_addr + 32, sv + 32);
+        tmem_ld_32x32b_x32p(s_addr + 64, sv + 64);
+        tmem_ld_32x32b_x32p(s_addr + 96, sv + 96);
+        tmem_ld_wait();
+        if (!(all_visible && (kt * kTile + kTile <= seg.klen))) {
+          // slow path (growing cache / ragged last tile): knock masked scores out before the statistics
 #pragma unroll
-          for (int t = 0; t < 32; ++t) {
-            float x = __uint_as_float(r[t]) * sl2;
-            if (need_mask && !visible(cc + t)) x = -INFINITY;
-            tmax = fmaxf(tmax, x);
+          for (int c = 0; c < 4; ++c) {
+            const uint32_t vm = visible_mask32(seg, kt * kTile + c * 32, limit);
+#pragma unroll
+            for (int t = 0; t < 32; ++t)
+              if (!((vm >> t) & 1u)) sv[c * 32 + t] = 0xff800000u;   // -inf
           }
         }
+        float tmax = -INFINITY;
+#pragma unroll
+        for (int t = 0; t < kTile; ++t) tmax = fmaxf(tmax, __uint_as_float(sv[t]));
+        tmax *= sl2;                                 // scale > 0: max commutes with the scaling
         float alpha = 1.f;
         bool rescale = false;
         if (tmax > m_used + kRescaleThreshold || (m_used == -INFINITY && tmax > -INFINITY)) {
-          alpha = (m_used == -INFINITY) ? 0.f : exp2f(m_used - tmax);
+          alpha = (m_used == -INFINITY) ? 0.f : ex2_approx(m_used - tmax);
           m_used = tmax;
           rescale = true;
         }
         // P smem and O are owned by the tensor pipe until P.V of the previous tile has completed
-        if (kt > 0) mbar_wait(pv_done, (kt - 1) & 1);
-        if (kt > 0 && __any_sync(0xffffffffu, rescale)) {
+        if (it > 0) mbar_wait(pv_done, (it - 1) & 1);
+        if (it > 0 && __any_sync(0xffffffffu, rescale)) {
           tc_fence_after();
 #pragma unroll 1
           for (int cc = 0; cc < p.d_pad; cc += 16) {
@@ -208,23 +236,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           tmem_st_wait();
         }
         l_sum *= alpha;
-        // pass 2: probabilities -> bf16 -> swizzled K-major P tile
+        // probabilities -> bf16 -> swizzled K-major P tile
         const float mref = (m_used == -INFINITY) ? 0.f : m_used;
-#pragma unroll 1
+        float acc_l = 0.f;
+#pragma unroll
         for (int cc = 0; cc < kTile; cc += 32) {
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(s_addr + cc, r);
-          tmem_ld_wait();
           uint32_t pk[16];
 #pragma unroll
           for (int t = 0; t < 32; t += 2) {
-            float x0 = exp2f(__uint_as_float(r[t]) * sl2 - mref);
-            float x1 = exp2f(__uint_as_float(r[t + 1]) * sl2 - mref);
-            if (need_mask) {
-              if (!visible(cc + t)) x0 = 0.f;
-              if (!visible(cc + t + 1)) x1 = 0.f;
-            }
-            l_sum += x0 + x1;
+            const float x0 = ex2_approx(fmaf(__uint_as_float(sv[cc + t]), sl2, -mref));
+            const float x1 = ex2_approx(fmaf(__uint_as_float(sv[cc + t + 1]), sl2, -mref));
+            acc_l += x0 + x1;
             pk[t >> 1] = pack_bf16x2(x0, x1);
           }
           uint8_t* base = prow + (cc >> 6) * kAtomBytes;
@@ -235,20 +257,31 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             *reinterpret_cast<uint4*>(base + sw * 16) = make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
           }
         }
+        l_sum += acc_l;
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(p_full);
       }
-      // epilogue: O / l -> bf16 -> out[token, (blk*group + r)*d + c]
-      mbar_wait(pv_done, (nkt - 1) & 1);
+      mbar_wait(pv_done, (nkt - 1) & 1);   // O complete
       tc_fence_after();
+    }
+  }
+
+  if (splits == 1) {
+    if (warp >= 4) {
+      // epilogue straight from TMEM: O / l -> bf16 -> out[token, (blk*group + r)*d + c]
       const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
       bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
 #pragma unroll 1
       for (int cc = 0; cc < p.d_pad; cc += 16) {
         uint32_t r[16];
-        tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
-        tmem_ld_wait();
+        if (nkt > 0) {
+          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int t = 0; t < 16; ++t) r[t] = 0u;
+        }
         if (row_valid) {
           float v[16];
 #pragma unroll
@@ -259,7 +292,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             st_v4(orow + cc + 8, make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
                                             pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15])));
           } else {
-#pragma unroll
+#pragma unroll 4
             for (int t = 0; t < 16; ++t)
               if (cc + t < p.d) orow[cc + t] = f2b(v[t]);
           }
@@ -267,14 +300,75 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
       tc_fence_before();
     }
-  } else if (warp >= 4) {
-    // no visible keys at all: the reference's softmax over an empty set never happens in practice; write zeros
-    const int m = qt * kTile + (warp & 3) * 32 + lane;
-    if (m < p.nq_rows) {
-      bf16* orow = p.out + (size_t)(seg.out_row0 + m / p.group) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
-      for (int c = 0; c < p.d; ++c) orow[c] = f2b(0.f);
+  } else {
+    // ---- key-split merge over the cluster (1 x 1 x splits), deterministic rank order ----
+    // every CTA parks its unnormalised O (fp32, column-major [d_pad][128]) over the idle K ring and (m, l) over the P tile
+    float* stage = reinterpret_cast<float*>(sK);
+    float* stat_m = reinterpret_cast<float*>(sP);
+    float* stat_l = stat_m + kTile;
+    if (warp >= 4) {
+#pragma unroll 1
+      for (int cc = 0; cc < p.d_pad; cc += 16) {
+        uint32_t r[16];
+        if (nkt > 0) {
+          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int t = 0; t < 16; ++t) r[t] = 0u;
+        }
+#pragma unroll
+        for (int t = 0; t < 16; ++t) stage[(cc + t) * kTile + row] = __uint_as_float(r[t]);
+      }
+      stat_m[row] = m_used;
+      stat_l[row] = l_sum;
+      tc_fence_before();
     }
+    cg::cluster_group cluster = cg::this_cluster();
+    __syncwarp();
+    cluster.sync();
+    if (warp >= 4) {
+      const int rank = (int)cluster.block_rank();
+      float mx = -INFINITY;
+      for (int s = 0; s < splits; ++s) mx = fmaxf(mx, cluster.map_shared_rank(stat_m, s)[row]);
+      float wgt[8];
+      float L = 0.f;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        wgt[s] = 0.f;
+        if (s < splits) {
+          const float ms = cluster.map_shared_rank(stat_m, s)[row];
+          wgt[s] = (ms == -INFINITY) ? 0.f : ex2_approx(ms - mx);
+          L += wgt[s] * cluster.map_shared_rank(stat_l, s)[row];
+        }
+      }
+      const float inv = L > 0.f ? 1.f / L : 0.f;
+      bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
+#pragma unroll 1
+      for (int c = rank; c < (p.d_pad >> 4); c += splits) {
+        const int cc = c * 16;
+        float acc[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          if (s < splits) {
+            const float* peer = cluster.map_shared_rank(stage, s) + cc * kTile + row;
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] += wgt[s] * peer[t * kTile];
+          }
+        }
+        if (row_valid) {
+#pragma unroll 4
+          for (int t = 0; t < 16; ++t)
+            if (cc + t < p.d) orow[cc + t] = f2b(acc[t] * inv);
+        }
+      }
+    }
+    __syncwarp();
+    cluster.sync();   // nobody leaves while peers still read its shared memory
   }
+
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
@@ -298,14 +392,30 @@ int op_attention(const AttnProblem& p, cudaStream_t st) {
     AHA_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_smem = smem;
   }
-  // MN-major V descriptor strides: LBO = bytes between 64-column blocks (one [128][64] box), SBO = 8 keys * 128 B.
-  uint32_t v_lbo = kAtomBytes, v_sbo = 1024;
-  if (const char* e = getenv("AHA_DEBUG_VDESC")) {  // bring-up aid: "lbo,sbo" in bytes
-    unsigned a = 0, b = 0;
-    if (sscanf(e, "%u,%u", &a, &b) == 2) { v_lbo = a; v_sbo = b; }
+  // key-axis split: a frame chunk has only a handful of (query tile, kv head) pairs, far fewer than SMs
+  const int q_tiles = (p.nq_rows + kTile - 1) / kTile;
+  const int ctas = q_tiles * p.n_blocks * p.n_segs;
+  int max_tiles = 0;
+  for (int i = 0; i < p.n_segs; ++i) max_tiles = max_tiles > (p.segs[i].klen + kTile - 1) / kTile ? max_tiles : (p.segs[i].klen + kTile - 1) / kTile;
+  int splits = 1;
+  if (ctas < 148 && max_tiles > 1) {
+    splits = (2 * 148 + ctas - 1) / ctas;
+    if (splits > 8) splits = 8;
+    if (splits > max_tiles) splits = max_tiles;
+    const int per = (max_tiles + splits - 1) / splits;
+    splits = (max_tiles + per - 1) / per;       // no empty splits for the longest segment
   }
-  dim3 grid((p.nq_rows + kTile - 1) / kTile, p.n_blocks, p.n_segs);
-  attention_kernel<<<grid, kAttnThreads, smem, st>>>(tq, tk, tv, p, v_lbo, v_sbo);
+  if (const char* e = getenv("AHA_ATTN_SPLITS")) { const int v = atoi(e); if (v >= 1 && v <= 8) splits = v; }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(q_tiles, p.n_blocks, p.n_segs * splits);
+  cfg.blockDim = dim3(kAttnThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = splits;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;

@@ -57,109 +57,148 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-// Applies bias / activation / residual to 16 consecutive accumulator columns (j = jc .. jc+15) of
-// tile row i and stores them.  `acc` are fp32 sums.
-__device__ __forceinline__ void epilogue_store16(const GemmParams& p, int a0, int b0, int i, int jc, float (&acc)[16]) {
+// Activation on a bf16-rounded pre-activation, result rounded to bf16 again (PyTorch evaluates the op on a bf16 tensor).
+// The transcendental helpers are kept out of line: the epilogue must stay small, an instruction-cache miss costs more
+// than a call (the weight stream evicts the code from L2 between launches).
+__device__ __noinline__ float act_gelu_tanh(float x) { return bf16r(gelu_tanh_f(x)); }
+__device__ __noinline__ float act_gelu_erf(float x) { return bf16r(gelu_erf_f(x)); }
+
+// Applies bias / activation / residual to 16 consecutive accumulator columns (j = jc .. jc+15) of tile row i and
+// stores them.  `acc` are fp32 sums.  One out-of-line copy per kernel instantiation.
+template <bool kSwap>
+__device__ __noinline__ void epilogue_store16(const GemmParams& p, int a0, int b0, int i, int jc, float (&acc)[16]) {
   const int ai = a0 + i;  // global A row
-  if (!p.swap) {
+  const bool round_out = !p.out_f32 || p.round_bf16;
+  if (!kSwap) {
     // token = A row (fixed for this thread); features = B rows jc..jc+15 (contiguous in memory)
     const int token = ai;
-    if (token >= p.Ma) return;
     const int f0 = b0 + jc;
-    if (f0 >= p.Nb) return;
+    if (token >= p.Ma || f0 >= p.Nb) return;
     const int nvalid = min(16, p.Nb - f0);
-    float v[16];
+    if (p.bias) {
+#pragma unroll 4
+      for (int t = 0; t < 16; ++t) acc[t] += (t < nvalid) ? b2f(p.bias[f0 + t]) : 0.f;
+    }
+    if (round_out) {
+#pragma unroll
+      for (int t = 0; t < 16; ++t) acc[t] = bf16r(acc[t]);
+    }
     if (p.act == GEMM_ACT_SILU_MUL) {
       // features interleaved: even = gate f, odd = up f  ->  out[token, f0/2 + t] = bf16(bf16(silu(gate)) * up)
       bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + (f0 >> 1);
-      float w[8];
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        float g = acc[2 * t], u = acc[2 * t + 1];
-        if (p.bias && 2 * t + 1 < nvalid) { g += b2f(p.bias[f0 + 2 * t]); u += b2f(p.bias[f0 + 2 * t + 1]); }
-        g = bf16r(g); u = bf16r(u);
-        w[t] = bf16r(bf16r(silu_f(g)) * u);
-      }
-      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-        st_v4(o, make_uint4(pack_bf16x2(w[0], w[1]), pack_bf16x2(w[2], w[3]), pack_bf16x2(w[4], w[5]), pack_bf16x2(w[6], w[7])));
-      } else {
-#pragma unroll
-        for (int t = 0; t < 8; ++t)
-          if (2 * t + 1 < nvalid) o[t] = f2b(w[t]);
-      }
+#pragma unroll 2
+      for (int t = 0; t < 8; ++t)
+        if (2 * t + 1 < nvalid) o[t] = f2b(bf16r(silu_f(acc[2 * t])) * acc[2 * t + 1]);
       return;
     }
-#pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      float x = acc[t];
-      if (p.bias && t < nvalid) x += b2f(p.bias[f0 + t]);
-      if (!p.out_f32 || p.round_bf16) x = bf16r(x);
-      if (p.act == GEMM_ACT_GELU_TANH) x = bf16r(gelu_tanh_f(x));
-      else if (p.act == GEMM_ACT_GELU_ERF) x = bf16r(gelu_erf_f(x));
-      v[t] = x;
+    if (p.act == GEMM_ACT_GELU_TANH) {
+#pragma unroll 1
+      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_tanh(acc[t]);
+    } else if (p.act == GEMM_ACT_GELU_ERF) {
+#pragma unroll 1
+      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_erf(acc[t]);
     }
+    const bool vec = nvalid == 16;
     if (p.residual) {
       const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
       const bf16* r = p.residual + (size_t)rrow * p.ldr + f0;
+      if (vec && ((reinterpret_cast<uintptr_t>(r) & 15) == 0)) {
+        const uint4 r0 = *reinterpret_cast<const uint4*>(r), r1 = *reinterpret_cast<const uint4*>(r + 8);
+        const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
-      for (int t = 0; t < 16; ++t)
-        if (t < nvalid) v[t] = bf16r(b2f(r[t]) + v[t]);
+        for (int t = 0; t < 8; ++t) {
+          const float2 f = unpack_bf16x2(rw[t]);
+          acc[2 * t] = bf16r(f.x + acc[2 * t]);
+          acc[2 * t + 1] = bf16r(f.y + acc[2 * t + 1]);
+        }
+      } else {
+#pragma unroll 4
+        for (int t = 0; t < 16; ++t)
+          if (t < nvalid) acc[t] = bf16r(b2f(r[t]) + acc[t]);
+      }
     }
     if (p.out_f32) {
       float* o = reinterpret_cast<float*>(p.out) + (size_t)token * p.ldo + f0;
+      if (vec && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
-      for (int t = 0; t < 16; ++t)
-        if (t < nvalid) o[t] = v[t];
+        for (int t = 0; t < 16; t += 4) *reinterpret_cast<float4*>(o + t) = make_float4(acc[t], acc[t + 1], acc[t + 2], acc[t + 3]);
+      } else {
+#pragma unroll 4
+        for (int t = 0; t < 16; ++t)
+          if (t < nvalid) o[t] = acc[t];
+      }
     } else {
       bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + f0;
-      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-        uint4 w0, w1;
-        w0.x = pack_bf16x2(v[0], v[1]);   w0.y = pack_bf16x2(v[2], v[3]);
-        w0.z = pack_bf16x2(v[4], v[5]);   w0.w = pack_bf16x2(v[6], v[7]);
-        w1.x = pack_bf16x2(v[8], v[9]);   w1.y = pack_bf16x2(v[10], v[11]);
-        w1.z = pack_bf16x2(v[12], v[13]); w1.w = pack_bf16x2(v[14], v[15]);
-        st_v4(o, w0);
-        st_v4(o + 8, w1);
+      if (vec && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+        st_v4(o, make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
+                            pack_bf16x2(acc[6], acc[7])));
+        st_v4(o + 8, make_uint4(pack_bf16x2(acc[8], acc[9]), pack_bf16x2(acc[10], acc[11]), pack_bf16x2(acc[12], acc[13]),
+                                pack_bf16x2(acc[14], acc[15])));
       } else {
-#pragma unroll
+#pragma unroll 4
         for (int t = 0; t < 16; ++t)
-          if (t < nvalid) o[t] = f2b(v[t]);
+          if (t < nvalid) o[t] = f2b(acc[t]);
       }
     }
   } else {
-    // feature = A row (fixed for this thread); tokens = B rows jc..jc+15
+    // feature = A row (fixed for this thread); tokens = B rows jc..jc+15.  Lanes hold consecutive features, so every
+    // per-token access of a warp is one contiguous 64-byte (bf16) or 128-byte (fp32) segment.
     const int feat = ai;
     const bool fvalid = feat < p.Ma;
     const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
+    const int tok0 = b0 + jc;
 #pragma unroll
     for (int t = 0; t < 16; ++t) {
-      const int token = b0 + jc + t;
-      float x = acc[t] + bias;
-      if (!p.out_f32 || p.round_bf16) x = bf16r(x);
-      if (p.act == GEMM_ACT_SILU_MUL) {
-        // rows interleaved: even A row = gate feature f, odd A row = up feature f
-        float other = __shfl_down_sync(0xffffffffu, x, 1);
-        float s = bf16r(silu_f(x));
-        x = bf16r(s * other);
-        if ((i & 1) == 0 && fvalid && token < p.Nb) {
-          reinterpret_cast<bf16*>(p.out)[(size_t)token * p.ldo + (feat >> 1)] = f2b(x);
-        }
-        continue;
+      acc[t] += bias;
+      if (round_out) acc[t] = bf16r(acc[t]);
+    }
+    if (p.act == GEMM_ACT_SILU_MUL) {
+      // rows interleaved: even A row = gate feature f, odd A row = up feature f (the neighbouring lane)
+      bf16* o = reinterpret_cast<bf16*>(p.out) + (feat >> 1);
+#pragma unroll 4
+      for (int t = 0; t < 16; ++t) {
+        const float up = __shfl_down_sync(0xffffffffu, acc[t], 1);
+        const float x = bf16r(bf16r(silu_f(acc[t])) * up);
+        if ((i & 1) == 0 && fvalid && tok0 + t < p.Nb) o[(size_t)(tok0 + t) * p.ldo] = f2b(x);
       }
-      if (p.act == GEMM_ACT_GELU_TANH) x = bf16r(gelu_tanh_f(x));
-      else if (p.act == GEMM_ACT_GELU_ERF) x = bf16r(gelu_erf_f(x));
-      if (!fvalid || token >= p.Nb) continue;
-      if (p.residual) {
+      return;
+    }
+    if (p.act == GEMM_ACT_GELU_TANH) {
+#pragma unroll 1
+      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_tanh(acc[t]);
+    } else if (p.act == GEMM_ACT_GELU_ERF) {
+#pragma unroll 1
+      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_erf(acc[t]);
+    }
+    if (!fvalid) return;
+    const int ntok = min(16, p.Nb - tok0);
+    if (p.residual) {
+      // all loads first (they may alias the output rows written below by this same thread only)
+      float r[16];
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const int token = tok0 + t;
         const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
-        x = bf16r(b2f(p.residual[(size_t)rrow * p.ldr + feat]) + x);
+        r[t] = (t < ntok) ? b2f(p.residual[(size_t)rrow * p.ldr + feat]) : 0.f;
       }
-      if (p.out_f32) reinterpret_cast<float*>(p.out)[(size_t)token * p.ldo + feat] = x;
-      else reinterpret_cast<bf16*>(p.out)[(size_t)token * p.ldo + feat] = f2b(x);
+#pragma unroll
+      for (int t = 0; t < 16; ++t) acc[t] = bf16r(r[t] + acc[t]);
+    }
+    if (p.out_f32) {
+      float* o = reinterpret_cast<float*>(p.out) + feat;
+#pragma unroll 4
+      for (int t = 0; t < 16; ++t)
+        if (t < ntok) o[(size_t)(tok0 + t) * p.ldo] = acc[t];
+    } else {
+      bf16* o = reinterpret_cast<bf16*>(p.out) + feat;
+#pragma unroll 4
+      for (int t = 0; t < 16; ++t)
+        if (t < ntok) o[(size_t)(tok0 + t) * p.ldo] = f2b(acc[t]);
     }
   }
 }
 
-template <int BN>
+template <int BN, bool kSwap>
 __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmParams p) {
@@ -205,8 +244,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 0) {
     // ===== TMA producer =====
     if (elect_one()) {
-      const uint64_t pol_a = p.swap ? l2_policy_evict_first() : l2_policy_evict_last();
-      const uint64_t pol_b = p.swap ? l2_policy_evict_last() : l2_policy_evict_first();
+      const uint64_t pol_a = kSwap ? l2_policy_evict_first() : l2_policy_evict_last();
+      const uint64_t pol_b = kSwap ? l2_policy_evict_last() : l2_policy_evict_first();
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % C::kStages;
         const uint32_t ph = (kb / C::kStages) & 1;
@@ -253,7 +292,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         float acc[16];
 #pragma unroll
         for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
-        epilogue_store16(p, a0, b0, i, jc, acc);
+        epilogue_store16<kSwap>(p, a0, b0, i, jc, acc);
       }
     } else {
       // Split-K over a thread-block cluster (cluster dims 1 x 1 x splits): every CTA parks its fp32 partial
@@ -292,7 +331,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
           for (int t = 0; t < 16; ++t) acc[t] += peer[t * kBlockM];
         }
-        epilogue_store16(p, a0, b0, i, jc, acc);
+        epilogue_store16<kSwap>(p, a0, b0, i, jc, acc);
       }
     }
     __syncwarp();
@@ -394,12 +433,12 @@ void prof_end(ProfSlot* s, cudaStream_t st, double bytes, double flops) {
   cudaEventRecord(s->e1, st);
 }
 
-template <int BN>
+template <int BN, bool kSwap>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_done = false;
   if (!attr_done) {
-    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
@@ -408,7 +447,7 @@ int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN>, ta, tb, p));
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, kSwap>, ta, tb, p));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;
@@ -471,10 +510,10 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   dim3 grid(tiles_a, tiles_b, splits);
   ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);
   switch (bn) {
-    case 32: rc = launch_bn<32>(ta, tb, p, grid, stream); break;
-    case 64: rc = launch_bn<64>(ta, tb, p, grid, stream); break;
-    case 128: rc = launch_bn<128>(ta, tb, p, grid, stream); break;
-    default: rc = launch_bn<256>(ta, tb, p, grid, stream); break;
+    case 32: rc = swap ? launch_bn<32, true>(ta, tb, p, grid, stream) : launch_bn<32, false>(ta, tb, p, grid, stream); break;
+    case 64: rc = swap ? launch_bn<64, true>(ta, tb, p, grid, stream) : launch_bn<64, false>(ta, tb, p, grid, stream); break;
+    case 128: rc = swap ? launch_bn<128, true>(ta, tb, p, grid, stream) : launch_bn<128, false>(ta, tb, p, grid, stream); break;
+    default: rc = swap ? launch_bn<256, true>(ta, tb, p, grid, stream) : launch_bn<256, false>(ta, tb, p, grid, stream); break;
   }
   if (slot) {
     const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * (c.out_f32 ? 4 : 2);

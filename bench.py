@@ -394,6 +394,16 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: aha_b200 has no CPU path (use --impl reference for the CPU arm)")
     peaks = measured_peaks()
     r = run_ours(args)
+    if os.environ.get("AHA_NCU"):
+        # profiling aid (never a bench value): one vision batch + 32 steady-state frames inside a cudaProfiler range,
+        # for `ncu --profile-from-start off`
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        for _ in range(int(os.environ.get("AHA_NCU_STEPS", "32"))):
+            r["step"]()
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     roof = roofline_leg(r, args, peaks)
     e2e = e2e_leg(r, args)
     line = None
