@@ -21,6 +21,7 @@ struct GemmParams {
   const __nv_bfloat16* residual;  // residual[(token % res_mod) * ldr + feature] or null
   int ldr;
   int res_mod;          // 0 = no modulo
+  int dbg;              // bring-up knob (AHA_GEMM_DBG): 1 = return at entry, 2 = skip epilogue math/stores
 };
 
 // Description of one GEMM call as the model layers see it:  out[tokens, features] = X[tokens, K] . W[features, K]^T

@@ -32,6 +32,7 @@
 
 #include <cuda.h>
 #include <cooperative_groups.h>
+#include <cstdlib>
 #include <deque>
 #include <map>
 #include <mutex>
@@ -57,148 +58,237 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-// Activation on a bf16-rounded pre-activation, result rounded to bf16 again (PyTorch evaluates the op on a bf16 tensor).
-// The transcendental helpers are kept out of line: the epilogue must stay small, an instruction-cache miss costs more
-// than a call (the weight stream evicts the code from L2 between launches).
-__device__ __noinline__ float act_gelu_tanh(float x) { return bf16r(gelu_tanh_f(x)); }
-__device__ __noinline__ float act_gelu_erf(float x) { return bf16r(gelu_erf_f(x)); }
+// ---- epilogue math: fast approximations whose error is far below one bf16 step of the result ----
+__device__ __forceinline__ float fast_silu(float x) { return x * __frcp_rn(1.f + __expf(-x)); }
+__device__ __forceinline__ float fast_gelu_tanh(float x) {
+  const float u = 0.79788456080286535588f * (x + 0.044715f * x * x * x);
+  const float t = 1.f - 2.f * __frcp_rn(1.f + __expf(2.f * u));   // tanh(u)
+  return 0.5f * x * (1.f + t);
+}
+__device__ __forceinline__ float fast_gelu_erf(float x) {
+  // erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7)
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __frcp_rn(1.f + 0.3275911f * z);
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float e = 1.f - poly * __expf(-z * z);
+  return 0.5f * x * (1.f + copysignf(e, x));
+}
+template <int kAct>
+__device__ __forceinline__ float apply_act(float x) {   // x is already bf16-rounded; result is rounded by the caller
+  if (kAct == GEMM_ACT_GELU_TANH) return fast_gelu_tanh(x);
+  if (kAct == GEMM_ACT_GELU_ERF) return fast_gelu_erf(x);
+  return x;
+}
 
-// Applies bias / activation / residual to 16 consecutive accumulator columns (j = jc .. jc+15) of tile row i and
-// stores them.  `acc` are fp32 sums.  One out-of-line copy per kernel instantiation.
-template <bool kSwap>
-__device__ __noinline__ void epilogue_store16(const GemmParams& p, int a0, int b0, int i, int jc, float (&acc)[16]) {
-  const int ai = a0 + i;  // global A row
+// Skinny orientation, 16 tokens of one feature row (thread = feature).  Lanes hold consecutive features, so every
+// per-token access of a warp is one contiguous 64-byte (bf16) or 128-byte (fp32) segment.
+template <int kAct>
+__device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool fvalid, float bias, int i, int tok0,
+                                           float (&acc)[16]) {
   const bool round_out = !p.out_f32 || p.round_bf16;
-  if (!kSwap) {
-    // token = A row (fixed for this thread); features = B rows jc..jc+15 (contiguous in memory)
-    const int token = ai;
-    const int f0 = b0 + jc;
-    if (token >= p.Ma || f0 >= p.Nb) return;
-    const int nvalid = min(16, p.Nb - f0);
-    if (p.bias) {
-#pragma unroll 4
-      for (int t = 0; t < 16; ++t) acc[t] += (t < nvalid) ? b2f(p.bias[f0 + t]) : 0.f;
-    }
-    if (round_out) {
 #pragma unroll
-      for (int t = 0; t < 16; ++t) acc[t] = bf16r(acc[t]);
-    }
-    if (p.act == GEMM_ACT_SILU_MUL) {
-      // features interleaved: even = gate f, odd = up f  ->  out[token, f0/2 + t] = bf16(bf16(silu(gate)) * up)
-      bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + (f0 >> 1);
-#pragma unroll 2
-      for (int t = 0; t < 8; ++t)
-        if (2 * t + 1 < nvalid) o[t] = f2b(bf16r(silu_f(acc[2 * t])) * acc[2 * t + 1]);
-      return;
-    }
-    if (p.act == GEMM_ACT_GELU_TANH) {
-#pragma unroll 1
-      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_tanh(acc[t]);
-    } else if (p.act == GEMM_ACT_GELU_ERF) {
-#pragma unroll 1
-      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_erf(acc[t]);
-    }
-    const bool vec = nvalid == 16;
-    if (p.residual) {
-      const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
-      const bf16* r = p.residual + (size_t)rrow * p.ldr + f0;
-      if (vec && ((reinterpret_cast<uintptr_t>(r) & 15) == 0)) {
-        const uint4 r0 = *reinterpret_cast<const uint4*>(r), r1 = *reinterpret_cast<const uint4*>(r + 8);
-        const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-#pragma unroll
-        for (int t = 0; t < 8; ++t) {
-          const float2 f = unpack_bf16x2(rw[t]);
-          acc[2 * t] = bf16r(f.x + acc[2 * t]);
-          acc[2 * t + 1] = bf16r(f.y + acc[2 * t + 1]);
-        }
-      } else {
-#pragma unroll 4
-        for (int t = 0; t < 16; ++t)
-          if (t < nvalid) acc[t] = bf16r(b2f(r[t]) + acc[t]);
-      }
-    }
-    if (p.out_f32) {
-      float* o = reinterpret_cast<float*>(p.out) + (size_t)token * p.ldo + f0;
-      if (vec && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-        for (int t = 0; t < 16; t += 4) *reinterpret_cast<float4*>(o + t) = make_float4(acc[t], acc[t + 1], acc[t + 2], acc[t + 3]);
-      } else {
-#pragma unroll 4
-        for (int t = 0; t < 16; ++t)
-          if (t < nvalid) o[t] = acc[t];
-      }
-    } else {
-      bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + f0;
-      if (vec && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-        st_v4(o, make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
-                            pack_bf16x2(acc[6], acc[7])));
-        st_v4(o + 8, make_uint4(pack_bf16x2(acc[8], acc[9]), pack_bf16x2(acc[10], acc[11]), pack_bf16x2(acc[12], acc[13]),
-                                pack_bf16x2(acc[14], acc[15])));
-      } else {
-#pragma unroll 4
-        for (int t = 0; t < 16; ++t)
-          if (t < nvalid) o[t] = f2b(acc[t]);
-      }
-    }
-  } else {
-    // feature = A row (fixed for this thread); tokens = B rows jc..jc+15.  Lanes hold consecutive features, so every
-    // per-token access of a warp is one contiguous 64-byte (bf16) or 128-byte (fp32) segment.
-    const int feat = ai;
-    const bool fvalid = feat < p.Ma;
-    const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
-    const int tok0 = b0 + jc;
+  for (int t = 0; t < 16; ++t) {
+    acc[t] += bias;
+    if (round_out) acc[t] = bf16r(acc[t]);
+  }
+  const int ntok = min(16, p.Nb - tok0);
+  if (kAct == GEMM_ACT_SILU_MUL) {
+    // rows interleaved: even A row = gate feature f, odd A row = up feature f (the neighbouring lane)
+    bf16* o = reinterpret_cast<bf16*>(p.out) + (feat >> 1) + (size_t)tok0 * p.ldo;
+    const bool writer = (i & 1) == 0 && fvalid;
 #pragma unroll
     for (int t = 0; t < 16; ++t) {
-      acc[t] += bias;
-      if (round_out) acc[t] = bf16r(acc[t]);
+      const float up = __shfl_down_sync(0xffffffffu, acc[t], 1);
+      const float x = bf16r(fast_silu(acc[t])) * up;
+      if (writer && t < ntok) o[(size_t)t * p.ldo] = f2b(x);
     }
-    if (p.act == GEMM_ACT_SILU_MUL) {
-      // rows interleaved: even A row = gate feature f, odd A row = up feature f (the neighbouring lane)
-      bf16* o = reinterpret_cast<bf16*>(p.out) + (feat >> 1);
-#pragma unroll 4
-      for (int t = 0; t < 16; ++t) {
-        const float up = __shfl_down_sync(0xffffffffu, acc[t], 1);
-        const float x = bf16r(bf16r(silu_f(acc[t])) * up);
-        if ((i & 1) == 0 && fvalid && tok0 + t < p.Nb) o[(size_t)(tok0 + t) * p.ldo] = f2b(x);
-      }
-      return;
-    }
-    if (p.act == GEMM_ACT_GELU_TANH) {
-#pragma unroll 1
-      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_tanh(acc[t]);
-    } else if (p.act == GEMM_ACT_GELU_ERF) {
-#pragma unroll 1
-      for (int t = 0; t < 16; ++t) acc[t] = act_gelu_erf(acc[t]);
-    }
-    if (!fvalid) return;
-    const int ntok = min(16, p.Nb - tok0);
-    if (p.residual) {
-      // all loads first (they may alias the output rows written below by this same thread only)
-      float r[16];
+    return;
+  }
+  if (kAct != GEMM_ACT_NONE) {
 #pragma unroll
-      for (int t = 0; t < 16; ++t) {
-        const int token = tok0 + t;
-        const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
-        r[t] = (t < ntok) ? b2f(p.residual[(size_t)rrow * p.ldr + feat]) : 0.f;
-      }
+    for (int t = 0; t < 16; ++t) acc[t] = bf16r(apply_act<kAct>(acc[t]));
+  }
+  if (!fvalid) return;
+  if (p.residual) {
+    // all loads first (they may alias the output elements written below, by this same thread only)
+    float r[16];
 #pragma unroll
-      for (int t = 0; t < 16; ++t) acc[t] = bf16r(r[t] + acc[t]);
+    for (int t = 0; t < 16; ++t) {
+      const int token = tok0 + t;
+      const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
+      r[t] = (t < ntok) ? b2f(p.residual[(size_t)rrow * p.ldr + feat]) : 0.f;
     }
-    if (p.out_f32) {
-      float* o = reinterpret_cast<float*>(p.out) + feat;
-#pragma unroll 4
-      for (int t = 0; t < 16; ++t)
-        if (t < ntok) o[(size_t)(tok0 + t) * p.ldo] = acc[t];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) acc[t] = bf16r(r[t] + acc[t]);
+  }
+  if (p.out_f32) {
+    float* o = reinterpret_cast<float*>(p.out) + feat + (size_t)tok0 * p.ldo;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < ntok) o[(size_t)t * p.ldo] = acc[t];
+  } else {
+    bf16* o = reinterpret_cast<bf16*>(p.out) + feat + (size_t)tok0 * p.ldo;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < ntok) o[(size_t)t * p.ldo] = f2b(acc[t]);
+  }
+}
+
+// Tall orientation, direct form: 16 consecutive features of one token row (thread = token).  Used by the split-K merge
+// and for fp32 outputs; the unsplit bf16 path goes through the shared-memory staged form below.
+template <int kAct>
+__device__ __forceinline__ void epi_tall16(const GemmParams& p, int token, int f0, float (&acc)[16]) {
+  if (token >= p.Ma || f0 >= p.Nb) return;
+  const int nvalid = min(16, p.Nb - f0);
+  const bool round_out = !p.out_f32 || p.round_bf16;
+  if (p.bias) {
+#pragma unroll
+    for (int t = 0; t < 16; ++t) acc[t] += (t < nvalid) ? b2f(p.bias[f0 + t]) : 0.f;
+  }
+  if (round_out) {
+#pragma unroll
+    for (int t = 0; t < 16; ++t) acc[t] = bf16r(acc[t]);
+  }
+  if (kAct == GEMM_ACT_SILU_MUL) {
+    bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + (f0 >> 1);
+#pragma unroll
+    for (int t = 0; t < 8; ++t)
+      if (2 * t + 1 < nvalid) o[t] = f2b(bf16r(fast_silu(acc[2 * t])) * acc[2 * t + 1]);
+    return;
+  }
+  if (kAct != GEMM_ACT_NONE) {
+#pragma unroll
+    for (int t = 0; t < 16; ++t) acc[t] = bf16r(apply_act<kAct>(acc[t]));
+  }
+  if (p.residual) {
+    const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
+    const bf16* r = p.residual + (size_t)rrow * p.ldr + f0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < nvalid) acc[t] = bf16r(b2f(r[t]) + acc[t]);
+  }
+  if (p.out_f32) {
+    float* o = reinterpret_cast<float*>(p.out) + (size_t)token * p.ldo + f0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < nvalid) o[t] = acc[t];
+  } else {
+    bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + f0;
+    if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      st_v4(o, make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
+                          pack_bf16x2(acc[6], acc[7])));
+      st_v4(o + 8, make_uint4(pack_bf16x2(acc[8], acc[9]), pack_bf16x2(acc[10], acc[11]), pack_bf16x2(acc[12], acc[13]),
+                              pack_bf16x2(acc[14], acc[15])));
     } else {
-      bf16* o = reinterpret_cast<bf16*>(p.out) + feat;
-#pragma unroll 4
+#pragma unroll
       for (int t = 0; t < 16; ++t)
-        if (t < ntok) o[(size_t)(tok0 + t) * p.ldo] = f2b(acc[t]);
+        if (t < nvalid) o[t] = f2b(acc[t]);
     }
   }
 }
 
-template <int BN, bool kSwap>
+// Tall orientation, staged form.  Phase 1 (thread = token row): TMEM -> bias / activation -> bf16 -> this warp's
+// [32 rows][BN] staging tile in shared memory (row pitch BN*2 + 16 bytes: conflict-free 16-byte accesses).
+// Phase 2 (warp-cooperative): 16-byte pieces leave in row order, so a warp instruction covers whole 256-byte row
+// segments of the output (and of the residual it adds): fully coalesced HBM traffic.
+template <int BN, int kAct>
+__device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t taddr, uint8_t* stage_warp, int a0, int b0,
+                                                int ew, int lane) {
+  constexpr int kPitch = BN * 2 + 16;
+  constexpr int kOutCols = (kAct == GEMM_ACT_SILU_MUL) ? BN / 2 : BN;    // SiLU*mul halves the feature count
+  uint8_t* my = stage_warp + lane * kPitch;
+#pragma unroll 1
+  for (int jc = 0; jc < BN; jc += 32) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(taddr + jc, r);
+    tmem_ld_wait();
+    float v[32];
+#pragma unroll
+    for (int t = 0; t < 32; ++t) v[t] = __uint_as_float(r[t]);
+    if (p.bias) {
+      const int f0 = b0 + jc;
+      if (f0 + 32 <= p.Nb) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint4 bu = *reinterpret_cast<const uint4*>(p.bias + f0 + c * 8);   // same address in every lane: one broadcast
+          const uint32_t bw[4] = {bu.x, bu.y, bu.z, bu.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack_bf16x2(bw[e]);
+            v[c * 8 + 2 * e] += f.x; v[c * 8 + 2 * e + 1] += f.y;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < 32; ++t) v[t] += (f0 + t < p.Nb) ? b2f(p.bias[f0 + t]) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 32; ++t) v[t] = bf16r(v[t]);
+    if (kAct == GEMM_ACT_SILU_MUL) {
+      uint32_t pk[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        pk[t] = pack_bf16x2(bf16r(fast_silu(v[4 * t])) * v[4 * t + 1], bf16r(fast_silu(v[4 * t + 2])) * v[4 * t + 3]);
+      *reinterpret_cast<uint4*>(my + jc) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      *reinterpret_cast<uint4*>(my + jc + 16) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    } else {
+      uint32_t pk[16];
+#pragma unroll
+      for (int t = 0; t < 16; ++t) pk[t] = pack_bf16x2(apply_act<kAct>(v[2 * t]), apply_act<kAct>(v[2 * t + 1]));
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        *reinterpret_cast<uint4*>(my + jc * 2 + c * 16) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+    }
+  }
+  __syncwarp();
+  constexpr int kChunksPerRow = kOutCols / 8;
+  const int ob0 = (kAct == GEMM_ACT_SILU_MUL) ? (b0 >> 1) : b0;
+  const int n_out = (kAct == GEMM_ACT_SILU_MUL) ? (p.Nb >> 1) : p.Nb;
+  bf16* out = reinterpret_cast<bf16*>(p.out);
+#pragma unroll 4
+  for (int idx = lane; idx < 32 * kChunksPerRow; idx += 32) {
+    const int rrow_in_warp = idx / kChunksPerRow, ch = idx % kChunksPerRow;
+    const int token = a0 + ew * 32 + rrow_in_warp;
+    const int f = ob0 + ch * 8;
+    if (token >= p.Ma || f >= n_out) continue;
+    uint4 u = *reinterpret_cast<const uint4*>(stage_warp + rrow_in_warp * kPitch + ch * 16);
+    bf16* o = out + (size_t)token * p.ldo + f;
+    const bool full = (f + 8 <= n_out) && ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
+    if (p.residual) {
+      const int rr = p.res_mod > 0 ? (token % p.res_mod) : token;
+      const bf16* rp = p.residual + (size_t)rr * p.ldr + f;
+      uint32_t w[4] = {u.x, u.y, u.z, u.w};
+      if (full && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
+        const uint4 ru = *reinterpret_cast<const uint4*>(rp);
+        const uint32_t rw[4] = {ru.x, ru.y, ru.z, ru.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 a = unpack_bf16x2(w[e]), b = unpack_bf16x2(rw[e]);
+          w[e] = pack_bf16x2(b.x + a.x, b.y + a.y);
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 a = unpack_bf16x2(w[e]);
+          const float r0 = (f + 2 * e < n_out) ? b2f(rp[2 * e]) : 0.f, r1 = (f + 2 * e + 1 < n_out) ? b2f(rp[2 * e + 1]) : 0.f;
+          w[e] = pack_bf16x2(r0 + a.x, r1 + a.y);
+        }
+      }
+      u = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    if (full) {
+      st_v4(o, u);
+    } else {
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (f + e < n_out) reinterpret_cast<uint16_t*>(o)[e] = (uint16_t)(w[e >> 1] >> ((e & 1) * 16));
+    }
+  }
+}
+
+template <int BN, bool kSwap, int kAct>
 __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmParams p) {
@@ -222,6 +312,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int kb_begin = split * p.kb_per_split;
   const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
   const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
+  if (p.dbg == 1) return;
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmap_a);
@@ -283,16 +374,37 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     mbar_wait(accum_bar, 0);
     tc_fence_after();
     const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
-    if (p.splits == 1) {
+    if (p.dbg == 2) {
+    } else if (p.splits == 1) {
+      if (kSwap) {
+        const int feat = a0 + i;
+        const bool fvalid = feat < p.Ma;
+        const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
 #pragma unroll 1
-      for (int jc = 0; jc < BN; jc += 16) {
-        uint32_t r[16];
-        tmem_ld_32x32b_x16(taddr + jc, r);
-        tmem_ld_wait();
-        float acc[16];
+        for (int jc = 0; jc < BN; jc += 16) {
+          if (b0 + jc >= p.Nb) break;
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(taddr + jc, r);
+          tmem_ld_wait();
+          float acc[16];
 #pragma unroll
-        for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
-        epilogue_store16<kSwap>(p, a0, b0, i, jc, acc);
+          for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
+          epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+        }
+      } else if (p.out_f32) {
+#pragma unroll 1
+        for (int jc = 0; jc < BN; jc += 16) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(taddr + jc, r);
+          tmem_ld_wait();
+          float acc[16];
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
+          epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
+        }
+      } else {
+        // the operand ring is idle by now (accum_bar fired after the last MMA read it): reuse it as the staging tile
+        epi_tall_staged<BN, kAct>(p, taddr, smem + ew * 32 * (BN * 2 + 16), a0, b0, ew, lane);
       }
     } else {
       // Split-K over a thread-block cluster (cluster dims 1 x 1 x splits): every CTA parks its fp32 partial
@@ -331,7 +443,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
           for (int t = 0; t < 16; ++t) acc[t] += peer[t * kBlockM];
         }
-        epilogue_store16<kSwap>(p, a0, b0, i, jc, acc);
+        if (kSwap) {
+          const int feat = a0 + i;
+          const bool fvalid = feat < p.Ma;
+          epi_swap16<kAct>(p, feat, fvalid, (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f, i, b0 + jc, acc);
+        } else {
+          epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
+        }
       }
     }
     __syncwarp();
@@ -433,12 +551,12 @@ void prof_end(ProfSlot* s, cudaStream_t st, double bytes, double flops) {
   cudaEventRecord(s->e1, st);
 }
 
-template <int BN, bool kSwap>
+template <int BN, bool kSwap, int kAct>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_done = false;
   if (!attr_done) {
-    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
@@ -447,12 +565,44 @@ int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, kSwap>, ta, tb, p));
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, kSwap, kAct>, ta, tb, p));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;
 }
 
+}  // namespace
+
+namespace {
+template <int BN, bool kSwap>
+int dispatch_act(int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t st) {
+  if (kSwap) {   // skinny orientation: plain or SiLU*mul (GELU callers are routed to the tall orientation)
+    if (act == GEMM_ACT_SILU_MUL) return launch_bn<BN, kSwap, GEMM_ACT_SILU_MUL>(ta, tb, p, grid, st);
+    return launch_bn<BN, kSwap, GEMM_ACT_NONE>(ta, tb, p, grid, st);
+  }
+  switch (act) {
+    case GEMM_ACT_GELU_TANH: return launch_bn<BN, false, GEMM_ACT_GELU_TANH>(ta, tb, p, grid, st);
+    case GEMM_ACT_GELU_ERF: return launch_bn<BN, false, GEMM_ACT_GELU_ERF>(ta, tb, p, grid, st);
+    case GEMM_ACT_SILU_MUL: return launch_bn<BN, false, GEMM_ACT_SILU_MUL>(ta, tb, p, grid, st);
+    default: return launch_bn<BN, false, GEMM_ACT_NONE>(ta, tb, p, grid, st);
+  }
+}
+int dispatch(int bn, int swap, int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid,
+             cudaStream_t st) {
+  if (swap) {
+    switch (bn) {
+      case 32: return dispatch_act<32, true>(act, ta, tb, p, grid, st);
+      case 64: return dispatch_act<64, true>(act, ta, tb, p, grid, st);
+      case 128: return dispatch_act<128, true>(act, ta, tb, p, grid, st);
+      default: return dispatch_act<256, true>(act, ta, tb, p, grid, st);
+    }
+  }
+  switch (bn) {
+    case 64: return dispatch_act<64, false>(act, ta, tb, p, grid, st);
+    case 128: return dispatch_act<128, false>(act, ta, tb, p, grid, st);
+    default: return dispatch_act<256, false>(act, ta, tb, p, grid, st);
+  }
+}
 }  // namespace
 
 int gemm_workspace_create(GemmWorkspace* w, int device) {
@@ -467,6 +617,7 @@ void gemm_workspace_destroy(GemmWorkspace*) {}
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
   int swap = c.force_swap >= 0 ? c.force_swap : (c.tokens <= 256 ? 1 : 0);
+  if (c.act == GEMM_ACT_GELU_TANH || c.act == GEMM_ACT_GELU_ERF) swap = 0;   // GELU epilogues exist in the tall orientation only
   if (c.act == GEMM_ACT_SILU_MUL) {
     AHA_REQUIRE(!c.out_f32 && !c.residual, "SiLU*mul epilogue writes bf16 without residual");
   }
@@ -481,9 +632,10 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   int bn = c.force_bn;
   if (bn == 0) {
     if (swap) bn = p.Nb <= 32 ? 32 : p.Nb <= 64 ? 64 : p.Nb <= 128 ? 128 : 256;
-    else bn = p.Nb <= 32 ? 32 : p.Nb <= 64 ? 64 : 128;
+    else bn = p.Nb <= 64 ? 64 : 128;
   }
   AHA_REQUIRE(bn == 32 || bn == 64 || bn == 128 || bn == 256, "unsupported GEMM BN tile");
+  if (!swap && bn == 32) bn = 64;
   const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM;
   const int tiles_b = (p.Nb + bn - 1) / bn;
   const int tiles = tiles_a * tiles_b;
@@ -503,18 +655,14 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   int kb_per = (kb_total + splits - 1) / splits;
   splits = (kb_total + kb_per - 1) / kb_per;  // no empty splits
   p.splits = splits; p.kb_per_split = kb_per;
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("AHA_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   AHA_REQUIRE(splits <= 8, "split-K factor above the portable cluster size (8)");
   CUtensorMap ta, tb;
   int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
   dim3 grid(tiles_a, tiles_b, splits);
   ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);
-  switch (bn) {
-    case 32: rc = swap ? launch_bn<32, true>(ta, tb, p, grid, stream) : launch_bn<32, false>(ta, tb, p, grid, stream); break;
-    case 64: rc = swap ? launch_bn<64, true>(ta, tb, p, grid, stream) : launch_bn<64, false>(ta, tb, p, grid, stream); break;
-    case 128: rc = swap ? launch_bn<128, true>(ta, tb, p, grid, stream) : launch_bn<128, false>(ta, tb, p, grid, stream); break;
-    default: rc = swap ? launch_bn<256, true>(ta, tb, p, grid, stream) : launch_bn<256, false>(ta, tb, p, grid, stream); break;
-  }
+  rc = dispatch(bn, swap, c.act, ta, tb, p, grid, stream);
   if (slot) {
     const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * (c.out_f32 ? 4 : 2);
     prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,
