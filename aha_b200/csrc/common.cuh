@@ -35,6 +35,30 @@ int aha_cuda_fail(cudaError_t e, const char* what, const char* file, int line);
     }                                                  \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ----
+// Every hot-path kernel is launched with cudaLaunchAttributeProgrammaticStreamSerialization: its prologue (barrier
+// init, TMEM allocation, weight prefetch) may start while the previous kernel on the stream is still running; it calls
+// pdl_wait() before touching anything an earlier kernel produced (and before its first global write), and
+// pdl_launch_dependents() as early as possible so that its own successor can do the same.  AHA_PDL=0 disables it.
+bool aha_pdl_enabled();
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline int launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+  ++g_aha_launch_count;
+  return AHA_OK;
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
 #ifdef __CUDACC__
 
 __device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }

@@ -16,6 +16,8 @@ template <bool kLayerNorm>
 __global__ void __launch_bounds__(kNormThreads) norm_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
                                                             const bf16* __restrict__ b, bf16* __restrict__ out,
                                                             int cols, float eps) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ float red[32];
   const int row = blockIdx.x;
   const int nvec = cols >> 3;
@@ -117,6 +119,8 @@ __global__ void preprocess_kernel(const uint8_t* __restrict__ in, bf16* __restri
 template <bool kU8>
 __global__ void patchify_kernel(const uint8_t* __restrict__ fu8, const bf16* __restrict__ fpx, bf16* __restrict__ out,
                                 int n, int image, int patch, int kpad) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ bf16 lut[256];
   if (kU8) {
     if (threadIdx.x < 256) lut[threadIdx.x] = f2b(preprocess_value(threadIdx.x));
@@ -155,6 +159,8 @@ __global__ void patchify_kernel(const uint8_t* __restrict__ fu8, const bf16* __r
 // One thread per (frame, output token, 8 channels): 4..25 x 16-byte loads, one 16-byte store.
 __global__ void pool_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, int frames, int side, int channels,
                             int stride, int mode, int os) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int cvec = channels >> 3;
   const long long total = (long long)frames * os * os * cvec;
   const float scale = (float)side / (float)os;
@@ -218,6 +224,8 @@ __global__ void pool_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, 
 // cos/sin in fp32, cast to bf16.  inv_freq is computed on the host exactly as torch does (model.cu).
 __global__ void rope_table_kernel(RopeTableArgs a, int q, int d, const float* __restrict__ inv_freq,
                                   bf16* __restrict__ cos_out, bf16* __restrict__ sin_out) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int s = blockIdx.y;
   const int half = d >> 1;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < q * half; idx += gridDim.x * blockDim.x) {
@@ -234,6 +242,8 @@ __global__ void rope_table_kernel(RopeTableArgs a, int q, int d, const float* __
 __global__ void embed_assemble_kernel(const bf16* __restrict__ table, const int64_t* __restrict__ ids, int n_ids,
                                       const bf16* __restrict__ frame_embeds, bf16* __restrict__ out, int hidden,
                                       int vocab) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int row = blockIdx.x;
   const bf16* src;
   if (row < n_ids) {
@@ -256,6 +266,8 @@ __global__ void __launch_bounds__(128) heads_kernel(const bf16* __restrict__ h, 
                                                     int hidden, int q, float* __restrict__ informative,
                                                     float* __restrict__ relevance, float* __restrict__ uncertainty,
                                                     float* __restrict__ scores3) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ float red[4][4];
   const int row = blockIdx.x;
   const uint4* hr = reinterpret_cast<const uint4*>(h + (size_t)row * hidden);
@@ -320,18 +332,12 @@ inline int grid_for(long long work_items, int threads, int cap = 148 * 16) {
 
 int op_rmsnorm(const bf16* x, const bf16* w, bf16* out, int rows, int cols, float eps, cudaStream_t st) {
   AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= kNormThreads * kNormMaxVec * 8, "rmsnorm: bad shape");
-  norm_kernel<false><<<rows, kNormThreads, 0, st>>>(x, w, nullptr, out, cols, eps);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(norm_kernel<false>, dim3(rows), dim3(kNormThreads), 0, st, x, w, (const bf16*)nullptr, out, cols, eps);
 }
 
 int op_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* out, int rows, int cols, float eps, cudaStream_t st) {
   AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= kNormThreads * kNormMaxVec * 8, "layernorm: bad shape");
-  norm_kernel<true><<<rows, kNormThreads, 0, st>>>(x, w, b, out, cols, eps);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(norm_kernel<true>, dim3(rows), dim3(kNormThreads), 0, st, x, w, b, out, cols, eps);
 }
 
 int op_preprocess(const uint8_t* in, bf16* out, long long n, cudaStream_t st) {
@@ -351,11 +357,8 @@ int op_patchify(const uint8_t* frames_u8, const bf16* pixels, bf16* out, int n, 
   AHA_REQUIRE(n > 0 && image >= patch && kpad >= 3 * patch * patch, "patchify: bad geometry");
   const int side = image / patch;
   const long long total = (long long)n * side * side * (3 * patch + 1);
-  if (frames_u8) patchify_kernel<true><<<grid_for(total, 256, 148 * 32), 256, 0, st>>>(frames_u8, nullptr, out, n, image, patch, kpad);
-  else patchify_kernel<false><<<grid_for(total, 256, 148 * 32), 256, 0, st>>>(nullptr, pixels, out, n, image, patch, kpad);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  if (frames_u8) return launch_pdl(patchify_kernel<true>, dim3(grid_for(total, 256, 148 * 32)), dim3(256), 0, st, frames_u8, (const bf16*)nullptr, out, n, image, patch, kpad);
+  return launch_pdl(patchify_kernel<false>, dim3(grid_for(total, 256, 148 * 32)), dim3(256), 0, st, (const uint8_t*)nullptr, pixels, out, n, image, patch, kpad);
 }
 
 int pool_out_side(int side, int stride, int mode) {
@@ -370,39 +373,27 @@ int op_pool(const bf16* x, bf16* out, int frames, int side, int channels, int st
   const int os = pool_out_side(side, stride, mode);
   AHA_REQUIRE(os > 0, "pool: empty output");
   const long long total = (long long)frames * os * os * (channels / 8);
-  pool_kernel<<<grid_for(total, 256), 256, 0, st>>>(x, out, frames, side, channels, stride, mode, os);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(pool_kernel, dim3(grid_for(total, 256)), dim3(256), 0, st, x, out, frames, side, channels, stride, mode, os);
 }
 
 int op_rope_table(const RopeTableArgs& a, int n_streams, int q, int d, const float* inv_freq_dev, bf16* cos_out,
                   bf16* sin_out, cudaStream_t st) {
   AHA_REQUIRE(n_streams > 0 && n_streams <= 16 && q > 0 && d % 2 == 0, "rope_table: bad shape");
   dim3 grid((q * (d / 2) + 127) / 128, n_streams);
-  rope_table_kernel<<<grid, 128, 0, st>>>(a, q, d, inv_freq_dev, cos_out, sin_out);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(rope_table_kernel, grid, dim3(128), 0, st, a, q, d, inv_freq_dev, cos_out, sin_out);
 }
 
 int op_embed_assemble(const bf16* table, const int64_t* ids, int n_ids, const bf16* frame_embeds, int n_frame_tokens,
                       bf16* out, int hidden, int vocab, cudaStream_t st) {
   AHA_REQUIRE(n_ids >= 0 && n_frame_tokens >= 0 && hidden % 8 == 0, "assemble: bad shape");
   if (n_ids + n_frame_tokens == 0) return AHA_OK;
-  embed_assemble_kernel<<<n_ids + n_frame_tokens, 128, 0, st>>>(table, ids, n_ids, frame_embeds, out, hidden, vocab);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(embed_assemble_kernel, dim3(n_ids + n_frame_tokens), dim3(128), 0, st, table, ids, n_ids, frame_embeds, out, hidden, vocab);
 }
 
 int op_heads(const bf16* h, const bf16* w_inf, const bf16* w_rel, const bf16* w_unc, int rows, int hidden, int q,
              float* informative, float* relevance, float* uncertainty, float* scores3, cudaStream_t st) {
   AHA_REQUIRE(rows > 0 && hidden % 8 == 0 && q > 0, "heads: bad shape");
-  heads_kernel<<<rows, 128, 0, st>>>(h, w_inf, w_rel, w_unc, hidden, q, informative, relevance, uncertainty, scores3);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(heads_kernel, dim3(rows), dim3(128), 0, st, h, w_inf, w_rel, w_unc, hidden, q, informative, relevance, uncertainty, scores3);
 }
 
 int op_copy_rows(const bf16* src, int src_ld, bf16* dst, int dst_ld, int rows, int cols, int dst_row0, int dst_row_step,

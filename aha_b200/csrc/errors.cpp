@@ -12,3 +12,10 @@ int aha_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
           std::to_string(line) + " in " + what;
   return AHA_ERR_RUNTIME;
 }
+
+#include <cstdlib>
+bool aha_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("AHA_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}

@@ -314,30 +314,44 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
   if (p.dbg == 1) return;
 
+  // The weight operand (A when skinny, B when tall) does not depend on any earlier kernel: its first ring of tiles is
+  // requested before griddepcontrol.wait, i.e. while the previous kernel on the stream may still be running (PDL).
+  const int pre = min(C::kStages, num_kb);
+  const uint64_t pol_a = kSwap ? l2_policy_evict_first() : l2_policy_evict_last();
+  const uint64_t pol_b = kSwap ? l2_policy_evict_last() : l2_policy_evict_first();
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmap_a);
     prefetch_tensormap(&tmap_b);
-  }
-  if (warp == 1 && lane == 0) {
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
     fence_barrier_init();
+    for (int kb = 0; kb < pre; ++kb) {
+      mbar_arrive_expect_tx(&full_bar[kb], C::kStageBytes);
+      const int kc = (kb_begin + kb) * kBlockK;
+      if (kSwap) tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], kc, a0, pol_a);
+      else tma_load_2d_hint(smem_b + kb * C::kBBytes, &tmap_b, &full_bar[kb], kc, b0, pol_b);
+    }
   }
   if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (elect_one()) {
-      const uint64_t pol_a = kSwap ? l2_policy_evict_first() : l2_policy_evict_last();
-      const uint64_t pol_b = kSwap ? l2_policy_evict_last() : l2_policy_evict_first();
-      for (int kb = 0; kb < num_kb; ++kb) {
+    if (lane == 0) {
+      pdl_wait();   // activations (and everything else written by earlier kernels) are visible from here on
+      for (int kb = 0; kb < pre; ++kb) {
+        const int kc = (kb_begin + kb) * kBlockK;
+        if (kSwap) tma_load_2d_hint(smem_b + kb * C::kBBytes, &tmap_b, &full_bar[kb], kc, b0, pol_b);
+        else tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], kc, a0, pol_a);
+      }
+      for (int kb = pre; kb < num_kb; ++kb) {
         const int s = kb % C::kStages;
         const uint32_t ph = (kb / C::kStages) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
@@ -371,6 +385,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 =====
     const int ew = warp & 3;
     const int i = ew * 32 + lane;  // tile row
+    pdl_wait();   // the epilogue reads residuals and writes outputs that earlier kernels may still be using
     mbar_wait(accum_bar, 0);
     tc_fence_after();
     const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
@@ -561,10 +576,12 @@ int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 2 : 1;
   AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, kSwap, kAct>, ta, tb, p));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
@@ -643,9 +660,11 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   int splits = c.force_splits;
   if (splits == 0) {
     splits = 1;
-    const int target = 2 * w->sm_count;
+    // measured on B200 (profiles/r01_gemm_sweep.json): keep the grid within ~1.75 CTAs per SM - clusters of 8 that
+    // spill into a second wave cost more than the extra parallelism brings
+    const int target = (7 * w->sm_count) / 4;
     if (tiles < target) {
-      splits = (target + tiles - 1) / tiles;
+      splits = target / tiles;
       const int max_by_k = kb_total / 4 > 0 ? kb_total / 4 : 1;  // at least 4 k-blocks per split
       if (splits > max_by_k) splits = max_by_k;
       if (splits > 8) splits = 8;

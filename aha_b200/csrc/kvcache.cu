@@ -70,6 +70,8 @@ struct RerotLayers { bf16* k[64]; };
 
 __global__ void __launch_bounds__(256) rerotate_kernel(RerotLayers ls, const bf16* __restrict__ rerot, int kvh, int d,
                                                        int cap, int S, int R, int base, int keep) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int tpk = d >> 4;  // threads per key
   const long long total = (long long)kvh * keep * tpk;
   bf16* K = ls.k[blockIdx.y];
@@ -167,6 +169,8 @@ __global__ void move_ids_kernel(const int32_t* __restrict__ src, int32_t* __rest
 __global__ void __launch_bounds__(256) rope_append_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ cos,
                                                           const bf16* __restrict__ sin, bf16* __restrict__ qbuf,
                                                           RopeAppendArgs a, int q, int heads, int kvh, int d, int cap) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int tph = d >> 4;                 // threads per head row
   const int slots = heads + 2 * kvh;
   const int ld = slots * d;
@@ -389,8 +393,8 @@ int cache_rerotate(aha_cache_s* c, int layer0, int n, const UpdatePlan& p, cudaS
     // enough CTAs per layer to put ~2 waves on 148 SMs across all layers of the launch
     int gx = (int)std::min<long long>((items + 255) / 256, std::max(1, (148 * 8 + cnt - 1) / cnt));
     dim3 grid(gx, cnt);
-    rerotate_kernel<<<grid, 256, 0, st>>>(ls, it->second, c->kvh, c->d, c->cap, c->S, c->R, p.new_base, p.keep);
-    ++g_aha_launch_count;
+    int rc = launch_pdl(rerotate_kernel, grid, dim3(256), 0, st, ls, (const bf16*)it->second, c->kvh, c->d, c->cap, c->S, c->R, p.new_base, p.keep);
+    if (rc) return rc;
   }
   AHA_CHECK_LAUNCH();
   return AHA_OK;
@@ -425,10 +429,7 @@ int op_rope_append(const bf16* qkv, const bf16* cos, const bf16* sin, bf16* qbuf
   AHA_REQUIRE(n_streams > 0 && n_streams <= 16 && d % 16 == 0 && heads % kvh == 0, "rope_append: bad shape");
   const long long items = (long long)q * (heads + 2 * kvh) * (d / 16);
   dim3 grid(grid_for(items, 256), n_streams);
-  rope_append_kernel<<<grid, 256, 0, st>>>(qkv, cos, sin, qbuf, a, q, heads, kvh, d, cap);
-  ++g_aha_launch_count;
-  AHA_CHECK_LAUNCH();
-  return AHA_OK;
+  return launch_pdl(rope_append_kernel, grid, dim3(256), 0, st, qkv, cos, sin, qbuf, a, q, heads, kvh, d, cap);
 }
 
 // =====================================================================================
