@@ -43,7 +43,7 @@ int aha_gemm_bf16(const void* x, int tokens, int ldx, const void* w, int feature
   c.w = (const bf16*)w; c.features = features; c.ldw = ldw; c.K = K;
   c.out = out; c.ldo = ldo; c.out_f32 = out_f32; c.round_bf16 = round_bf16; c.act = act;
   c.bias = (const bf16*)bias; c.residual = (const bf16*)residual; c.ldr = ldr; c.res_mod = res_mod;
-  c.force_swap = force_swap; c.force_bn = force_bn; c.force_splits = force_splits;
+  c.force_swap = force_swap; c.force_bn = force_bn; c.force_splits = force_splits; c.force_deep = -1;
   return gemm_bf16(c, ws, (cudaStream_t)stream);
 }
 

@@ -110,6 +110,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_slot);
+  // chunk-versus-cache attention is latency-bound and leaves HBM idle: warp 3 (otherwise unused) requests this CTA's
+  // slice of the weights the following GEMMs will stream (independent of every earlier kernel, so before pdl_wait)
+  if (warp == 3 && lane == 0 && p.pf_early)
+    l2_prefetch_slice(p.pf, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                      gridDim.x * gridDim.y * gridDim.z);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -147,6 +152,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, &tmap_v, &kv_full[s], v_col + b * 64, v_row + key0);
           }
         }
+        if (!p.pf_early)
+          l2_prefetch_slice(p.pf, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                            gridDim.x * gridDim.y * gridDim.z);
       }
     } else if (warp == 1) {
       // ===================== MMA issuer =====================

@@ -59,6 +59,37 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 #endif
 
+// ---- weight-stream L2 prefetch ----
+// The single-stream decoder step is bound by streaming ~13 GB of weights per frame, yet HBM idles during every kernel's
+// ramp-up / tail and during the latency-bound kernels (attention, norms, RoPE).  Each hot-path kernel therefore carries
+// up to two byte ranges of the weights that a LATER kernel will stream; one elected thread per CTA requests its slice
+// of them into L2 (cp.async.bulk.prefetch.L2) once the CTA's own loads are in flight.  model.cu keeps the rolling
+// window (how far ahead of consumption the stream has been requested) bounded by the L2 capacity.
+struct L2Prefetch {
+  const void* p[2];
+  unsigned long long n[2];   // bytes, multiples of 16
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void l2_prefetch_slice(const L2Prefetch& pf, unsigned cta, unsigned ncta) {
+  constexpr unsigned kGran = 8192;
+#pragma unroll 1
+  for (int s = 0; s < 2; ++s) {
+    const unsigned long long n = pf.n[s];
+    if (n == 0) continue;
+    const unsigned ngran = (unsigned)((n + kGran - 1) / kGran);
+    const unsigned per = (ngran + ncta - 1) / ncta;
+    const unsigned g1 = min(ngran, (cta + 1) * per);
+#pragma unroll 1
+    for (unsigned g = cta * per; g < g1; ++g) {
+      const unsigned long long off = (unsigned long long)g * kGran;
+      const unsigned bytes = (unsigned)min((unsigned long long)kGran, n - off);
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"((const char*)pf.p[s] + off), "r"(bytes) : "memory");
+    }
+  }
+}
+#endif
+
 #ifdef __CUDACC__
 
 __device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }

@@ -3,6 +3,9 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <map>
+#include <mutex>
+#include "common.cuh"
 
 enum GemmAct { GEMM_ACT_NONE = 0, GEMM_ACT_GELU_TANH = 1, GEMM_ACT_GELU_ERF = 2, GEMM_ACT_SILU_MUL = 3 };
 
@@ -10,7 +13,7 @@ enum GemmAct { GEMM_ACT_NONE = 0, GEMM_ACT_GELU_TANH = 1, GEMM_ACT_GELU_ERF = 2,
 struct GemmParams {
   int Ma, Nb, K;        // rows of A, rows of B, shared inner dimension
   int swap;             // 0: A = tokens, B = features ; 1: A = features (weights), B = tokens
-  int splits;           // split-K factor (gridDim.z == cluster size, <= 8)
+  int splits;           // split-K factor (gridDim.z)
   int kb_per_split;     // 64-wide k-blocks per split
   void* out;            // out[token * ldo + feature]; bf16 unless out_f32
   int ldo;
@@ -22,6 +25,9 @@ struct GemmParams {
   int ldr;
   int res_mod;          // 0 = no modulo
   int dbg;              // bring-up knob (AHA_GEMM_DBG): 1 = return at entry, 2 = skip epilogue math/stores
+  float* ws_partial;    // split-K workspace: [tile][split][BN][128] fp32 partial tiles
+  int* ws_counters;     // split-K arrival counter per tile (zero between launches)
+  L2Prefetch pf;        // weights of LATER kernels to request into L2 once this CTA's own loads are in flight
 };
 
 // Description of one GEMM call as the model layers see it:  out[tokens, features] = X[tokens, K] . W[features, K]^T
@@ -36,10 +42,18 @@ struct GemmCall {
   int force_swap;    // -1 auto, 0 tall, 1 skinny
   int force_bn;      // 0 auto
   int force_splits;  // 0 auto
+  int force_deep;    // -1 auto, 0 two CTAs per SM, 1 one CTA per SM with the deep operand ring (skinny only)
+  L2Prefetch pf;     // see common.cuh (all zero: nothing to prefetch)
 };
 
+// Split-K scratch is per CUDA stream (launches on one stream are ordered; two streams must not share counters).
+struct GemmSplitScratch { float* partial = nullptr; int* counters = nullptr; };
 struct GemmWorkspace {
   int sm_count = 148;
+  static constexpr size_t kPartialBytes = 64u << 20;
+  static constexpr int kCounters = 8192;
+  std::map<cudaStream_t, GemmSplitScratch> scratch;
+  std::mutex mu;
 };
 
 int gemm_workspace_create(GemmWorkspace* w, int device);

@@ -18,9 +18,10 @@
 //            distinct slab of weights - the skinny GEMMs are HBM-bound on weight bytes)
 // Output is always out[token * ldo + feature].
 //
-// Split-K: the gridDim.z K-splits of a tile form one thread-block cluster; partial tiles are parked in
-// shared memory and reduced in rank order through distributed shared memory (deterministic, no HBM
-// workspace, no atomics).
+// Split-K: the gridDim.z K-splits of a tile are ordinary, independently scheduled CTAs (no cluster: co-scheduling 5-8
+// CTAs inside one GPC cost more than it saved, profiles/r01_decoder_breakdown.txt).  Every split writes its fp32
+// partial tile to an L2-resident workspace and arrives at the tile's counter; once all splits have arrived, split r
+// reduces the 16-column chunks c with c mod s == r in split order 0..s-1 (deterministic) and runs their epilogue.
 //
 // Replaces the cuBLAS calls behind nn.Linear in the reference: SigLIP q/k/v/out/fc1/fc2
 // (LLaVA_NeXT/llava/model/multimodal_encoder/siglip_encoder.py:197-255), mm_projector
@@ -31,7 +32,6 @@
 #include "gemm.h"
 
 #include <cuda.h>
-#include <cooperative_groups.h>
 #include <cstdlib>
 #include <deque>
 #include <map>
@@ -39,7 +39,6 @@
 #include <tuple>
 
 using namespace sm100;
-namespace cg = cooperative_groups;
 
 namespace {
 
@@ -48,9 +47,13 @@ constexpr int kBlockK = 64;   // bf16 elements per stage row == one 128-byte swi
 constexpr int kUmmaK = 16;
 constexpr int kThreads = 256;
 
-template <int BN>
+// kDeep = 0: two CTAs per SM share the shared memory (grids of ~2 CTAs per SM: the big weight matrices, the tall GEMMs).
+// kDeep = 1: one CTA per SM owns a ~190 KB operand ring (grids of <= 1 CTA per SM: the small / split-K skinny GEMMs);
+//            the whole ring of weight tiles is requested before griddepcontrol.wait, i.e. under the previous kernel.
+template <int BN, bool kDeep>
 struct Cfg {
-  static constexpr int kStages = (BN <= 32) ? 5 : (BN <= 64) ? 4 : (BN <= 128) ? 3 : 4;
+  static constexpr int kStages = kDeep ? ((BN <= 32) ? 10 : (BN <= 64) ? 8 : (BN <= 128) ? 6 : 4)
+                                       : ((BN <= 32) ? 5 : (BN <= 64) ? 4 : (BN <= 128) ? 3 : 4);
   static constexpr int kABytes = kBlockM * kBlockK * 2;
   static constexpr int kBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -288,11 +291,11 @@ __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t ta
   }
 }
 
-template <int BN, bool kSwap, int kAct>
-__global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
+template <int BN, bool kSwap, int kAct, bool kDeep>
+__global__ void __launch_bounds__(kThreads, (BN <= 128 && !kDeep) ? 2 : 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, kDeep>;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte alignment.
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -360,6 +363,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         tma_load_2d_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kc, a0, pol_a);
         tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kc, b0, pol_b);
       }
+      // every load of this CTA is in flight: keep HBM busy through the tail (reduction, epilogue, the next kernel's
+      // ramp-up) by requesting this CTA's slice of the weights a later kernel will stream
+      l2_prefetch_slice(p.pf, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                        gridDim.x * gridDim.y * gridDim.z);
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
@@ -422,53 +429,59 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         epi_tall_staged<BN, kAct>(p, taddr, smem + ew * 32 * (BN * 2 + 16), a0, b0, ew, lane);
       }
     } else {
-      // Split-K over a thread-block cluster (cluster dims 1 x 1 x splits): every CTA parks its fp32 partial
-      // tile in its own shared memory (the operand ring is idle by now), then 16-column chunks are
-      // reduced through distributed shared memory in rank order (deterministic) by CTA (chunk % splits).
-      float* stage = reinterpret_cast<float*>(smem);  // [BN][128] fp32, column-major: conflict-free per warp
+      // Split-K: park this split's fp32 partial tile in the workspace ([column][128 rows]: a warp store is one
+      // 128-byte line), then the last CTA to arrive at the tile's counter reduces in split order.
+      const int tile_lin = blockIdx.y * gridDim.x + blockIdx.x;
+      const int ncols = min(BN, p.Nb - b0);
+      float* part = p.ws_partial + ((size_t)tile_lin * p.splits + split) * (size_t)(BN * kBlockM) + i;
 #pragma unroll 1
-      for (int jc = 0; jc < BN; jc += 16) {
+      for (int jc = 0; jc < ncols; jc += 16) {
         uint32_t r[16];
         tmem_ld_32x32b_x16(taddr + jc, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int t = 0; t < 16; ++t) stage[(jc + t) * kBlockM + i] = __uint_as_float(r[t]);
+        for (int t = 0; t < 16; ++t) __stcg(part + (jc + t) * kBlockM, __uint_as_float(r[t]));
       }
-    }
-    tc_fence_before();
-  }
-
-  if (p.splits > 1) {
-    cg::cluster_group cluster = cg::this_cluster();
-    __syncwarp();
-    cluster.sync();  // all partial tiles are visible cluster-wide
-    if (warp >= 4) {
-      const int ew = warp & 3;
-      const int i = ew * 32 + lane;
-      const int rank = (int)cluster.block_rank();
-      float* stage = reinterpret_cast<float*>(smem);
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      int* cnt = p.ws_counters + 2 * tile_lin;
+      if (threadIdx.x == 128) {
+        // arrive, then wait for the other splits of this tile.  All CTAs of a split grid are co-resident (the host keeps
+        // tiles*splits within the device's resident-CTA capacity), so the wait cannot deadlock; it is bounded anyway.
+        atomicAdd(cnt, 1);
+        uint32_t spins = 0;
+        while (*reinterpret_cast<volatile int*>(cnt) < p.splits) {
+          if (++spins > (1u << 24)) { printf("aha_b200: split-K arrival wait timed out (tile %d)\n", tile_lin); __trap(); }
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      __threadfence();
+      // 16-column chunk c is reduced (in split order 0..s-1: deterministic) and finished by split (c mod splits)
+      const float* base = p.ws_partial + (size_t)tile_lin * p.splits * (size_t)(BN * kBlockM) + i;
+      const int feat = a0 + i;
+      const bool fvalid = feat < p.Ma;
+      const float bias = (kSwap && p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
 #pragma unroll 1
-      for (int c = rank; c < BN / 16; c += p.splits) {
-        const int jc = c * 16;
+      for (int jc = split * 16; jc < ncols; jc += 16 * p.splits) {
         float acc[16];
 #pragma unroll
         for (int t = 0; t < 16; ++t) acc[t] = 0.f;
-        for (int s = 0; s < p.splits; ++s) {
-          const float* peer = cluster.map_shared_rank(stage, s) + jc * kBlockM + i;
+#pragma unroll 4
+        for (int sp = 0; sp < p.splits; ++sp) {
+          const float* pp = base + (size_t)sp * (BN * kBlockM) + jc * kBlockM;
+          float v[16];
 #pragma unroll
-          for (int t = 0; t < 16; ++t) acc[t] += peer[t * kBlockM];
+          for (int t = 0; t < 16; ++t) v[t] = __ldcg(pp + t * kBlockM);
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] += v[t];
         }
-        if (kSwap) {
-          const int feat = a0 + i;
-          const bool fvalid = feat < p.Ma;
-          epi_swap16<kAct>(p, feat, fvalid, (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f, i, b0 + jc, acc);
-        } else {
-          epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
-        }
+        if (kSwap) epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+        else epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
       }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 128 && atomicAdd(cnt + 1, 1) == p.splits - 1) { cnt[0] = 0; cnt[1] = 0; }   // last one out re-arms
     }
-    __syncwarp();
-    cluster.sync();  // nobody leaves while peers still read its shared memory
+    tc_fence_before();
   }
 
   __syncthreads();
@@ -566,23 +579,21 @@ void prof_end(ProfSlot* s, cudaStream_t st, double bytes, double flops) {
   cudaEventRecord(s->e1, st);
 }
 
-template <int BN, bool kSwap, int kAct>
+template <int BN, bool kSwap, int kAct, bool kDeep>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, kDeep>;
   static bool attr_done = false;
   if (!attr_done) {
-    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct, kDeep>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
   cudaLaunchAttribute attr[2];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
-  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 2 : 1;
-  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, kSwap, kAct>, ta, tb, p));
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, kSwap, kAct, kDeep>, ta, tb, p));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;
@@ -591,33 +602,41 @@ int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
 }  // namespace
 
 namespace {
-template <int BN, bool kSwap>
+template <int BN, bool kSwap, bool kDeep>
 int dispatch_act(int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t st) {
   if (kSwap) {   // skinny orientation: plain or SiLU*mul (GELU callers are routed to the tall orientation)
-    if (act == GEMM_ACT_SILU_MUL) return launch_bn<BN, kSwap, GEMM_ACT_SILU_MUL>(ta, tb, p, grid, st);
-    return launch_bn<BN, kSwap, GEMM_ACT_NONE>(ta, tb, p, grid, st);
+    if (act == GEMM_ACT_SILU_MUL) return launch_bn<BN, kSwap, GEMM_ACT_SILU_MUL, kDeep>(ta, tb, p, grid, st);
+    return launch_bn<BN, kSwap, GEMM_ACT_NONE, kDeep>(ta, tb, p, grid, st);
   }
   switch (act) {
-    case GEMM_ACT_GELU_TANH: return launch_bn<BN, false, GEMM_ACT_GELU_TANH>(ta, tb, p, grid, st);
-    case GEMM_ACT_GELU_ERF: return launch_bn<BN, false, GEMM_ACT_GELU_ERF>(ta, tb, p, grid, st);
-    case GEMM_ACT_SILU_MUL: return launch_bn<BN, false, GEMM_ACT_SILU_MUL>(ta, tb, p, grid, st);
-    default: return launch_bn<BN, false, GEMM_ACT_NONE>(ta, tb, p, grid, st);
+    case GEMM_ACT_GELU_TANH: return launch_bn<BN, false, GEMM_ACT_GELU_TANH, false>(ta, tb, p, grid, st);
+    case GEMM_ACT_GELU_ERF: return launch_bn<BN, false, GEMM_ACT_GELU_ERF, false>(ta, tb, p, grid, st);
+    case GEMM_ACT_SILU_MUL: return launch_bn<BN, false, GEMM_ACT_SILU_MUL, false>(ta, tb, p, grid, st);
+    default: return launch_bn<BN, false, GEMM_ACT_NONE, false>(ta, tb, p, grid, st);
   }
 }
-int dispatch(int bn, int swap, int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid,
-             cudaStream_t st) {
+int dispatch(int bn, int swap, int deep, int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
+             dim3 grid, cudaStream_t st) {
+  if (swap && deep) {
+    switch (bn) {
+      case 32: return dispatch_act<32, true, true>(act, ta, tb, p, grid, st);
+      case 64: return dispatch_act<64, true, true>(act, ta, tb, p, grid, st);
+      case 128: return dispatch_act<128, true, true>(act, ta, tb, p, grid, st);
+      default: return dispatch_act<256, true, false>(act, ta, tb, p, grid, st);   // BN 256 is one CTA per SM already
+    }
+  }
   if (swap) {
     switch (bn) {
-      case 32: return dispatch_act<32, true>(act, ta, tb, p, grid, st);
-      case 64: return dispatch_act<64, true>(act, ta, tb, p, grid, st);
-      case 128: return dispatch_act<128, true>(act, ta, tb, p, grid, st);
-      default: return dispatch_act<256, true>(act, ta, tb, p, grid, st);
+      case 32: return dispatch_act<32, true, false>(act, ta, tb, p, grid, st);
+      case 64: return dispatch_act<64, true, false>(act, ta, tb, p, grid, st);
+      case 128: return dispatch_act<128, true, false>(act, ta, tb, p, grid, st);
+      default: return dispatch_act<256, true, false>(act, ta, tb, p, grid, st);
     }
   }
   switch (bn) {
-    case 64: return dispatch_act<64, false>(act, ta, tb, p, grid, st);
-    case 128: return dispatch_act<128, false>(act, ta, tb, p, grid, st);
-    default: return dispatch_act<256, false>(act, ta, tb, p, grid, st);
+    case 64: return dispatch_act<64, false, false>(act, ta, tb, p, grid, st);
+    case 128: return dispatch_act<128, false, false>(act, ta, tb, p, grid, st);
+    default: return dispatch_act<256, false, false>(act, ta, tb, p, grid, st);
   }
 }
 }  // namespace
@@ -629,7 +648,24 @@ int gemm_workspace_create(GemmWorkspace* w, int device) {
   return AHA_OK;
 }
 
-void gemm_workspace_destroy(GemmWorkspace*) {}
+void gemm_workspace_destroy(GemmWorkspace* w) {
+  for (auto& kv : w->scratch) { cudaFree(kv.second.partial); cudaFree(kv.second.counters); }
+  w->scratch.clear();
+}
+
+static int split_scratch(GemmWorkspace* w, cudaStream_t st, GemmSplitScratch* out) {
+  std::lock_guard<std::mutex> lk(w->mu);
+  auto it = w->scratch.find(st);
+  if (it == w->scratch.end()) {
+    GemmSplitScratch s;
+    AHA_CUDA(cudaMalloc(&s.partial, GemmWorkspace::kPartialBytes));
+    AHA_CUDA(cudaMalloc(&s.counters, 2 * GemmWorkspace::kCounters * sizeof(int)));
+    AHA_CUDA(cudaMemsetAsync(s.counters, 0, 2 * GemmWorkspace::kCounters * sizeof(int), st));
+    it = w->scratch.emplace(st, s).first;
+  }
+  *out = it->second;
+  return AHA_OK;
+}
 
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
@@ -642,6 +678,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   p.K = c.K; p.swap = swap;
   p.out = c.out; p.ldo = c.ldo; p.out_f32 = c.out_f32; p.round_bf16 = c.round_bf16; p.act = c.act;
   p.bias = c.bias; p.residual = c.residual; p.ldr = c.ldr; p.res_mod = c.res_mod;
+  p.pf = c.pf;
   const void* a; const void* b; int lda, ldb;
   if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
   else      { p.Ma = c.tokens; p.Nb = c.features; a = c.x; lda = c.ldx; b = c.w; ldb = c.ldw; }
@@ -658,10 +695,25 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   const int tiles = tiles_a * tiles_b;
   const int kb_total = (p.K + kBlockK - 1) / kBlockK;
   int splits = c.force_splits;
-  if (splits == 0) {
+  int deep = c.force_deep;
+  { static int env = -2; if (env == -2) { const char* e = getenv("AHA_GEMM_DEEP"); env = e ? atoi(e) : -1; } if (env >= 0) deep = env; }
+  if (splits == 0 && swap) {
+    // Skinny (weight-streaming) orientation: every SM should pull the same number of weight bytes.  With s splits the
+    // grid has tiles*s CTAs of ceil(kb/s) k-blocks; CTAs beyond one per SM run as a second resident CTA (or a second
+    // wave), so the per-SM critical path is ceil(ctas / SMs) * kb_per_split.  Fewer splits win ties (cheaper merge).
+    long best_cost = -1;
+    for (int s = 1; s <= 8 && s <= kb_total; ++s) {
+      const int kb_per = (kb_total + s - 1) / s;
+      const int s_eff = (kb_total + kb_per - 1) / kb_per;
+      if (s_eff != s) continue;
+      const long ctas = (long)tiles * s;
+      if (s > 1 && ctas > (long)w->sm_count * (bn <= 128 ? 2 : 1)) continue;   // split CTAs must all be co-resident
+      const long cost = ((ctas + w->sm_count - 1) / w->sm_count) * kb_per + (s - 1);
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
+    }
+  } else if (splits == 0) {
     splits = 1;
-    // measured on B200 (profiles/r01_gemm_sweep.json): keep the grid within ~1.75 CTAs per SM - clusters of 8 that
-    // spill into a second wave cost more than the extra parallelism brings
+    // tall orientation (measured on B200, profiles/r01_gemm_sweep.json): keep the grid within ~1.75 CTAs per SM
     const int target = (7 * w->sm_count) / 4;
     if (tiles < target) {
       splits = target / tiles;
@@ -675,13 +727,29 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   splits = (kb_total + kb_per - 1) / kb_per;  // no empty splits
   p.splits = splits; p.kb_per_split = kb_per;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("AHA_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
-  AHA_REQUIRE(splits <= 8, "split-K factor above the portable cluster size (8)");
+  AHA_REQUIRE(splits <= 16, "split-K factor above 16");
+  // the splits of a tile wait for each other: the whole grid has to fit the device at once
+  while (splits > 1 && ((long)tiles * splits > (long)w->sm_count * (bn <= 128 ? 2 : 1) ||
+                        (size_t)tiles * splits * bn * kBlockM * sizeof(float) > GemmWorkspace::kPartialBytes ||
+                        tiles > GemmWorkspace::kCounters)) {
+    --splits;
+    kb_per = (kb_total + splits - 1) / splits;
+    splits = (kb_total + kb_per - 1) / kb_per;
+  }
+  p.splits = splits; p.kb_per_split = kb_per;
+  if (splits > 1) {
+    GemmSplitScratch sc;
+    int src = split_scratch(w, stream, &sc); if (src) return src;
+    p.ws_partial = sc.partial; p.ws_counters = sc.counters;
+  }
   CUtensorMap ta, tb;
   int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
   dim3 grid(tiles_a, tiles_b, splits);
+  if (deep < 0) deep = (swap && (long)tiles * splits <= w->sm_count) ? 1 : 0;   // <= one CTA per SM: give it the whole SM
+  if (deep && splits > 1 && (long)tiles * splits > w->sm_count) deep = 0;       // split CTAs must stay co-resident
   ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);
-  rc = dispatch(bn, swap, c.act, ta, tb, p, grid, stream);
+  rc = dispatch(bn, swap, deep, c.act, ta, tb, p, grid, stream);
   if (slot) {
     const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * (c.out_f32 ? 4 : 2);
     prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,

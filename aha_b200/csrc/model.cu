@@ -7,6 +7,7 @@
 #include "kvcache.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <map>
 #include <string>
 #include <vector>
@@ -24,8 +25,41 @@ struct DecoderLayerW {
 
 }  // namespace
 
+// The decoder's weights in the order one prefill step streams them (qkv, o, gate|up, down per layer), as one circular
+// byte stream.  `issued` is how far (relative to the start of the running step) L2 prefetch requests have been handed
+// out; it never runs more than `cap` bytes ahead of the kernel being launched, so the prefetched lines fit the L2.
+struct WeightStream {
+  std::vector<const char*> ptr;
+  std::vector<size_t> begin;      // begin[i] .. begin[i+1] = stream range of segment i
+  size_t total = 0, cap = 0;
+  long long issued = 0;
+  void add(const void* p, size_t bytes) {
+    if (begin.empty()) begin.push_back(0);
+    ptr.push_back((const char*)p); total += bytes; begin.push_back(total);
+  }
+  size_t end_of(int seg) const { return begin[seg + 1]; }
+  // ranges to request while a kernel runs that will have consumed the stream up to `consumed`
+  L2Prefetch take(size_t consumed) {
+    L2Prefetch pf{};
+    if (cap == 0 || total == 0) return pf;
+    if (issued < (long long)consumed) issued = (long long)consumed;
+    long long room = (long long)(consumed + cap) - issued;
+    for (int k = 0; k < 2 && room >= 16; ++k) {
+      const size_t pos = (size_t)(issued % (long long)total);
+      const int seg = (int)(std::upper_bound(begin.begin(), begin.end(), pos) - begin.begin()) - 1;
+      size_t n = std::min<size_t>(begin[seg + 1] - pos, (size_t)room) & ~(size_t)15;
+      if (n == 0) break;
+      pf.p[k] = ptr[seg] + (pos - begin[seg]); pf.n[k] = n;
+      issued += (long long)n; room -= (long long)n;
+    }
+    return pf;
+  }
+  void end_step() { issued = std::max<long long>(0, issued - (long long)total); }
+};
+
 struct aha_model_s {
   aha_model_desc d{};
+  WeightStream wstream;
   int device = 0;
   // derived geometry
   int v_side = 0, v_patches = 0, v_hd = 0, v_hd_pad = 0, v_kpad = 0, v_qkv_cols = 0;
@@ -173,6 +207,19 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
     TRY(op_copy_rows(uw, H, w.gu_w, H, d.inter, H, 1, 2, 0));
     TRY(copy_w(m, wt, p + "mlp.down_proj.weight", H, d.inter, &w.down_w));
   }
+  for (int l = 0; l < d.layers; ++l) {
+    const DecoderLayerW& w = m->dl[l];
+    m->wstream.add(w.qkv_w, (size_t)m->qkv_cols * H * 2);
+    m->wstream.add(w.o_w, (size_t)H * qd * 2);
+    m->wstream.add(w.gu_w, (size_t)2 * d.inter * H * 2);
+    m->wstream.add(w.down_w, (size_t)H * d.inter * 2);
+  }
+  {
+    // rolling L2 prefetch window in MB (AHA_PF_MB).  OFF by default: on B200 it measured no gain (the skinny GEMMs are
+    // bound by their latency chain, not by where their bytes come from; profiles/r01_l2_prefetch_sweep.txt)
+    const char* e = getenv("AHA_PF_MB");
+    m->wstream.cap = (size_t)(e ? std::max(0, atoi(e)) : 0) << 20;
+  }
   // Qwen2RotaryEmbedding: inv_freq = 1 / theta^(arange(0, d, 2) / d), float32 like torch
   {
     std::vector<float> inv(d.head_dim / 2);
@@ -210,14 +257,16 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
 namespace {
 
 int linear(const bf16* x, int tokens, int ldx, const bf16* w, int features, int K, void* out, int ldo, int act,
-           const bf16* bias, const bf16* residual, int ldr, int res_mod, int out_f32, cudaStream_t st) {
+           const bf16* bias, const bf16* residual, int ldr, int res_mod, int out_f32, cudaStream_t st,
+           const L2Prefetch* pf = nullptr) {
   int rc;
   GemmWorkspace* ws = aha_default_workspace(&rc);
   if (!ws) return rc;
   GemmCall c{};
   c.x = x; c.tokens = tokens; c.ldx = ldx; c.w = w; c.features = features; c.ldw = K; c.K = K;
   c.out = out; c.ldo = ldo; c.out_f32 = out_f32; c.round_bf16 = out_f32; c.act = act; c.bias = bias;
-  c.residual = residual; c.ldr = ldr; c.res_mod = res_mod; c.force_swap = -1; c.force_bn = 0; c.force_splits = 0;
+  c.residual = residual; c.ldr = ldr; c.res_mod = res_mod; c.force_swap = -1; c.force_bn = 0; c.force_splits = 0; c.force_deep = -1;
+  if (pf) c.pf = *pf;
   return gemm_bf16(c, ws, st);
 }
 
@@ -304,10 +353,17 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
   ap.scale = 1.0f / sqrtf((float)hd);
   ap.out = m->ws_attn; ap.out_ld = qd;
   ap.n_segs = 1;
+  // bring-up knob (timing breakdowns only, results are garbage): bit mask of per-layer kernels to skip
+  // 1 norms, 2 rope+append, 4 attention, 8 qkv, 16 o_proj, 32 gate|up, 64 down
+  static const int skip = getenv("AHA_SKIP") ? atoi(getenv("AHA_SKIP")) : 0;
   for (int l = 0; l < d.layers; ++l) {
     const DecoderLayerW& w = m->dl[l];
-    TRY(op_rmsnorm(m->ws_x, w.in_ln, m->ws_h, M, H, d.rms_eps, st));
-    TRY(linear(m->ws_h, M, H, w.qkv_w, m->qkv_cols, H, m->ws_qkv, m->qkv_cols, GEMM_ACT_NONE, w.qkv_b, nullptr, 0, 0, 0, st));
+    if (!(skip & 1)) TRY(op_rmsnorm(m->ws_x, w.in_ln, m->ws_h, M, H, d.rms_eps, st));
+    WeightStream& wsm = m->wstream;
+    static const int pf_gemm = getenv("AHA_PF_GEMM") ? atoi(getenv("AHA_PF_GEMM")) : 1;
+    auto take_g = [&](int seg) { return pf_gemm ? wsm.take(wsm.end_of(seg)) : L2Prefetch{}; };
+    L2Prefetch pf = take_g(4 * l);
+    if (!(skip & 8)) TRY(linear(m->ws_h, M, H, w.qkv_w, m->qkv_cols, H, m->ws_qkv, m->qkv_cols, GEMM_ACT_NONE, w.qkv_b, nullptr, 0, 0, 0, st, &pf));
     RopeAppendArgs aa{};
     int cap = caches[0]->cap;
     for (int s = 0; s < ns; ++s) {
@@ -316,7 +372,7 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
       aa.s[s] = RopeAppendStream{c->layers[l].k, c->layers[l].v, plans[s].store_begin, plans[s].store_end,
                                  plans[s].store_phys0, plans[s].wrap_end, plans[s].R};
     }
-    TRY(op_rope_append(m->ws_qkv, m->ws_cos, m->ws_sin, m->ws_qbuf, aa, ns, q, nh, kvh, hd, cap, st));
+    if (!(skip & 2)) TRY(op_rope_append(m->ws_qkv, m->ws_cos, m->ws_sin, m->ws_qbuf, aa, ns, q, nh, kvh, hd, cap, st));
     for (int s = 0; s < ns; ++s) {
       aha_cache_s* c = caches[s];
       const UpdatePlan& p = plans[s];
@@ -331,13 +387,20 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
       const bool ring = c->policy != AHA_POLICY_STATIC && p.klen <= c->W;
       sg.ring_S = c->S; sg.ring_R = ring ? c->R : 0; sg.ring_base = p.new_base;
       sg.out_row0 = s * q;
-      TRY(op_attention(ap, st));
+      static const int pf_attn = getenv("AHA_PF_ATTN") ? atoi(getenv("AHA_PF_ATTN")) : 1;
+      ap.pf = pf_attn ? wsm.take(wsm.end_of(4 * l)) : L2Prefetch{};
+      ap.pf_early = pf_attn == 2;
+      if (!(skip & 4)) TRY(op_attention(ap, st));
     }
-    TRY(linear(m->ws_attn, M, qd, w.o_w, H, qd, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st));
-    TRY(op_rmsnorm(m->ws_x, w.post_ln, m->ws_h, M, H, d.rms_eps, st));
-    TRY(linear(m->ws_h, M, H, w.gu_w, 2 * d.inter, H, m->ws_act, d.inter, GEMM_ACT_SILU_MUL, nullptr, nullptr, 0, 0, 0, st));
-    TRY(linear(m->ws_act, M, d.inter, w.down_w, H, d.inter, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st));
+    pf = take_g(4 * l + 1);
+    if (!(skip & 16)) TRY(linear(m->ws_attn, M, qd, w.o_w, H, qd, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf));
+    if (!(skip & 1)) TRY(op_rmsnorm(m->ws_x, w.post_ln, m->ws_h, M, H, d.rms_eps, st));
+    pf = take_g(4 * l + 2);
+    if (!(skip & 32)) TRY(linear(m->ws_h, M, H, w.gu_w, 2 * d.inter, H, m->ws_act, d.inter, GEMM_ACT_SILU_MUL, nullptr, nullptr, 0, 0, 0, st, &pf));
+    pf = take_g(4 * l + 3);
+    if (!(skip & 64)) TRY(linear(m->ws_act, M, d.inter, w.down_w, H, d.inter, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf));
   }
+  m->wstream.end_step();
   bf16* hn = hidden_out ? hidden_out : m->ws_hn;
   TRY(op_rmsnorm(m->ws_x, m->norm_w, hn, M, H, d.rms_eps, st));
   if (informative || relevance || uncertainty || scores3)

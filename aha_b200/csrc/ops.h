@@ -51,6 +51,8 @@ struct AttnProblem {
   int d_pad;                // head dim as laid out in Q/K/V columns (multiple of 16, pads are zero in Q and K)
   float scale;
   bf16* out; int out_ld;    // out[token, (block*group + r) * d + c]
+  L2Prefetch pf;            // weights of later kernels to request into L2 (common.cuh)
+  int pf_early;             // 1: request them at kernel entry, 0: after this CTA's own K/V loads are in flight
   int n_segs;
   AttnSeg segs[32];
 };

@@ -90,6 +90,11 @@ __device__ __forceinline__ uint64_t l2_policy_evict_last() {
   return p;
 }
 
+// Fire-and-forget request to pull [p, p + bytes) from HBM into L2 (bytes a multiple of 16, p 16-byte aligned).
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // ---------------- TMEM / tcgen05 ----------------
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst) {
