@@ -21,12 +21,10 @@
 #include "ops.h"
 #include "gemm.h"
 #include "ptx_sm100.cuh"
-#include <cooperative_groups.h>
 #include <cstdio>
 #include <cstdlib>
 
 using namespace sm100;
-namespace cg = cooperative_groups;
 
 namespace {
 
@@ -90,6 +88,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned long long* ts = (p.dbg_ts && threadIdx.x == 128 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg_ts : nullptr;
+  dbg_stamp(ts, 0);
   const int seg_idx = blockIdx.z / splits, split = blockIdx.z % splits;
   const AttnSeg& seg = p.segs[seg_idx];
   const int blk = blockIdx.y;
@@ -119,8 +119,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  dbg_stamp(ts, 1);
   pdl_wait();                 // Q, K and V were all written by earlier kernels on the stream
   pdl_launch_dependents();
+  dbg_stamp(ts, 2);
 
   // softmax-thread state (meaningful in warps 4-7)
   const int ew = warp & 3;
@@ -202,6 +204,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int kt = kt0 + it;
         mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
+        dbg_stamp(ts, 3 + 2 * min(it, 1));
         const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0);
         uint32_t sv[kTile];
         tmem_ld_32x32b_x32p(s_addr, sv);
@@ -271,9 +274,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(p_full);
+        dbg_stamp(ts, 4 + 2 * min(it, 1));
       }
       mbar_wait(pv_done, (nkt - 1) & 1);   // O complete
       tc_fence_after();
+      dbg_stamp(ts, 7);
     }
   }
 
@@ -311,12 +316,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       tc_fence_before();
     }
   } else {
-    // ---- key-split merge over the cluster (1 x 1 x splits), deterministic rank order ----
-    // every CTA parks its unnormalised O (fp32, column-major [d_pad][128]) over the idle K ring and (m, l) over the P tile
-    float* stage = reinterpret_cast<float*>(sK);
-    float* stat_m = reinterpret_cast<float*>(sP);
-    float* stat_l = stat_m + kTile;
+    // ---- key-split merge through an L2-resident workspace, deterministic split order ----
+    // (DSMEM moved these 72 KB per CTA at ~4 B/clk; L2 does it an order of magnitude faster and needs no cluster.)
+    // Every split parks its unnormalised O (fp32 [128][d_pad]) and (m, l), arrives at the counter of its
+    // (segment, block, query tile), waits for the other splits - the host keeps the grid co-resident - and then merges
+    // the 16-column chunks c with c mod splits == split.
     if (warp >= 4) {
+      const int group_lin = (seg_idx * gridDim.y + blk) * gridDim.x + qt;
+      const size_t cta_floats = (size_t)kTile * p.d_pad + 2 * kTile;
+      float* mine = p.ws_partial + ((size_t)group_lin * splits + split) * cta_floats;
 #pragma unroll 1
       for (int cc = 0; cc < p.d_pad; cc += 16) {
         uint32_t r[16];
@@ -327,56 +335,92 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
           for (int t = 0; t < 16; ++t) r[t] = 0u;
         }
+        float4* dst = reinterpret_cast<float4*>(mine + (size_t)row * p.d_pad + cc);
 #pragma unroll
-        for (int t = 0; t < 16; ++t) stage[(cc + t) * kTile + row] = __uint_as_float(r[t]);
+        for (int v4 = 0; v4 < 4; ++v4)
+          __stcg(dst + v4, make_float4(__uint_as_float(r[4 * v4]), __uint_as_float(r[4 * v4 + 1]),
+                                       __uint_as_float(r[4 * v4 + 2]), __uint_as_float(r[4 * v4 + 3])));
       }
-      stat_m[row] = m_used;
-      stat_l[row] = l_sum;
+      __stcg(mine + (size_t)kTile * p.d_pad + row, m_used);
+      __stcg(mine + (size_t)kTile * p.d_pad + kTile + row, l_sum);
       tc_fence_before();
-    }
-    cg::cluster_group cluster = cg::this_cluster();
-    __syncwarp();
-    cluster.sync();
-    if (warp >= 4) {
-      const int rank = (int)cluster.block_rank();
+      dbg_stamp(ts, 8);
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      int* cnt = p.ws_counters + 2 * group_lin;
+      if (threadIdx.x == 128) {
+        atomicAdd(cnt, 1);
+        uint32_t spins = 0;
+        while (*reinterpret_cast<volatile int*>(cnt) < splits) {
+          if (++spins > (1u << 24)) { printf("aha_b200: attention split arrival wait timed out (group %d)\n", group_lin); __trap(); }
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      __threadfence();
+      dbg_stamp(ts, 9);
+      const float* grp = p.ws_partial + (size_t)group_lin * splits * cta_floats;
+      // all loads of a step are issued before the first use (splits beyond `splits` alias split 0 with weight 0)
+      float ms[8], ls[8];
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const float* st = grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)kTile * p.d_pad;
+        ms[s] = __ldcg(st + row);
+        ls[s] = __ldcg(st + kTile + row);
+      }
       float mx = -INFINITY;
-      for (int s = 0; s < splits; ++s) mx = fmaxf(mx, cluster.map_shared_rank(stat_m, s)[row]);
+#pragma unroll
+      for (int s = 0; s < 8; ++s) if (s < splits) mx = fmaxf(mx, ms[s]);
       float wgt[8];
       float L = 0.f;
 #pragma unroll
       for (int s = 0; s < 8; ++s) {
-        wgt[s] = 0.f;
-        if (s < splits) {
-          const float ms = cluster.map_shared_rank(stat_m, s)[row];
-          wgt[s] = (ms == -INFINITY) ? 0.f : ex2_approx(ms - mx);
-          L += wgt[s] * cluster.map_shared_rank(stat_l, s)[row];
-        }
+        wgt[s] = (s < splits && ms[s] != -INFINITY) ? ex2_approx(ms[s] - mx) : 0.f;
+        L += wgt[s] * ls[s];
       }
       const float inv = L > 0.f ? 1.f / L : 0.f;
       bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
 #pragma unroll 1
-      for (int c = rank; c < (p.d_pad >> 4); c += splits) {
+      for (int c = split; c < (p.d_pad >> 4); c += splits) {
         const int cc = c * 16;
+        float4 v[8][4];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + cc);
+#pragma unroll
+          for (int v4 = 0; v4 < 4; ++v4) v[s][v4] = __ldcg(peer + v4);
+        }
         float acc[16];
 #pragma unroll
         for (int t = 0; t < 16; ++t) acc[t] = 0.f;
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
-          if (s < splits) {
-            const float* peer = cluster.map_shared_rank(stage, s) + cc * kTile + row;
 #pragma unroll
-            for (int t = 0; t < 16; ++t) acc[t] += wgt[s] * peer[t * kTile];
+          for (int v4 = 0; v4 < 4; ++v4) {
+            acc[4 * v4 + 0] += wgt[s] * v[s][v4].x;
+            acc[4 * v4 + 1] += wgt[s] * v[s][v4].y;
+            acc[4 * v4 + 2] += wgt[s] * v[s][v4].z;
+            acc[4 * v4 + 3] += wgt[s] * v[s][v4].w;
           }
         }
         if (row_valid) {
+          if (cc + 16 <= p.d && ((reinterpret_cast<uintptr_t>(orow + cc) & 15) == 0)) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] *= inv;
+            st_v4(orow + cc, make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
+                                        pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7])));
+            st_v4(orow + cc + 8, make_uint4(pack_bf16x2(acc[8], acc[9]), pack_bf16x2(acc[10], acc[11]),
+                                            pack_bf16x2(acc[12], acc[13]), pack_bf16x2(acc[14], acc[15])));
+          } else {
 #pragma unroll 4
-          for (int t = 0; t < 16; ++t)
-            if (cc + t < p.d) orow[cc + t] = f2b(acc[t] * inv);
+            for (int t = 0; t < 16; ++t)
+              if (cc + t < p.d) orow[cc + t] = f2b(acc[t] * inv);
+          }
         }
       }
+      dbg_stamp(ts, 10);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 128 && atomicAdd(cnt + 1, 1) == splits - 1) { cnt[0] = 0; cnt[1] = 0; }   // last one out re-arms
     }
-    __syncwarp();
-    cluster.sync();   // nobody leaves while peers still read its shared memory
   }
 
   __syncthreads();
@@ -384,11 +428,26 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
+  dbg_stamp(ts, 12);
 }
 
 }  // namespace
 
-int op_attention(const AttnProblem& p, cudaStream_t st) {
+static unsigned long long* g_attn_ts = nullptr;
+extern "C" int aha_debug_attention_timeline(unsigned long long* out16) {
+  if (!g_attn_ts) { aha_set_error("ValueError: run with AHA_TS=1"); return AHA_ERR_VALUE; }
+  AHA_CUDA(cudaDeviceSynchronize());
+  AHA_CUDA(cudaMemcpy(out16, g_attn_ts, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return AHA_OK;
+}
+
+int op_attention(const AttnProblem& p_in, cudaStream_t st) {
+  AttnProblem p = p_in;
+  static const bool want_ts = getenv("AHA_TS") && atoi(getenv("AHA_TS")) == 1;
+  if (want_ts) {
+    if (!g_attn_ts) { AHA_CUDA(cudaMalloc(&g_attn_ts, 16 * sizeof(unsigned long long))); AHA_CUDA(cudaMemset(g_attn_ts, 0, 128)); }
+    p.dbg_ts = g_attn_ts;
+  }
   AHA_REQUIRE(p.d_pad % 16 == 0 && p.d_pad >= 16 && p.d_pad <= 128 && p.d <= p.d_pad, "attention: head_dim must pad to <= 128");
   AHA_REQUIRE(p.n_segs > 0 && p.n_segs <= 32 && p.n_blocks > 0 && p.nq_rows > 0 && p.group > 0, "attention: bad problem");
   const int DB = (p.d_pad + 63) / 64;
@@ -407,26 +466,34 @@ int op_attention(const AttnProblem& p, cudaStream_t st) {
   const int ctas = q_tiles * p.n_blocks * p.n_segs;
   int max_tiles = 0;
   for (int i = 0; i < p.n_segs; ++i) max_tiles = max_tiles > (p.segs[i].klen + kTile - 1) / kTile ? max_tiles : (p.segs[i].klen + kTile - 1) / kTile;
+  // the splits of a group wait for each other, so the whole grid must be resident at once: one CTA per SM
+  static int sm_count = 0;
+  if (!sm_count) { int dev = 0; AHA_CUDA(cudaGetDevice(&dev)); AHA_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev)); }
   int splits = 1;
-  if (ctas < 148 && max_tiles > 1) {
-    splits = (2 * 148 + ctas - 1) / ctas;
+  if (ctas < sm_count && max_tiles > 1) {
+    splits = sm_count / ctas;
+    if (const char* e = getenv("AHA_ATTN_SPLITS")) { const int v = atoi(e); if (v >= 1 && v < splits) splits = v; }
     if (splits > 8) splits = 8;
     if (splits > max_tiles) splits = max_tiles;
     const int per = (max_tiles + splits - 1) / splits;
     splits = (max_tiles + per - 1) / per;       // no empty splits for the longest segment
   }
-  if (const char* e = getenv("AHA_ATTN_SPLITS")) { const int v = atoi(e); if (v >= 1 && v <= 8) splits = v; }
+  if (splits > 1) {
+    GemmSplitScratch sc;
+    rc = aha_split_scratch(st, &sc); if (rc) return rc;
+    const size_t need = (size_t)ctas * splits * ((size_t)kTile * p.d_pad + 2 * kTile) * sizeof(float);
+    if (need > GemmWorkspace::kPartialBytes || ctas > GemmWorkspace::kCounters) splits = 1;
+    p.ws_partial = sc.partial; p.ws_counters = sc.counters;
+  }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(q_tiles, p.n_blocks, p.n_segs * splits);
   cfg.blockDim = dim3(kAttnThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[2];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = splits;
-  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 2 : 1;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
   AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();

@@ -91,6 +91,13 @@ __device__ __forceinline__ void l2_prefetch_slice(const L2Prefetch& pf, unsigned
 #endif
 
 #ifdef __CUDACC__
+// bring-up aid (AHA_TS=1): one CTA of a kernel stamps its phases with the SM cycle counter
+__device__ __forceinline__ void dbg_stamp(unsigned long long* ts, int slot) {
+  if (ts) ts[slot] = (unsigned long long)clock64();
+}
+#endif
+
+#ifdef __CUDACC__
 
 __device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 __device__ __forceinline__ float b2f(bf16 x) { return __bfloat162float(x); }

@@ -25,8 +25,10 @@ struct GemmParams {
   int ldr;
   int res_mod;          // 0 = no modulo
   int dbg;              // bring-up knob (AHA_GEMM_DBG): 1 = return at entry, 2 = skip epilogue math/stores
+  int ring, ring_deep, ring_shallow;   // operand-ring stages actually used (0 = all the kernel variant has)
   float* ws_partial;    // split-K workspace: [tile][split][BN][128] fp32 partial tiles
   int* ws_counters;     // split-K arrival counter per tile (zero between launches)
+  unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
   L2Prefetch pf;        // weights of LATER kernels to request into L2 once this CTA's own loads are in flight
 };
 
@@ -57,6 +59,9 @@ struct GemmWorkspace {
 };
 
 int gemm_workspace_create(GemmWorkspace* w, int device);
+// Per-stream split scratch of the default workspace: 64 MB of fp32 partials and 2 x kCounters zeroed arrival counters
+// (the GEMM uses counters [0, kCounters), the attention merge [kCounters, 2 * kCounters)).
+int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out);
 void gemm_workspace_destroy(GemmWorkspace* w);
 // Enqueues the GEMM on `stream`. Returns AHA_OK or a negative error code.
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream);

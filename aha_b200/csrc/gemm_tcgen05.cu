@@ -62,16 +62,22 @@ struct Cfg {
 };
 
 // ---- epilogue math: fast approximations whose error is far below one bf16 step of the result ----
-__device__ __forceinline__ float fast_silu(float x) { return x * __frcp_rn(1.f + __expf(-x)); }
+// MUFU.RCP (about 1 ulp); __frcp_rn would add a branch and a slow-path call per element and serialise the epilogue
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_silu(float x) { return x * rcp_approx(1.f + __expf(-x)); }
 __device__ __forceinline__ float fast_gelu_tanh(float x) {
   const float u = 0.79788456080286535588f * (x + 0.044715f * x * x * x);
-  const float t = 1.f - 2.f * __frcp_rn(1.f + __expf(2.f * u));   // tanh(u)
+  const float t = 1.f - 2.f * rcp_approx(1.f + __expf(2.f * u));   // tanh(u)
   return 0.5f * x * (1.f + t);
 }
 __device__ __forceinline__ float fast_gelu_erf(float x) {
   // erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7)
   const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __frcp_rn(1.f + 0.3275911f * z);
+  const float t = rcp_approx(1.f + 0.3275911f * z);
   const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
   const float e = 1.f - poly * __expf(-z * z);
   return 0.5f * x * (1.f + copysignf(e, x));
@@ -135,6 +141,64 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
     for (int t = 0; t < 16; ++t)
       if (t < ntok) o[(size_t)t * p.ldo] = f2b(acc[t]);
   }
+}
+
+// Skinny orientation, staged form of the above for bf16 outputs of a fully valid 128-feature tile: the warp's
+// [16 tokens][32 features] block (16 features after SiLU*mul) goes through a small shared-memory tile so that it
+// leaves as 16-byte pieces - 8x fewer global memory instructions than the 2-byte per-token stores, the residual is
+// read the same way.  Same arithmetic and rounding order as epi_swap16.
+template <int kAct>
+__device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* stage_warp, int a0, int ew, int lane,
+                                                  float bias, int tok0, float (&acc)[16]) {
+  constexpr int kFeat = (kAct == GEMM_ACT_SILU_MUL) ? 16 : 32;
+  constexpr int kPitch = kFeat * 2 + 16;
+  constexpr int kPieces = kFeat / 8;            // 16-byte pieces per token
+#pragma unroll
+  for (int t = 0; t < 16; ++t) acc[t] = bf16r(acc[t] + bias);
+  if (kAct == GEMM_ACT_SILU_MUL) {
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      const float up = __shfl_down_sync(0xffffffffu, acc[t], 1);
+      const float x = bf16r(fast_silu(acc[t])) * up;
+      if ((lane & 1) == 0) *reinterpret_cast<bf16*>(stage_warp + t * kPitch + (lane >> 1) * 2) = f2b(x);
+    }
+  } else {
+#pragma unroll
+    for (int t = 0; t < 16; ++t) *reinterpret_cast<bf16*>(stage_warp + t * kPitch + lane * 2) = f2b(acc[t]);
+  }
+  __syncwarp();
+  const int ntok = min(16, p.Nb - tok0);
+  const int fbase = (kAct == GEMM_ACT_SILU_MUL) ? (a0 >> 1) + ew * 16 : a0 + ew * 32;
+  bf16* out = reinterpret_cast<bf16*>(p.out);
+#pragma unroll
+  for (int idx = lane; idx < 16 * kPieces; idx += 32) {
+    const int t = idx / kPieces, pc = idx % kPieces;
+    if (t < ntok) {
+      uint4 u = *reinterpret_cast<const uint4*>(stage_warp + t * kPitch + pc * 16);
+      const int token = tok0 + t, f = fbase + pc * 8;
+      if (p.residual) {
+        const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
+        const uint4 ru = *reinterpret_cast<const uint4*>(p.residual + (size_t)rrow * p.ldr + f);
+        uint32_t w[4] = {u.x, u.y, u.z, u.w};
+        const uint32_t rw[4] = {ru.x, ru.y, ru.z, ru.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 a = unpack_bf16x2(w[e]), b = unpack_bf16x2(rw[e]);
+          w[e] = pack_bf16x2(b.x + a.x, b.y + a.y);
+        }
+        u = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      st_v4(out + (size_t)token * p.ldo + f, u);
+    }
+  }
+  __syncwarp();
+}
+
+// the staged skinny epilogue needs a fully valid feature tile and 16-byte aligned bf16 rows
+__device__ __forceinline__ bool swap_staged_ok(const GemmParams& p, int a0) {
+  if (p.out_f32 || a0 + kBlockM > p.Ma || (p.ldo & 7) || (reinterpret_cast<uintptr_t>(p.out) & 15)) return false;
+  if (p.residual && ((p.ldr & 7) || (reinterpret_cast<uintptr_t>(p.residual) & 15))) return false;
+  return true;
 }
 
 // Tall orientation, direct form: 16 consecutive features of one token row (thread = token).  Used by the split-K merge
@@ -316,10 +380,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
   const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
   if (p.dbg == 1) return;
+  unsigned long long* ts = (p.dbg_ts && threadIdx.x == 128 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg_ts : nullptr;
+  dbg_stamp(ts, 0);
 
   // The weight operand (A when skinny, B when tall) does not depend on any earlier kernel: its first ring of tiles is
   // requested before griddepcontrol.wait, i.e. while the previous kernel on the stream may still be running (PDL).
-  const int pre = min(C::kStages, num_kb);
+  const int nst = (p.ring > 0 && p.ring < C::kStages) ? p.ring : C::kStages;   // stages actually used (bytes in flight)
+  const int pre = min(nst, num_kb);
   const uint64_t pol_a = kSwap ? l2_policy_evict_first() : l2_policy_evict_last();
   const uint64_t pol_b = kSwap ? l2_policy_evict_last() : l2_policy_evict_first();
   if (warp == 0 && lane == 0) {
@@ -355,8 +422,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         else tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], kc, a0, pol_a);
       }
       for (int kb = pre; kb < num_kb; ++kb) {
-        const int s = kb % C::kStages;
-        const uint32_t ph = (kb / C::kStages) & 1;
+        const int s = kb % nst;
+        const uint32_t ph = (kb / nst) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         mbar_arrive_expect_tx(&full_bar[s], C::kStageBytes);
         const int kc = (kb_begin + kb) * kBlockK;
@@ -373,8 +440,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, BN);
       for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % C::kStages;
-        const uint32_t ph = (kb / C::kStages) & 1;
+        const int s = kb % nst;
+        const uint32_t ph = (kb / nst) & 1;
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + s * C::kABytes));
@@ -392,9 +459,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 =====
     const int ew = warp & 3;
     const int i = ew * 32 + lane;  // tile row
+    dbg_stamp(ts, 1);
     pdl_wait();   // the epilogue reads residuals and writes outputs that earlier kernels may still be using
+    dbg_stamp(ts, 2);
     mbar_wait(accum_bar, 0);
     tc_fence_after();
+    dbg_stamp(ts, 3);
     const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
     if (p.dbg == 2) {
     } else if (p.splits == 1) {
@@ -402,16 +472,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const int feat = a0 + i;
         const bool fvalid = feat < p.Ma;
         const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
+        const bool staged = swap_staged_ok(p, a0);
+        // the operand ring is idle by now (accum_bar fired after the last MMA read it): 2 KB of it per warp stage the stores
+        uint8_t* stage_warp = smem + ew * 2048;
 #pragma unroll 1
         for (int jc = 0; jc < BN; jc += 16) {
           if (b0 + jc >= p.Nb) break;
           uint32_t r[16];
           tmem_ld_32x32b_x16(taddr + jc, r);
           tmem_ld_wait();
+          dbg_stamp(ts, 8 + (jc >> 4) * 2);
           float acc[16];
 #pragma unroll
           for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
-          epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+          if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
+          else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+          dbg_stamp(ts, 9 + (jc >> 4) * 2);
         }
       } else if (p.out_f32) {
 #pragma unroll 1
@@ -442,6 +518,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
         for (int t = 0; t < 16; ++t) __stcg(part + (jc + t) * kBlockM, __uint_as_float(r[t]));
       }
+      dbg_stamp(ts, 4);
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
       int* cnt = p.ws_counters + 2 * tile_lin;
@@ -456,11 +533,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       __threadfence();
+      dbg_stamp(ts, 5);
       // 16-column chunk c is reduced (in split order 0..s-1: deterministic) and finished by split (c mod splits)
       const float* base = p.ws_partial + (size_t)tile_lin * p.splits * (size_t)(BN * kBlockM) + i;
       const int feat = a0 + i;
       const bool fvalid = feat < p.Ma;
       const float bias = (kSwap && p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
+      const bool staged = kSwap && swap_staged_ok(p, a0);
 #pragma unroll 1
       for (int jc = split * 16; jc < ncols; jc += 16 * p.splits) {
         float acc[16];
@@ -482,6 +561,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       if (threadIdx.x == 128 && atomicAdd(cnt + 1, 1) == p.splits - 1) { cnt[0] = 0; cnt[1] = 0; }   // last one out re-arms
     }
     tc_fence_before();
+    dbg_stamp(ts, 6);
   }
 
   __syncthreads();
@@ -489,6 +569,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     tc_fence_after();
     tmem_dealloc<C::kTmemCols>(tmem_base);
   }
+  dbg_stamp(ts, 7);
 }
 
 }  // namespace
@@ -641,6 +722,27 @@ int dispatch(int bn, int swap, int deep, int act, const CUtensorMap& ta, const C
 }
 }  // namespace
 
+// ---- bring-up: phase stamps (SM cycles) of CTA (0,0,0) of the most recent launch of each (grid.x, grid.z) class ----
+static unsigned long long* g_gemm_ts = nullptr;   // [64 slots][8]
+static std::map<std::pair<int, int>, int> g_gemm_ts_slot;
+static unsigned long long* gemm_ts_slot(dim3 grid) {
+  static const bool want = getenv("AHA_TS") && atoi(getenv("AHA_TS")) == 1;
+  if (!want) return nullptr;
+  if (!g_gemm_ts) { if (cudaMalloc(&g_gemm_ts, 64 * 16 * 8) != cudaSuccess) return nullptr; cudaMemset(g_gemm_ts, 0, 64 * 8 * 8); }
+  auto key = std::make_pair((int)grid.x, (int)grid.z);
+  auto it = g_gemm_ts_slot.find(key);
+  if (it == g_gemm_ts_slot.end()) { if (g_gemm_ts_slot.size() >= 64) return nullptr; it = g_gemm_ts_slot.emplace(key, (int)g_gemm_ts_slot.size()).first; }
+  return g_gemm_ts + it->second * 16;
+}
+extern "C" int aha_debug_gemm_timeline(int* n_out, int* grid_x, int* grid_z, unsigned long long* out /*[64*16]*/) {
+  if (!g_gemm_ts) { aha_set_error("ValueError: run with AHA_TS=1"); return AHA_ERR_VALUE; }
+  AHA_CUDA(cudaDeviceSynchronize());
+  AHA_CUDA(cudaMemcpy(out, g_gemm_ts, 64 * 16 * 8, cudaMemcpyDeviceToHost));
+  *n_out = (int)g_gemm_ts_slot.size();
+  for (auto& kv : g_gemm_ts_slot) { grid_x[kv.second] = kv.first.first; grid_z[kv.second] = kv.first.second; }
+  return AHA_OK;
+}
+
 int gemm_workspace_create(GemmWorkspace* w, int device) {
   cudaDeviceProp prop;
   AHA_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -659,11 +761,22 @@ static int split_scratch(GemmWorkspace* w, cudaStream_t st, GemmSplitScratch* ou
   if (it == w->scratch.end()) {
     GemmSplitScratch s;
     AHA_CUDA(cudaMalloc(&s.partial, GemmWorkspace::kPartialBytes));
-    AHA_CUDA(cudaMalloc(&s.counters, 2 * GemmWorkspace::kCounters * sizeof(int)));
-    AHA_CUDA(cudaMemsetAsync(s.counters, 0, 2 * GemmWorkspace::kCounters * sizeof(int), st));
+    AHA_CUDA(cudaMalloc(&s.counters, 4 * GemmWorkspace::kCounters * sizeof(int)));
+    AHA_CUDA(cudaMemsetAsync(s.counters, 0, 4 * GemmWorkspace::kCounters * sizeof(int), st));
     it = w->scratch.emplace(st, s).first;
   }
   *out = it->second;
+  return AHA_OK;
+}
+
+GemmWorkspace* aha_default_workspace(int* rc_out);
+int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out) {
+  int rc;
+  GemmWorkspace* w = aha_default_workspace(&rc);
+  if (!w) return rc;
+  rc = split_scratch(w, st, out);
+  if (rc) return rc;
+  out->counters += 2 * GemmWorkspace::kCounters;
   return AHA_OK;
 }
 
@@ -727,6 +840,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   splits = (kb_total + kb_per - 1) / kb_per;  // no empty splits
   p.splits = splits; p.kb_per_split = kb_per;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("AHA_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
+  { static int ring = -1, ring2 = -1;
+    if (ring < 0) { const char* e = getenv("AHA_GEMM_RING"); ring = e ? atoi(e) : 0; e = getenv("AHA_GEMM_RING2"); ring2 = e ? atoi(e) : 0; }
+    p.ring = 0; p.ring_deep = ring; p.ring_shallow = ring2; }
   AHA_REQUIRE(splits <= 16, "split-K factor above 16");
   // the splits of a tile wait for each other: the whole grid has to fit the device at once
   while (splits > 1 && ((long)tiles * splits > (long)w->sm_count * (bn <= 128 ? 2 : 1) ||
@@ -746,9 +862,11 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
   dim3 grid(tiles_a, tiles_b, splits);
+  p.dbg_ts = gemm_ts_slot(grid);
   if (deep < 0) deep = (swap && (long)tiles * splits <= w->sm_count) ? 1 : 0;   // <= one CTA per SM: give it the whole SM
   if (deep && splits > 1 && (long)tiles * splits > w->sm_count) deep = 0;       // split CTAs must stay co-resident
   ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);
+  p.ring = swap ? (deep ? p.ring_deep : p.ring_shallow) : 0;
   rc = dispatch(bn, swap, deep, c.act, ta, tb, p, grid, stream);
   if (slot) {
     const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * (c.out_f32 ? 4 : 2);

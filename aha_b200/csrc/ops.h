@@ -52,6 +52,9 @@ struct AttnProblem {
   float scale;
   bf16* out; int out_ld;    // out[token, (block*group + r) * d + c]
   L2Prefetch pf;            // weights of later kernels to request into L2 (common.cuh)
+  unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
+  float* ws_partial;        // key-split scratch (filled in by op_attention): per CTA [128][d_pad] fp32 O, then m[128], l[128]
+  int* ws_counters;         // arrival / departure counter pair per (segment, block, query tile)
   int pf_early;             // 1: request them at kernel entry, 0: after this CTA's own K/V loads are in flight
   int n_segs;
   AttnSeg segs[32];

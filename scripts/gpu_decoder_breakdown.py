@@ -24,3 +24,22 @@ for _ in range(n):
 e1.record(); torch.cuda.synchronize()
 print(json.dumps(dict(skip=os.environ.get("AHA_SKIP", "0"), pdl=os.environ.get("AHA_PDL", "1"),
                       ms_per_frame=e0.elapsed_time(e1) / n)))
+
+if os.environ.get("AHA_TS") == "1":
+    import ctypes
+    lib = A._lib.load()
+    GHZ = 1.965
+    a = (ctypes.c_ulonglong * 16)()
+    A._lib.check(lib.aha_debug_attention_timeline(a))
+    t = list(a)
+    names = ["entry", "setup", "pdl_wait", "S0 ready", "P0 written", "S1 ready", "P1 written", "O done", "O parked",
+             "cluster.sync", "merged", "cluster.sync2", "exit"]
+    print("attention CTA(0,0,0) us since entry:", {n: round((x - t[0]) / GHZ / 1e3, 2) for n, x in zip(names, t) if x})
+    n, gx, gz = ctypes.c_int(), (ctypes.c_int * 64)(), (ctypes.c_int * 64)()
+    out = (ctypes.c_ulonglong * 1024)()
+    A._lib.check(lib.aha_debug_gemm_timeline(ctypes.byref(n), gx, gz, out))
+    gn = ["entry", "pre-wait", "pdl_wait", "accum done", "partial parked", "all arrived", "epilogue done", "exit",
+          "c0 ld", "c0 end", "c1 ld", "c1 end", "c2 ld", "c2 end", "c3 ld", "c3 end"]
+    for i in range(n.value):
+        t = list(out[i * 16:(i + 1) * 16])
+        print(f"gemm grid.x={gx[i]} splits={gz[i]} us since entry:", {k: round((x - t[0]) / GHZ / 1e3, 2) for k, x in zip(gn, t) if x})
