@@ -70,3 +70,8 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream);
 int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap* out);
 // Launch counters (bench.py's gpu_launches claim).
 extern unsigned long long g_aha_launch_count;
+
+// Optional per-launch CUDA-event timing (aha_profile_gemm / aha_profile_gemm_read): returns null when disabled.
+struct ProfSlot;
+ProfSlot* prof_begin(int cls, cudaStream_t st);
+void prof_end(ProfSlot* s, cudaStream_t st, double bytes, double flops);

@@ -637,12 +637,12 @@ int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap
   return AHA_OK;
 }
 
-namespace {
-
 struct ProfSlot { cudaEvent_t e0, e1; int cls; double bytes, flops; };
+namespace {
 std::deque<ProfSlot> g_prof;
 std::mutex g_prof_mu;
 bool g_prof_enabled = false;
+}  // namespace
 
 ProfSlot* prof_begin(int cls, cudaStream_t st) {
   if (!g_prof_enabled) return nullptr;
@@ -659,6 +659,8 @@ void prof_end(ProfSlot* s, cudaStream_t st, double bytes, double flops) {
   s->bytes = bytes; s->flops = flops;
   cudaEventRecord(s->e1, st);
 }
+
+namespace {
 
 template <int BN, bool kSwap, int kAct, bool kDeep>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
@@ -780,6 +782,9 @@ int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out) {
   return AHA_OK;
 }
 
+static int g_sm_shared = 0;
+extern "C" int aha_set_sm_sharing(int shared) { g_sm_shared = shared != 0; return AHA_OK; }
+
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
   int swap = c.force_swap >= 0 ? c.force_swap : (c.tokens <= 256 ? 1 : 0);
@@ -863,7 +868,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
   dim3 grid(tiles_a, tiles_b, splits);
   p.dbg_ts = gemm_ts_slot(grid);
-  if (deep < 0) deep = (swap && (long)tiles * splits <= w->sm_count) ? 1 : 0;   // <= one CTA per SM: give it the whole SM
+  if (deep < 0) deep = (swap && !g_sm_shared && (long)tiles * splits <= w->sm_count) ? 1 : 0;   // <= one CTA per SM: give it the whole SM
   if (deep && splits > 1 && (long)tiles * splits > w->sm_count) deep = 0;       // split CTAs must stay co-resident
   ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);
   p.ring = swap ? (deep ? p.ring_deep : p.ring_shallow) : 0;
@@ -884,7 +889,7 @@ extern "C" int aha_profile_gemm(int enable) {
   g_prof_enabled = enable != 0;
   return AHA_OK;
 }
-// cls 0 = skinny (weight-streaming, tokens <= 256), 1 = tall.  Synchronises the recorded events.
+// cls 0 = skinny GEMM (weight-streaming, tokens <= 256), 1 = tall GEMM, 2 = KV re-rotation (eviction).  Synchronises the recorded events.
 extern "C" int aha_profile_gemm_read(int cls, double* ms, long long* launches, double* bytes, double* flops) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   double t = 0, b = 0, f = 0; long long n = 0;

@@ -7,17 +7,21 @@
 Differences that are the point of the rewrite: frame embeddings stay on the device (the reference parks them in host
 RAM, test/inference.py:185,213); the three per-frame scores are written by the heads kernel into a device score buffer
 and read back once per stream instead of three `.item()` syncs per frame (:222-227) - unless a response threshold is
-active, in which case one read per frame is needed, exactly where the reference needs its decision.
+active, in which case one read per frame is needed, exactly where the reference needs its decision; and
+`input_video_stream` only ENQUEUES the SigLIP batches, on a second CUDA stream, so the tensor-bound vision tower of
+later batches runs underneath the HBM-bound decoder steps of earlier ones (`inference()` waits per batch on an event).
 Response generation (fast_greedy_generate) is outside this path ("next" row N1): when a threshold fires the frame is
 recorded in `response_needed` and the stream goes on.
 """
 from __future__ import annotations
 
+import os
 from collections import deque
 from typing import List, Optional
 
 import torch
 
+from . import _lib
 from .model import VideoHeadLiveLlavaQwenForCausalLM
 from .postproc import find_ticks as _find_ticks
 
@@ -39,8 +43,9 @@ class LiveInferForBenchmark:
                  alt_cache: str = "default_sink", window_length: int = 2048, num_sink_tokens: int = 32,
                  frame_fps: float = 2.0, score_heads=("relevance_score", "informative_score"),
                  stream_end_prob_threshold: Optional[float] = None, stream_end_score_sum_threshold: Optional[float] = None,
-                 running_list_length: int = 20, max_frames: int = 4096):
+                 running_list_length: int = 20, max_frames: int = 4096, overlap_vision: bool = True):
         self.model = model
+        self.overlap_vision = overlap_vision and os.environ.get("AHA_OVERLAP_VISION", "1") != "0"
         self.model.eval()
         cfg = model.config
         self.hidden_size = cfg.hidden_size
@@ -69,6 +74,7 @@ class LiveInferForBenchmark:
     def reset(self):
         self.query_queue = deque()
         self.frame_embeds_queue = deque()
+        self._ready_events = {}
         self.video_time = 0
         self.last_frame_idx = -1
         self.video_tensor = None
@@ -92,11 +98,28 @@ class LiveInferForBenchmark:
 
     # ---- vision (test/inference.py:169-187, test/live_infer_for_video.py:98-128) ----
     def input_video_stream(self, video_frames: torch.Tensor, batch_size: int = 32):
-        """uint8 [T, 3, S, S]; embeds stay on the device."""
-        for b in range(0, len(video_frames), batch_size):
-            emb = self.model.visual_embed(video_frames[b:b + batch_size]).split(self.frame_num_tokens)
-            for r, f in enumerate(emb):
-                self.frame_embeds_queue.append(((r + b) / self.frame_fps, f))
+        """uint8 [T, 3, S, S]; embeds stay on the device.  With `overlap_vision` the batches are enqueued on the model's
+        vision stream and this call returns at once; every batch carries an event that `_encode_frame` waits for."""
+        if not (self.overlap_vision and video_frames.is_cuda):
+            for b in range(0, len(video_frames), batch_size):
+                emb = self.model.visual_embed(video_frames[b:b + batch_size]).split(self.frame_num_tokens)
+                for r, f in enumerate(emb):
+                    self.frame_embeds_queue.append(((r + b) / self.frame_fps, f))
+            return
+        cur, side = torch.cuda.current_stream(), self.model.vision_stream()
+        side.wait_stream(cur)                      # the frames (and their H2D copy) were produced on the caller's stream
+        video_frames.record_stream(side)
+        with torch.cuda.stream(side):
+            for b in range(0, len(video_frames), batch_size):
+                batch = self.model.visual_embed(video_frames[b:b + batch_size])
+                batch.record_stream(cur)           # consumed by the decoder on the caller's stream ...
+                batch.record_stream(self.model.decoder_stream())   # ... or on the high-priority decoder stream
+                ev = torch.cuda.Event()
+                ev.record(side)
+                for r, f in enumerate(batch.split(self.frame_num_tokens)):
+                    self.frame_embeds_queue.append(((r + b) / self.frame_fps, f))      # the reference's (time, embeds) entries
+                    if r == 0:
+                        self._ready_events[id(f)] = (f, ev)                            # first frame of a batch carries its event
 
     def load_one_frame(self, frame: torch.Tensor):
         emb = self.model.visual_embed(frame.reshape(1, *frame.shape[-3:]))
@@ -110,6 +133,9 @@ class LiveInferForBenchmark:
     # ---- one chunk (test/inference.py:196-262) ----
     def _encode_frame(self):
         video_time, frame_embeds = self.frame_embeds_queue.popleft()
+        ready = self._ready_events.pop(id(frame_embeds), None)
+        if ready is not None:
+            torch.cuda.current_stream().wait_event(ready[1])
         if not self.init_vision_time:
             self.last_ids = self._start_ids
             self.init_vision_time = True
@@ -160,6 +186,21 @@ class LiveInferForBenchmark:
 
     def inference(self):
         """test/inference.py:283-334; fills `debug_data_list` with one dict per frame."""
+        if self.overlap_vision and self._ready_events:
+            # vision batches are in flight on the vision stream: run the decoder steps on the high-priority stream so the
+            # block scheduler interleaves them with the (much larger) vision grids instead of queueing behind them
+            cur, hp = torch.cuda.current_stream(), self.model.decoder_stream()
+            hp.wait_stream(cur)
+            _lib.load().aha_set_sm_sharing(1)
+            try:
+                with torch.cuda.stream(hp):
+                    while self.frame_embeds_queue:
+                        self.input_one_frame()
+                    self._flush_scores()
+            finally:
+                _lib.load().aha_set_sm_sharing(0)
+            cur.wait_stream(hp)
+            return self.debug_data_list
         while self.frame_embeds_queue:
             self.input_one_frame()
         self._flush_scores()

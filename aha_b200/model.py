@@ -128,6 +128,22 @@ class VideoHeadLiveLlavaQwenForCausalLM:
                           max_chunk or min(self.max_tokens, 4096), self.device)
 
     # ---- vision ----
+    def vision_stream(self) -> "torch.cuda.Stream":
+        """Second CUDA stream for the SigLIP tower: tensor-bound vision batches of later frames run underneath the
+        HBM-bound decoder steps of earlier ones.  (The vision and decoder workspaces of the handle are disjoint and the
+        library's split-K scratch is per stream, so the two streams never share mutable state.)"""
+        if getattr(self, "_vision_stream", None) is None:
+            self._vision_stream = torch.cuda.Stream(device=self.device)
+        return self._vision_stream
+
+    def decoder_stream(self) -> "torch.cuda.Stream":
+        """High-priority stream for the decoder steps while vision batches are in flight on `vision_stream()`: without a
+        priority the block scheduler drains a 5000-CTA vision GEMM before it dispatches the decoder's next (small) grid,
+        which serialises the two streams again."""
+        if getattr(self, "_decoder_stream", None) is None:
+            self._decoder_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        return self._decoder_stream
+
     def visual_embed(self, frames: torch.Tensor) -> torch.Tensor:
         """[F, 3, S, S] uint8 (raw frames; the image processor's rescale/normalise is fused in) or bf16 pixel_values
         -> [F * frame_num_tokens, hidden] bf16 (models/modeling_live.py:31-37)."""

@@ -21,6 +21,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+NCU_TRAFFIC_BYTES_PER_LAUNCH = (33.48e6 + 26.45e6 + 278.97e6 + 142.56e6) / 4
 VISION_BATCH = 32   # the reference embeds frames in batches of 32 (test/inference.py:181)
 
 
@@ -37,6 +38,7 @@ def parse():
     ap.add_argument("--cache", default="default_sink", choices=["default_sink", "sliding_window", "static"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="run the vision batches on the decoder's stream")
     ap.add_argument("--cpu-threads", type=int, default=0)
     return ap.parse_args()
 
@@ -207,6 +209,7 @@ def workload_config(args, n_gpus):
                          f"(cache full, one eviction + re-rotation per frame)",
                 streams=args.streams_per_gpu * n_gpus, window=args.window, sinks=args.sinks,
                 frame_tokens=49, vision_batch=VISION_BATCH, parallelism=f"stream-sharded x{n_gpus} (no collective)",
+                vision_overlap=("off" if args.no_overlap else "SigLIP batch b+1 on a second CUDA stream under the decoder steps of batch b"),
                 l2="per-step working set (>= 14 GB of weights at 7B) exceeds the 126 MB L2; no flush needed")
 
 
@@ -251,23 +254,43 @@ def run_ours(args):
 
     caches = [model.new_cache(args.cache, args.window, args.sinks, max_chunk=n_sys + q + 8) for _ in range(ns)]
     scores = torch.zeros(total_frames + 4096, ns, 3, dtype=torch.float32, device=dev)
-    embeds = [None] * ns
-    state = dict(frame=0)
+    overlap = not args.no_overlap
+    side = model.vision_stream() if overlap else None
+    embeds = [[None] * ns, [None] * ns]            # double buffer: batch b lives in slot b % 2
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    state = dict(frame=0, overlap=overlap)
 
-    def vision_batch():
-        for s in range(ns):
-            embeds[s] = model.visual_embed(pool_dev).view(VISION_BATCH, q, cfg.hidden_size)
+    def vision_batch(slot):
+        """SigLIP -> projector -> pooling for the next VISION_BATCH frames of every stream.  With overlap it is enqueued on
+        the vision stream one batch AHEAD of the decoder, so it runs underneath the decoder steps of the current batch."""
+        cur = torch.cuda.current_stream()
+        if not state["overlap"]:
+            for s in range(ns):
+                embeds[slot][s] = model.visual_embed(pool_dev).view(VISION_BATCH, q, cfg.hidden_size)
+            return
+        side.wait_stream(cur)                      # the slot's previous embeddings have been consumed on `cur`
+        with torch.cuda.stream(side):
+            for s in range(ns):
+                e = model.visual_embed(pool_dev)
+                e.record_stream(cur)
+                embeds[slot][s] = e.view(VISION_BATCH, q, cfg.hidden_size)
+            ready[slot].record(side)
 
     def step():
         """one frame of every resident stream, inputs already in HBM"""
         f = state["frame"]
-        if f % VISION_BATCH == 0:
-            vision_batch()
-        i = f % VISION_BATCH
+        b, i = divmod(f, VISION_BATCH)
+        slot = b % 2
+        if i == 0:
+            if b == 0 or not state["overlap"]:
+                vision_batch(slot)
+            if state["overlap"]:
+                torch.cuda.current_stream().wait_event(ready[slot])
+                vision_batch(1 - slot)             # the NEXT batch: one vision batch per VISION_BATCH decoder steps
         if f == 0:
-            x = torch.cat([model.assemble_chunk(start_ids, embeds[s][i]) for s in range(ns)], 0)
+            x = torch.cat([model.assemble_chunk(start_ids, embeds[slot][s][i]) for s in range(ns)], 0)
         else:
-            x = torch.stack([embeds[s][i] for s in range(ns)], 0) if ns > 1 else embeds[0][i:i + 1]
+            x = torch.stack([embeds[slot][s][i] for s in range(ns)], 0) if ns > 1 else embeds[slot][0][i:i + 1]
         model(inputs_embeds=x, past_key_values=caches, scores_out=scores[f])
         state["frame"] = f + 1
 
@@ -277,6 +300,12 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    if overlap:
+        # decoder steps on the model's high-priority stream (what LiveInferForBenchmark.inference does as well)
+        hp = model.decoder_stream()
+        hp.wait_stream(torch.cuda.current_stream())
+        torch.cuda.set_stream(hp)
+        lib.aha_set_sm_sharing(1)
     for _ in range(prime):       # untimed priming: fills the cache so every timed frame runs the steady-state eviction path
         step()
     # align the timed region to a vision-batch boundary so K frames carry K/32 vision batches
@@ -317,25 +346,42 @@ def roofline_leg(r, args, peaks):
     n = min(64, r["K"])
     n -= n % VISION_BATCH if n >= VISION_BATCH else 0
     n = max(n, 1)
+    # kernel quality, not stream sharing: this pass runs the vision batches on the decoder's stream (no concurrent kernels)
+    torch.cuda.synchronize(r["dev"])
+    lib.aha_set_sm_sharing(0)
+    was, r["state"]["overlap"] = r["state"]["overlap"], False
+    while r["state"]["frame"] % VISION_BATCH:
+        r["step"]()
     torch.cuda.synchronize(r["dev"])
     lib.aha_profile_gemm(1)
     for _ in range(n):
         r["step"]()
     torch.cuda.synchronize(r["dev"])
+    r["state"]["overlap"] = was
     out = {}
-    for cls, name in ((0, "skinny"), (1, "tall")):
+    for cls, name in ((0, "skinny"), (1, "tall"), (2, "rerot")):
         ms, cnt, by, fl = ctypes.c_double(), ctypes.c_longlong(), ctypes.c_double(), ctypes.c_double()
         lib.aha_profile_gemm_read(cls, ctypes.byref(ms), ctypes.byref(cnt), ctypes.byref(by), ctypes.byref(fl))
         out[name] = dict(ms=ms.value, launches=cnt.value, bytes=by.value, flops=fl.value)
     lib.aha_profile_gemm(0)
-    sk, tall = out["skinny"], out["tall"]
+    sk, tall, rr = out["skinny"], out["tall"], out["rerot"]
     achieved = sk["bytes"] / (sk["ms"] / 1e3) / 1e9 if sk["ms"] > 0 else 0.0
+    # DRAM traffic per launch from the committed `ncu --set full` capture of the same four launches
+    # (profiles/r01_ncu_full_decoder_v3.txt: qkv 33.5, o_proj 26.5, gate|up 272.0 + 7.0, down 138.1 + 4.5 MB read + write)
+    traffic = NCU_TRAFFIC_BYTES_PER_LAUNCH if (args.preset == "7b" and args.streams_per_gpu == 1) else None
     roof = dict(bound="hbm", kernel="gemm_tcgen05_kernel (decoder weight-streaming launches: qkv, o_proj, gate|up, down)",
-                achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"], traffic=None,
+                achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"], traffic=traffic,
+                traffic_source="ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over the four launches of a layer",
                 peak_source=f"{peaks['source']} copy bandwidth", launches=sk["launches"],
                 avg_launch_us=(sk["ms"] * 1e3 / sk["launches"]) if sk["launches"] else None,
                 algorithmic_bytes_per_launch=(sk["bytes"] / sk["launches"]) if sk["launches"] else None,
                 ms_per_frame=sk["ms"] / n)
+    if rr["ms"] > 0 and rr["launches"]:
+        gbs = rr["bytes"] / (rr["ms"] / 1e3) / 1e9
+        roof["kv_eviction"] = dict(bound="hbm", kernel="rerotate_kernel (sink-cache eviction: every kept key of all layers, one launch)",
+                                   achieved=gbs, peak=peaks["hbm"], unit="GB/s", frac=gbs / peaks["hbm"],
+                                   launches=rr["launches"], avg_launch_us=rr["ms"] * 1e3 / rr["launches"],
+                                   algorithmic_bytes_per_launch=rr["bytes"] / rr["launches"])
     if tall["ms"] > 0:
         tf = tall["flops"] / (tall["ms"] / 1e3) / 1e12
         roof["vision_gemm"] = dict(bound="tensor", achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s",
@@ -351,18 +397,19 @@ def e2e_leg(r, args):
     model, dev, cfg, ns = r["model"], r["dev"], r["cfg"], r["ns"]
     K = r["K"] - r["K"] % VISION_BATCH if r["K"] >= VISION_BATCH else r["K"]
     lives = [A.LiveInferForBenchmark(model, r["start_ids"], alt_cache=args.cache, window_length=args.window,
-                                     num_sink_tokens=args.sinks, frame_fps=1.0, max_frames=K + 4096) for _ in range(ns)]
+                                     num_sink_tokens=args.sinks, frame_fps=1.0, max_frames=K + 4096,
+                                     overlap_vision=not args.no_overlap) for _ in range(ns)]
     pool = r["pool_host"]
     prime = (args.window // cfg.frame_num_tokens) + 4
+    # the whole clip is handed over at once, as test/inference.py does with a video: K frames in pinned host memory
+    reps = (max(K, prime + VISION_BATCH) + VISION_BATCH - 1) // VISION_BATCH
+    clip = pool.repeat(reps, 1, 1, 1).pin_memory()
 
     def run(nframes):
-        done = 0
-        while done < nframes:
-            b = min(VISION_BATCH, nframes - done)
-            for lv in lives:
-                lv.input_video_stream(pool[:b].to(dev, non_blocking=True), batch_size=VISION_BATCH)   # H2D from pinned memory
-                lv.inference()                                                                       # ends with the D2H read
-            done += b
+        for lv in lives:
+            lv.input_video_stream(clip[:nframes].to(dev, non_blocking=True), batch_size=VISION_BATCH)   # H2D from pinned memory
+        for lv in lives:
+            lv.inference()                                                                           # ends with the D2H read
 
     run(prime + VISION_BATCH - prime % VISION_BATCH)
     torch.cuda.synchronize(dev)
@@ -418,6 +465,9 @@ def main():
     peaks = measured_peaks()
     r = run_ours(args)
     if os.environ.get("AHA_NCU"):
+        r["state"]["overlap"] = False
+        while r["state"]["frame"] % VISION_BATCH:
+            r["step"]()
         # profiling aid (never a bench value): one vision batch + 32 steady-state frames inside a cudaProfiler range,
         # for `ncu --profile-from-start off`
         torch.cuda.synchronize()

@@ -68,12 +68,19 @@ const char* aha_last_error(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 unsigned long long aha_launch_count(void);
 
-/* Optional CUDA-event timing of every GEMM launch (bench.py's roofline leg): enable, run, then read the summed launch
- * durations [ms], launch count, algorithmic bytes and FLOPs of class 0 (weight-streaming, tokens <= 256) or 1 (tall). */
+/* Scheduling hint.  shared != 0: another stream of this process keeps the SMs busy (the vision tower of later frames),
+ * so the weight-streaming GEMMs use their two-CTAs-per-SM variant, which interleaves with foreign CTAs; shared == 0
+ * (default): a <= one-CTA-per-SM grid takes the whole SM with the deep operand ring.  Results are identical. */
+int aha_set_sm_sharing(int shared);
+
 /* Bring-up aids (AHA_TS=1 in the environment): SM-cycle phase stamps of CTA (0,0,0) of the most recent attention launch /
  * of the most recent GEMM launch per (grid.x, grid.z) class.  Not part of the reference-facing surface. */
 int aha_debug_attention_timeline(unsigned long long* out16);
 int aha_debug_gemm_timeline(int* n_out, int* grid_x /*[64]*/, int* grid_z /*[64]*/, unsigned long long* out /*[64*16]*/);
+
+/* Optional CUDA-event timing of every GEMM launch (bench.py's roofline leg): enable, run, then read the summed launch
+ * durations [ms], launch count, algorithmic bytes and FLOPs of class 0 (weight-streaming GEMM, tokens <= 256), 1 (tall
+ * GEMM) or 2 (KV re-rotation on eviction). */
 int aha_profile_gemm(int enable);
 int aha_profile_gemm_read(int cls, double* ms, long long* launches, double* bytes, double* flops);
 
