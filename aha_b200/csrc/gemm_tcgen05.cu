@@ -260,7 +260,7 @@ __device__ __forceinline__ void epi_tall16(const GemmParams& p, int token, int f
 // segments of the output (and of the residual it adds): fully coalesced HBM traffic.
 template <int BN, int kAct>
 __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t taddr, uint8_t* stage_warp, int a0, int b0,
-                                                int ew, int lane) {
+                                                int ew, int lane, uint64_t* release_bar = nullptr) {
   constexpr int kPitch = BN * 2 + 16;
   constexpr int kOutCols = (kAct == GEMM_ACT_SILU_MUL) ? BN / 2 : BN;    // SiLU*mul halves the feature count
   uint8_t* my = stage_warp + lane * kPitch;
@@ -307,6 +307,11 @@ __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t ta
       for (int c = 0; c < 4; ++c)
         *reinterpret_cast<uint4*>(my + jc * 2 + c * 16) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
     }
+  }
+  if (release_bar) {   // persistent kernel: the accumulator buffer is free again as soon as it has been read
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(release_bar);
   }
   __syncwarp();
   constexpr int kChunksPerRow = kOutCols / 8;
@@ -572,6 +577,129 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   dbg_stamp(ts, 7);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Persistent tall GEMM (tokens >> 256: the SigLIP tower and the projector).  One CTA per SM walks over 128 x BN output
+// tiles (n fastest, so the CTAs in flight share a few activation row blocks and the whole weight matrix in L2):
+//   * the TMA producer and the MMA issuer run ahead across tile boundaries - the operand ring never drains,
+//   * two accumulator buffers in TMEM (2 x BN columns): the epilogue warps drain tile t while tile t+1 is being
+//     multiplied, so bias / GELU / residual / stores cost no tensor-pipe time,
+//   * a 128 x 256 tile reads 48 KB of shared memory per 512 tensor-pipe cycles (96 B/clk) where the 128 x 128 tiles of
+//     the one-shot kernel sit exactly at the 128 B/clk shared-memory limit.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int BN>
+struct PCfg {
+  static constexpr int kStages = 3;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBBytes = BN * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  // BN = 128 is the variant that shares the SM with a weight-streaming decoder CTA of another stream: 256 TMEM columns,
+  // ~115 KB of shared memory (its epilogue stages 64 columns at a time)
+  static constexpr int kEpiBN = (BN == 128) ? 64 : BN;
+  static constexpr int kEpiWarpBytes = 32 * (kEpiBN * 2 + 16);
+  static constexpr int kTmemCols = (BN <= 128) ? 256 : 512;   // two accumulators of BN columns, power of two
+  static constexpr int kSmemBytes = kStages * kStageBytes + 4 * kEpiWarpBytes + 1024 + 256;
+};
+
+template <int BN, int kAct>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                            const GemmParams p, const int tiles_m, const int tiles_n) {
+  using C = PCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + C::kStages * C::kABytes;
+  uint8_t* smem_epi = smem + C::kStages * C::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_epi + 4 * C::kEpiWarpBytes);
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tmem_full = empty_bar + C::kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;             // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  const int n_tiles = tiles_m * tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();   // activations, residuals and the output buffer belong to earlier kernels until here
+
+  if (warp == 0) {
+    // ===== TMA producer: one continuous stream of k-blocks over all tiles of this CTA =====
+    if (lane == 0) {
+      const uint64_t pol_a = l2_policy_evict_first(), pol_b = l2_policy_evict_last();
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int a0 = (t / tiles_n) * kBlockM, b0 = (t % tiles_n) * BN;
+        for (int kb = 0; kb < kb_total; ++kb, ++it) {
+          const int s = it % C::kStages;
+          mbar_wait(&empty_bar[s], ((it / C::kStages) & 1) ^ 1);
+          mbar_arrive_expect_tx(&full_bar[s], C::kStageBytes);
+          tma_load_2d_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kb * kBlockK, a0, pol_a);
+          tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, b0, pol_b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, BN);
+      uint32_t it = 0, tl = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+        const uint32_t buf = tl & 1;
+        mbar_wait(&tmem_empty[buf], ((tl >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * BN;
+        for (int kb = 0; kb < kb_total; ++kb, ++it) {
+          const int s = it % C::kStages;
+          mbar_wait(&full_bar[s], (it / C::kStages) & 1);
+          tc_fence_after();
+          const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + s * C::kABytes));
+          const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + s * C::kBBytes));
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma_f16_ss(tacc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          umma_commit(&empty_bar[s]);
+        }
+        umma_commit(&tmem_full[buf]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 of both accumulators =====
+    const int ew = warp & 3;
+    uint32_t tl = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+      const int a0 = (t / tiles_n) * kBlockM, b0 = (t % tiles_n) * BN;
+      const uint32_t buf = tl & 1;
+      mbar_wait(&tmem_full[buf], (tl >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(ew * 32) << 16);
+#pragma unroll 1
+      for (int h = 0; h < BN; h += C::kEpiBN)
+        epi_tall_staged<C::kEpiBN, kAct>(p, taddr + h, smem_epi + ew * C::kEpiWarpBytes, a0, b0 + h, ew, lane,
+                                         (h + C::kEpiBN >= BN) ? &tmem_empty[buf] : nullptr);
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // =====================================================================================
@@ -668,6 +796,7 @@ int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
   static bool attr_done = false;
   if (!attr_done) {
     AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct, kDeep>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct, kDeep>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
@@ -720,6 +849,43 @@ int dispatch(int bn, int swap, int deep, int act, const CUtensorMap& ta, const C
     case 64: return dispatch_act<64, false, false>(act, ta, tb, p, grid, st);
     case 128: return dispatch_act<128, false, false>(act, ta, tb, p, grid, st);
     default: return dispatch_act<256, false, false>(act, ta, tb, p, grid, st);
+  }
+}
+}  // namespace
+
+namespace {
+template <int BN, int kAct>
+int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_m, int tiles_n, int sm_count,
+                      cudaStream_t stream) {
+  using C = PCfg<BN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tall_persistent_kernel<BN, kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    // same (maximal) shared-memory carve-out as every other kernel of the library: CTAs of two kernels only share an SM
+    // when their carve-outs agree
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tall_persistent_kernel<BN, kAct>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_done = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(std::min(tiles_m * tiles_n, sm_count)); cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tall_persistent_kernel<BN, kAct>, ta, tb, p, tiles_m, tiles_n));
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+template <int BN>
+int dispatch_persistent(int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_m, int tiles_n,
+                        int sm_count, cudaStream_t st) {
+  switch (act) {
+    case GEMM_ACT_GELU_TANH: return launch_persistent<BN, GEMM_ACT_GELU_TANH>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
+    case GEMM_ACT_GELU_ERF: return launch_persistent<BN, GEMM_ACT_GELU_ERF>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
+    case GEMM_ACT_SILU_MUL: return launch_persistent<BN, GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
+    default: return launch_persistent<BN, GEMM_ACT_NONE>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
   }
 }
 }  // namespace
@@ -801,12 +967,45 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
   else      { p.Ma = c.tokens; p.Nb = c.features; a = c.x; lda = c.ldx; b = c.w; ldb = c.ldw; }
 
+  // Persistent tall path: bf16 output, enough 128 x BN tiles to give every SM several of them
+  {
+    static int persist = -1;
+    if (persist < 0) { const char* e = getenv("AHA_GEMM_PERSIST"); persist = e ? atoi(e) : 1; }
+    // While another stream shares the SMs (vision under the decoder) the one-shot kernel is used instead: a persistent CTA
+    // holds its SM for the whole GEMM and the decoder's grids queue behind it (measured 4.80 vs 4.53 ms per frame; the
+    // 128-column persistent variant, which leaves room for a decoder CTA on paper, measured 4.77).
+    const bool forced = c.force_bn == 192 || c.force_bn == 256 || c.force_bn == 1128;
+    if (!swap && persist && !c.out_f32 && c.force_splits <= 1 && (forced || (c.force_bn == 0 && !g_sm_shared))) {
+      int pbn = c.force_bn == 1128 ? 128 : c.force_bn;   // 1128: the persistent 128-column variant (tests / experiments)
+      if (pbn == 0) {      // fewer wasted columns wins; ties go to the wider tile
+        const int w256 = (p.Nb + 255) / 256 * 256, w192 = (p.Nb + 191) / 192 * 192;
+        pbn = w192 < w256 ? 192 : 256;
+      }
+      const int tm = (p.Ma + kBlockM - 1) / kBlockM, tn = (p.Nb + pbn - 1) / pbn;
+      if ((long)tm * tn >= 2L * w->sm_count || c.force_bn != 0) {
+        p.splits = 1; p.kb_per_split = (p.K + kBlockK - 1) / kBlockK; p.dbg = 0; p.dbg_ts = nullptr;
+        CUtensorMap ta, tb;
+        int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
+        rc = get_tmap(b, p.Nb, p.K, ldb, pbn, &tb); if (rc) return rc;
+        ProfSlot* slot = prof_begin(1, stream);
+        rc = pbn == 128 ? dispatch_persistent<128>(c.act, ta, tb, p, tm, tn, w->sm_count, stream)
+           : pbn == 192 ? dispatch_persistent<192>(c.act, ta, tb, p, tm, tn, w->sm_count, stream)
+                        : dispatch_persistent<256>(c.act, ta, tb, p, tm, tn, w->sm_count, stream);
+        if (slot) {
+          const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * 2;
+          prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,
+                   2.0 * c.tokens * (double)c.features * c.K);
+        }
+        return rc;
+      }
+    }
+  }
   int bn = c.force_bn;
   if (bn == 0) {
     if (swap) bn = p.Nb <= 32 ? 32 : p.Nb <= 64 ? 64 : p.Nb <= 128 ? 128 : 256;
     else bn = p.Nb <= 64 ? 64 : 128;
   }
-  AHA_REQUIRE(bn == 32 || bn == 64 || bn == 128 || bn == 256, "unsupported GEMM BN tile");
+  AHA_REQUIRE(bn == 32 || bn == 64 || bn == 128 || bn == 256, "unsupported GEMM BN tile (one-shot kernel: 32/64/128/256)");
   if (!swap && bn == 32) bn = 64;
   const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM;
   const int tiles_b = (p.Nb + bn - 1) / bn;

@@ -109,6 +109,7 @@ class LiveInferForBenchmark:
         cur, side = torch.cuda.current_stream(), self.model.vision_stream()
         side.wait_stream(cur)                      # the frames (and their H2D copy) were produced on the caller's stream
         video_frames.record_stream(side)
+        _lib.load().aha_set_sm_sharing(1)      # vision kernels that leave room for the decoder's CTAs on every SM
         with torch.cuda.stream(side):
             for b in range(0, len(video_frames), batch_size):
                 batch = self.model.visual_embed(video_frames[b:b + batch_size])
@@ -120,6 +121,7 @@ class LiveInferForBenchmark:
                     self.frame_embeds_queue.append(((r + b) / self.frame_fps, f))      # the reference's (time, embeds) entries
                     if r == 0:
                         self._ready_events[id(f)] = (f, ev)                            # first frame of a batch carries its event
+        _lib.load().aha_set_sm_sharing(0)
 
     def load_one_frame(self, frame: torch.Tensor):
         emb = self.model.visual_embed(frame.reshape(1, *frame.shape[-3:]))

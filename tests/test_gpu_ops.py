@@ -165,3 +165,45 @@ def test_gemm_vs_torch(cuda, T, F_, K, act):
         ref = (F.silu(ref[:, 0::2]).bfloat16().float() * ref[:, 1::2])
     err = (out.float() - ref.bfloat16().float()).abs().max().item()
     assert err <= 0.02 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("T,F_,K,act,bn", [(5832, 3840, 1152, 0, 0), (5832, 4304, 1152, 1, 0), (5832, 1152, 4304, 0, 0),
+                                          (5000, 1152, 1152, 2, 256), (3001, 520, 200, 0, 192), (5832, 4304, 1152, 1, 1128),
+                                          (3001, 520, 200, 2, 1128)])
+def test_gemm_persistent_tall(cuda, T, F_, K, act, bn):
+    """The persistent 128 x {192, 256} kernel (two TMEM accumulators): bias, activation and an in-place residual, ragged
+    token / feature / K tails."""
+    torch.manual_seed(8)
+    x = (torch.randn(T, K, device=cuda) * 0.5).bfloat16()
+    w = (torch.randn(F_, K, device=cuda) / K ** 0.5).bfloat16()
+    bias = (torch.randn(F_, device=cuda) * 0.1).bfloat16()
+    res = (torch.randn(T, F_, device=cuda) * 0.5).bfloat16()
+    out = res.clone()                                    # residual aliases the output, as in the SigLIP tower
+    _lib.check(_lib.load().aha_gemm_bf16(_lib.ptr(x), T, K, _lib.ptr(w), F_, K, K, _lib.ptr(out), F_, 0, 0, act,
+                                         _lib.ptr(bias), _lib.ptr(out), F_, 0, 0, bn, 0, _st()))
+    y = (x.float() @ w.float().t() + bias.float()).bfloat16().float()
+    if act == 1:
+        y = F.gelu(y, approximate="tanh").bfloat16().float()
+    if act == 2:
+        y = F.gelu(y).bfloat16().float()
+    ref = (res.float() + y).bfloat16().float()
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 0.03 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("splits", [2, 3, 5, 8])
+def test_gemm_split_k_workspace_is_deterministic(cuda, splits):
+    """Split-K through the L2 workspace: any split count gives the same bits run after run, and matches torch."""
+    torch.manual_seed(9)
+    T, F_, K = 49, 3584, 18944
+    x = (torch.randn(T, K, device=cuda) * 0.5).bfloat16()
+    w = (torch.randn(F_, K, device=cuda) / K ** 0.5).bfloat16()
+    outs = []
+    for _ in range(3):
+        out = torch.full((T, F_), float("nan"), dtype=torch.bfloat16, device=cuda)
+        _lib.check(_lib.load().aha_gemm_bf16(_lib.ptr(x), T, K, _lib.ptr(w), F_, K, K, _lib.ptr(out), F_, 0, 0, 0, None, None,
+                                             0, 0, -1, 0, splits, _st()))
+        outs.append(out)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    ref = (x.float() @ w.float().t()).bfloat16().float()
+    assert (outs[0].float() - ref).abs().max().item() <= 0.02 * max(1.0, ref.abs().max().item())
