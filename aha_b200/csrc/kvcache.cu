@@ -71,7 +71,7 @@ struct RerotLayers { bf16* k[64]; };
 
 // Thread = (kept key r, 16-byte column chunk c) of one layer: its cos/sin entries are loaded once and applied to the key
 // of every kv head, so a thread has 2 * kvh independent 16-byte HBM loads in flight (8 at 7B) before the first use.
-__global__ void __launch_bounds__(256) rerotate_kernel(RerotLayers ls, const bf16* __restrict__ rerot, int kvh, int d,
+__global__ void __launch_bounds__(256, 3) rerotate_kernel(RerotLayers ls, const bf16* __restrict__ rerot, int kvh, int d,
                                                        int cap, int S, int R, int base, int keep) {
   pdl_wait();
   pdl_launch_dependents();
