@@ -5,10 +5,13 @@ from .config import AhaConfig, VisionConfig, config_preset
 from .caches import SinkCache, SlidingWindowCache, TrulyStaticCache, make_cache
 from .model import VideoHeadLiveLlavaQwenForCausalLM, VideoHeadCausalLMOutputWithPast, build_model_from_state_dict
 from .postproc import find_ticks, find_ticks_batched
+from .highlight import (fuse_scores, fuse_scores_batched, knapsack_selection, knapsack_select_batched, highlight_indices,
+                        highlight_mask_batched)
 from .live_infer import LiveInferForBenchmark, LiveInferForDemo, round_numbers
 from .weights import random_init_state_dict, synthetic_frames
 
 __all__ = ["AhaConfig", "VisionConfig", "config_preset", "SinkCache", "SlidingWindowCache", "TrulyStaticCache",
            "make_cache", "VideoHeadLiveLlavaQwenForCausalLM", "VideoHeadCausalLMOutputWithPast",
            "build_model_from_state_dict", "find_ticks", "find_ticks_batched", "LiveInferForBenchmark", "LiveInferForDemo",
-           "round_numbers", "random_init_state_dict", "synthetic_frames"]
+           "round_numbers", "random_init_state_dict", "synthetic_frames", "fuse_scores", "fuse_scores_batched",
+           "knapsack_selection", "knapsack_select_batched", "highlight_indices", "highlight_mask_batched"]

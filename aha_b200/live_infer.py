@@ -10,7 +10,9 @@ and read back once per stream instead of three `.item()` syncs per frame (:222-2
 active, in which case one read per frame is needed, exactly where the reference needs its decision; and
 `input_video_stream` only ENQUEUES the SigLIP batches, on a second CUDA stream, so the tensor-bound vision tower of
 later batches runs underneath the HBM-bound decoder steps of earlier ones (`inference()` waits per batch on an event).
-Response generation (fast_greedy_generate) is outside this path ("next" row N1): when a threshold fires the frame is
+Response generation ("next" row N1) runs when the driver is given `added_stream_generation_ids` (the reference gets them
+from its tokenizer's chat template): a fired threshold then calls `_generate_response` (greedy decode against the same
+cache, aha_b200/generate.py) and the token ids are recorded in `model_response_list`; without them the frame is only
 recorded in `response_needed` and the stream goes on.
 """
 from __future__ import annotations
@@ -43,7 +45,10 @@ class LiveInferForBenchmark:
                  alt_cache: str = "default_sink", window_length: int = 2048, num_sink_tokens: int = 32,
                  frame_fps: float = 2.0, score_heads=("relevance_score", "informative_score"),
                  stream_end_prob_threshold: Optional[float] = None, stream_end_score_sum_threshold: Optional[float] = None,
-                 running_list_length: int = 20, max_frames: int = 4096, overlap_vision: bool = True):
+                 running_list_length: int = 20, max_frames: int = 4096, overlap_vision: bool = True,
+                 added_stream_generation_ids: Optional[torch.Tensor] = None, eos_token_id: Optional[int] = None,
+                 repetition_penalty: Optional[float] = None, remove_assistant_turns: bool = False,
+                 max_new_tokens: int = 200):
         self.model = model
         self.overlap_vision = overlap_vision and os.environ.get("AHA_OVERLAP_VISION", "1") != "0"
         self.model.eval()
@@ -60,6 +65,12 @@ class LiveInferForBenchmark:
         self._start_ids = start_ids.reshape(1, -1).to(model.device)
         self._added_stream_prompt_ids = None if added_stream_prompt_ids is None else \
             added_stream_prompt_ids.reshape(1, -1).to(model.device)
+        self._added_stream_generation_ids = None if added_stream_generation_ids is None else \
+            added_stream_generation_ids.reshape(1, -1).to(model.device)
+        self.eos_token_id = cfg.eos_token_id if eos_token_id is None else eos_token_id
+        self.repetition_penalty = repetition_penalty
+        self.remove_assistant_turns = remove_assistant_turns
+        self.inplace_output_ids = torch.zeros(1, max_new_tokens, device=model.device, dtype=torch.long)   # test/inference.py:73
         self._cache_args = dict(alt_cache=alt_cache, window_length=window_length, num_sink_tokens=num_sink_tokens,
                                 sink_cache=sink_cache, n_sys=self._start_ids.shape[1])
         self._max_frames = max_frames
@@ -88,6 +99,8 @@ class LiveInferForBenchmark:
         self.consec_frames = 0
         self.init_vision_time = False
         self.response_needed = []
+        self.model_response_list = []
+        self.last_role = None
         self._n_scored = 0
         self._times = []
 
@@ -141,7 +154,9 @@ class LiveInferForBenchmark:
         if not self.init_vision_time:
             self.last_ids = self._start_ids
             self.init_vision_time = True
-        elif self.last_ids is None:
+        elif self.last_role == 'assistant' and not self.remove_assistant_turns and self._added_stream_prompt_ids is not None:
+            self.last_ids = torch.cat([self.last_ids, self._added_stream_prompt_ids], dim=1)     # test/inference.py:205-206
+        else:       # last_role is stream, now we just input another frame
             self.last_ids = torch.tensor([[]], device=self.model.device, dtype=torch.long)
         x = self.model.assemble_chunk(self.last_ids, frame_embeds)
         if self._n_scored >= self._max_frames:
@@ -150,7 +165,7 @@ class LiveInferForBenchmark:
         out = self.model(inputs_embeds=x, use_cache=True, past_key_values=self.past_key_values, return_dict=True,
                          scores_out=slot)
         self.past_key_values = out.past_key_values
-        self.last_ids = None
+        self.last_role = 'stream'
         self._times.append(video_time)
         self._n_scored += 1
         return out
@@ -161,7 +176,26 @@ class LiveInferForBenchmark:
         out = self.model(inputs_embeds=x, use_cache=True, past_key_values=self.past_key_values, return_dict=True)
         self.past_key_values = out.past_key_values
         self.last_query_output = out
+        self.last_role = 'user'
         return out
+
+    def _generate_response(self):
+        """test/inference.py:264-281 without the tokenizer: returns the generated token ids."""
+        from .generate import fast_greedy_generate
+        self.last_ids = self._added_stream_generation_ids
+        inputs_embeds = self.model.get_input_embeddings()(self.last_ids)
+        output_ids, past_key_values, self.generated_token_ids = fast_greedy_generate(
+            model=self.model, inputs_embeds=inputs_embeds, past_key_values=self.past_key_values,
+            eos_token_id=self.eos_token_id, inplace_output_ids=self.inplace_output_ids,
+            repetition_penalty=self.repetition_penalty, generated_token_ids=self.generated_token_ids)
+        if not self.remove_assistant_turns:
+            self.past_key_values = past_key_values
+            self.last_ids = output_ids[:, -1:].clone()
+        else:
+            self.last_ids = torch.tensor([[]], device=self.model.device, dtype=torch.long)
+        self.num_frames_no_reply = 0
+        self.last_role = 'assistant'
+        return output_ids[0].tolist()
 
     def input_one_frame(self):
         """One iteration of the loop (test/live_infer_for_video.py:135-176)."""
@@ -184,6 +218,9 @@ class LiveInferForBenchmark:
                 need = True
             if need:
                 self.response_needed.append(self.video_time)
+                if self._added_stream_generation_ids is not None:
+                    response = self._generate_response()
+                    self.model_response_list.append({'time': self.video_time, 'content': response, 'role': 'assistant'})
         self.video_time += 1 / self.frame_fps
 
     def inference(self):

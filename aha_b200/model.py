@@ -180,6 +180,9 @@ class VideoHeadLiveLlavaQwenForCausalLM:
                 labels=None, informative_labels=None, relevance_labels=None, use_cache=None, output_attentions=None,
                 output_hidden_states=None, frames=None, return_dict=None, scores_out: Optional[torch.Tensor] = None,
                 **kwargs) -> VideoHeadCausalLMOutputWithPast:
+        logits_mode = kwargs.pop("logits_mode", None)       # per-call override: "none" | "last" | "all"
+        logits_mode = self.logits_mode if logits_mode is None else \
+            {"none": _lib.LOGITS_NONE, "last": _lib.LOGITS_LAST, "all": _lib.LOGITS_ALL}[logits_mode]
         if labels is not None or informative_labels is not None or relevance_labels is not None:
             raise NotImplementedError("training losses are out of scope of aha_b200 (inference hot path only)")
         if inputs_embeds is None:
@@ -211,15 +214,15 @@ class VideoHeadLiveLlavaQwenForCausalLM:
         if scores.dtype != torch.float32 or scores.numel() != ns * 3 or not scores.is_contiguous():
             raise ValueError("scores_out must be a contiguous float32 [n_streams, 3] tensor")
         logits = None
-        if self.logits_mode == _lib.LOGITS_ALL:
+        if logits_mode == _lib.LOGITS_ALL:
             logits = torch.empty(ns, q, cfg.vocab_size, **f32)
-        elif self.logits_mode == _lib.LOGITS_LAST:
+        elif logits_mode == _lib.LOGITS_LAST:
             logits = torch.empty(ns, 1, cfg.vocab_size, **f32)
         hidden = torch.empty(ns, q, H, dtype=torch.bfloat16, device=dev) if output_hidden_states else None
         handles = (ctypes.c_void_p * ns)(*[c.handle for c in caches])
         with torch.cuda.device(dev):
             _lib.check(_lib.load().aha_prefill_chunk(
-                self._h, handles, ns, _lib.ptr(x), q, self.mask_mode, self.logits_mode, _lib.ptr(logits), _lib.ptr(inf),
+                self._h, handles, ns, _lib.ptr(x), q, self.mask_mode, logits_mode, _lib.ptr(logits), _lib.ptr(inf),
                 _lib.ptr(rel), _lib.ptr(unc), _lib.ptr(scores), _lib.ptr(hidden), _lib.stream_ptr()))
         return VideoHeadCausalLMOutputWithPast(
             informative_logits=inf, relevance_logits=rel, uncertainty=unc, logits=logits, past_key_values=past_key_values,

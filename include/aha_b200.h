@@ -145,6 +145,28 @@ int aha_find_ticks(const double* scores, int n_streams, int T, double prominence
                    double* thresh_out, void* stream);
 
 /* ---- single operators, exported for the parity tests and for callers that run their own layer loop ---- */
+/* ---- greedy next-token choice of the response decode loop (models/modeling_live.py:64-90) ----
+ * logits [vocab] f32 (last position).  With n_generated > 0 and penalty != 1 the repetition penalty of transformers'
+ * RepetitionPenaltyLogitsProcessor is applied to a copy in `scratch` [vocab] first.  out_id (device, int64) = argmax,
+ * first maximum on ties. */
+int aha_greedy_pick(const float* logits, int vocab, const long long* generated_ids, int n_generated,
+                    float repetition_penalty, float* scratch, long long* out_id, void* stream);
+
+/* ---- score fusion and highlight selection, float64, bit-identical to the reference's Python ----
+ * aha_fuse_scores: test/grid_search.py:58-65  out = alpha*inf + beta*rel - (unc >= thr ? (unc - thr)*epsilon : 0), n values.
+ * aha_knapsack_select: test/highlight_generator.py:8-37 (knapsack_selection), inf/rel/unc [n_streams, T]; every frame
+ *   costs 1, value = inf*alpha + rel*beta + unc*epsilon, budget max_duration <= 31; selected[n_streams, T] gets 0/1,
+ *   scratch_bits [n_streams, T] is caller-allocated work space.
+ * aha_highlight_mask: test/highlight_generator.py:76-86; mask [n_streams, last_frame + 1] = union over selected frames i
+ *   of [gt_frames[i] - half_width, gt_frames[i] + half_width] clipped to [0, last_frame]. */
+int aha_fuse_scores(const double* inf, const double* rel, const double* unc, long long n, double alpha, double beta,
+                    double epsilon, double uncertainty_threshold, double* out, void* stream);
+int aha_knapsack_select(const double* inf, const double* rel, const double* unc, int n_streams, int T, int max_duration,
+                        double alpha, double beta, double epsilon, uint32_t* scratch_bits, uint8_t* selected,
+                        void* stream);
+int aha_highlight_mask(const uint8_t* selected, const int32_t* gt_frames, int n_streams, int T, int half_width,
+                       int last_frame, uint8_t* mask, void* stream);
+
 /* out[tokens, features] = X[tokens, K] . W[features, K]^T (+bias) (activation) (+residual); nn.Linear replacement. */
 int aha_gemm_bf16(const void* x, int tokens, int ldx, const void* w, int features, int ldw, int K, void* out, int ldo,
                   int out_f32, int round_bf16, int act, const void* bias, const void* residual, int ldr, int res_mod,

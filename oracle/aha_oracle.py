@@ -666,3 +666,88 @@ def find_ticks_restated(scores, fps: float = 1.0, prominence: float = 0.02, thre
         if y[p] - max(lm, rm) >= prominence:
             out.append(p)
     return np.array(out, dtype=np.int64), y, float(thresh)
+
+
+# ----------------------------------------------------------------------------------------------
+# N3: score fusion and highlight selection (pure-Python restatement; test infrastructure only)
+# ----------------------------------------------------------------------------------------------
+def fuse_scores(debug_data, alpha, beta, epsilon, uncertainty_threshold):
+    """test/grid_search.py:58-65 (hisum) and :95-104 (tvsum): one fused score per frame."""
+    out = []
+    for e in debug_data:
+        s = alpha * e["informative_score"] + beta * e["relevance_score"]
+        if e["uncertainty_score"] >= uncertainty_threshold:
+            s -= (e["uncertainty_score"] - uncertainty_threshold) * epsilon
+        out.append(s)
+    return out
+
+
+def knapsack_selection(frames_with_index, max_duration, alpha, beta, epsilon):
+    """test/highlight_generator.py:8-37: 0/1 knapsack with unit costs; keeps the reference's DP recurrence, its
+    float comparisons and its backtracking rule, so ties resolve the same way."""
+    n = len(frames_with_index)
+    prev = [0] * (max_duration + 1)
+    changed = []                                   # changed[i-1][j] <=> dp[i][j] != dp[i-1][j]
+    for i in range(1, n + 1):
+        f = frames_with_index[i - 1]
+        value = f["informative_score"] * alpha + f["relevance_score"] * beta + f["uncertainty_score"] * epsilon
+        cur = list(prev)
+        for j in range(1, max_duration + 1):
+            cur[j] = max(prev[j], prev[j - 1] + value)
+        changed.append([cur[j] != prev[j] for j in range(max_duration + 1)])
+        prev = cur
+    selected, rc = [], max_duration
+    for i in range(n, 0, -1):
+        if changed[i - 1][rc]:
+            selected.append(frames_with_index[i - 1]["idx"])
+            rc -= 1
+    return set(selected)
+
+
+def highlight_indices(selected, ground_truth_frames, fps):
+    """test/highlight_generator.py:76-86."""
+    last_frame = ground_truth_frames[-1]
+    half_width = int(fps // 2)
+    out = set()
+    for idx in selected:
+        g = ground_truth_frames[idx]
+        for i in range(max(0, g - half_width), min(last_frame + 1, g + half_width + 1)):
+            out.add(i)
+    return sorted(out)
+
+
+# ----------------------------------------------------------------------------------------------
+# N1: greedy response decode (restatement; test infrastructure only)
+# ----------------------------------------------------------------------------------------------
+def repetition_penalty_logits(scores: torch.Tensor, input_ids: torch.Tensor, penalty: float) -> torch.Tensor:
+    """transformers RepetitionPenaltyLogitsProcessor.__call__ (logits_process.py, 4.49): scores [1,V], input_ids [1,n]."""
+    score = torch.gather(scores, 1, input_ids)
+    score = torch.where(score < 0, score * penalty, score / penalty)
+    return scores.scatter(1, input_ids, score)
+
+
+def greedy_step_logits(w, dims, cache, inputs_embeds, mask_mode="sdpa") -> torch.Tensor:
+    """One decode step of fast_greedy_generate (models/modeling_live.py:72-73): last-position logits [1, V] float32."""
+    out = qwen2_prefill(w, dims, cache, inputs_embeds, mask_mode, want_logits=True)
+    return out.logits[:, -1, :]
+
+
+def fast_greedy_generate(w, dims, cache, inputs_embeds, eos_token_id, max_new_tokens, repetition_penalty=None,
+                         generated_token_ids=None, mask_mode="sdpa", forced_ids=None):
+    """models/modeling_live.py:64-90.  Returns (output ids, generated_token_ids, per-step processed logits).  With
+    `forced_ids` the chosen token of every step is overridden (teacher forcing, for tolerance-aware parity checks)."""
+    generated_token_ids = [] if generated_token_ids is None else generated_token_ids
+    out_ids, step_logits = [], []
+    for i in range(max_new_tokens):
+        logits = greedy_step_logits(w, dims, cache, inputs_embeds, mask_mode)
+        if repetition_penalty is not None and len(generated_token_ids) > 0:
+            logits = repetition_penalty_logits(logits, torch.tensor(generated_token_ids).unsqueeze(0), repetition_penalty)
+        step_logits.append(logits[0].clone())
+        tok = int(logits.argmax(dim=-1)) if forced_ids is None else int(forced_ids[i])
+        if repetition_penalty is not None and tok != eos_token_id:
+            generated_token_ids.append(tok)
+        out_ids.append(tok)
+        if tok == eos_token_id or (forced_ids is not None and i + 1 >= len(forced_ids)):
+            break
+        inputs_embeds = F.embedding(torch.tensor([[tok]]), w["model.embed_tokens.weight"])
+    return out_ids, generated_token_ids, step_logits
