@@ -8,10 +8,11 @@ from .postproc import find_ticks, find_ticks_batched
 from .highlight import (fuse_scores, fuse_scores_batched, knapsack_selection, knapsack_select_batched, highlight_indices,
                         highlight_mask_batched)
 from .live_infer import LiveInferForBenchmark, LiveInferForDemo, round_numbers
-from .weights import random_init_state_dict, synthetic_frames
+from .weights import random_init_state_dict, synthetic_frames, merge_lora_state_dict
 
 __all__ = ["AhaConfig", "VisionConfig", "config_preset", "SinkCache", "SlidingWindowCache", "TrulyStaticCache",
            "make_cache", "VideoHeadLiveLlavaQwenForCausalLM", "VideoHeadCausalLMOutputWithPast",
            "build_model_from_state_dict", "find_ticks", "find_ticks_batched", "LiveInferForBenchmark", "LiveInferForDemo",
            "round_numbers", "random_init_state_dict", "synthetic_frames", "fuse_scores", "fuse_scores_batched",
-           "knapsack_selection", "knapsack_select_batched", "highlight_indices", "highlight_mask_batched"]
+           "knapsack_selection", "knapsack_select_batched", "highlight_indices", "highlight_mask_batched",
+           "merge_lora_state_dict"]

@@ -79,3 +79,53 @@ def synthetic_frames(n: int, image: int = 384, seed: int = 1, device="cpu") -> t
     up = torch.nn.functional.interpolate(coarse, size=(image, image), mode="bilinear", align_corners=False)
     noise = torch.rand(n, 3, image, image, generator=g, device=device) * 0.2
     return ((up * 0.8 + noise).clamp(0, 1) * 255).to(torch.uint8)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# N2: LoRA adapters at load time.  The reference runs the adapters UNMERGED through peft (PeftModel.from_pretrained,
+# models/modeling_live.py:170-173; r = 16, alpha = 32 on q/k/v/o/gate/up/down of every decoder layer, plus full copies of
+# the `modules_to_save`, arguments_live.py:14-18): y = W x + (alpha / r) * B (A x).  The native engine streams ONE weight
+# matrix per projection, so the adapters are folded in once: W' = W + (alpha / r) * B A, accumulated in fp32 and rounded
+# to bf16 (14 skinny GEMMs per layer less on the hot path).
+# ----------------------------------------------------------------------------------------------------------------------
+def merge_lora_state_dict(base: Dict[str, torch.Tensor], adapter: Dict[str, torch.Tensor], lora_alpha: float = 32.0,
+                          r: int = None, adapter_name: str = "default") -> Dict[str, torch.Tensor]:
+    """`base`: the LLM checkpoint's state dict; `adapter`: a peft adapter state dict (adapter_model.safetensors keys such as
+    `base_model.model.model.layers.0.self_attn.q_proj.lora_A.weight`, with or without the `.default` adapter infix, and
+    `base_model.model.informative_head.modules_to_save.default.weight` / `...informative_head.weight` for saved modules).
+    Returns a new state dict in the base naming with every adapter folded in."""
+    out = dict(base)
+
+    def strip(k: str) -> str:
+        for pre in ("base_model.model.",):
+            if k.startswith(pre):
+                k = k[len(pre):]
+        return k
+
+    a_mats, b_mats, saved = {}, {}, {}
+    for k, t in adapter.items():
+        k = strip(k)
+        k = k.replace(f".lora_A.{adapter_name}.", ".lora_A.").replace(f".lora_B.{adapter_name}.", ".lora_B.")
+        k = k.replace(f".modules_to_save.{adapter_name}.", ".").replace(".original_module.", ".")
+        if ".lora_A." in k:
+            a_mats[k.replace(".lora_A.", ".")] = t
+        elif ".lora_B." in k:
+            b_mats[k.replace(".lora_B.", ".")] = t
+        else:
+            saved[k] = t
+    if set(a_mats) != set(b_mats):
+        raise ValueError(f"unpaired LoRA matrices: {sorted(set(a_mats) ^ set(b_mats))[:4]}")
+    for name, A in a_mats.items():
+        if name not in out:
+            raise KeyError(f"LoRA target '{name}' is not in the base state dict")
+        B = b_mats[name]
+        rank = A.shape[0]
+        if B.shape[1] != rank or (r is not None and rank != r):
+            raise ValueError(f"LoRA rank mismatch for '{name}': A {tuple(A.shape)}, B {tuple(B.shape)}")
+        W = out[name]
+        scale = float(lora_alpha) / rank
+        delta = (B.to(device=W.device, dtype=torch.float32) @ A.to(device=W.device, dtype=torch.float32)) * scale
+        out[name] = (W.float() + delta).to(W.dtype)
+    for name, t in saved.items():          # modules_to_save: full replacements (heads, projector, ...)
+        out[name] = t.to(dtype=out[name].dtype, device=out[name].device) if name in out else t
+    return out
