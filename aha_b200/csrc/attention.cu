@@ -212,8 +212,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tmem_ld_32x32b_x32p(s_addr + 64, sv + 64);
         tmem_ld_32x32b_x32p(s_addr + 96, sv + 96);
         tmem_ld_wait();
-        if (!(all_visible && (kt * kTile + kTile <= seg.klen))) {
-          // slow path (growing cache / ragged last tile): knock masked scores out before the statistics
+        if (all_visible && kt * kTile + kTile > seg.klen) {
+          // ragged last tile without a causal limit (SigLIP's 729 keys, a full cache): only slots >= klen are masked
+          const int nvalid = seg.klen - kt * kTile;
+#pragma unroll
+          for (int t = 0; t < kTile; ++t)
+            if (t >= nvalid) sv[t] = 0xff800000u;   // -inf
+        } else if (!all_visible) {
+          // slow path (growing cache: causal limit through the ring geometry): knock masked scores out before the statistics
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             const uint32_t vm = visible_mask32(seg, kt * kTile + c * 32, limit);
@@ -470,7 +476,7 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   static int sm_count = 0;
   if (!sm_count) { int dev = 0; AHA_CUDA(cudaGetDevice(&dev)); AHA_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev)); }
   int splits = 1;
-  if (ctas < sm_count && max_tiles > 1) {
+  if (ctas < sm_count && max_tiles > 1 && !p.no_split) {
     splits = sm_count / ctas;
     if (const char* e = getenv("AHA_ATTN_SPLITS")) { const int v = atoi(e); if (v >= 1 && v < splits) splits = v; }
     if (splits > 8) splits = 8;

@@ -330,6 +330,64 @@ inline int grid_for(long long work_items, int threads, int cap = 148 * 16) {
 
 }  // namespace
 
+// nn.LayerNorm for many short rows (the SigLIP tower: 23 328 rows x 1152): one WARP per row, the row lives in registers
+// (kV 16-byte loads per lane, all in flight at once), statistics by shuffles only - no block barrier, 8 rows per CTA.
+// Same formula and roundings as norm_kernel<true> (two-pass variance, one bf16 rounding at the end).
+template <int kV>
+__global__ void __launch_bounds__(256) layernorm_warp_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                             const bf16* __restrict__ b, bf16* __restrict__ out, int rows,
+                                                             int cols, float eps) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int nvec = cols >> 3;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * cols);
+  uint4 u[kV];
+#pragma unroll
+  for (int it = 0; it < kV; ++it) {
+    const int c = lane + it * 32;
+    u[it] = c < nvec ? ld_nc_v4(xr + c) : make_uint4(0, 0, 0, 0);
+  }
+  float v[kV][8];
+  float s = 0.f;
+#pragma unroll
+  for (int it = 0; it < kV; ++it) {
+    const float2 a0 = unpack_bf16x2(u[it].x), a1 = unpack_bf16x2(u[it].y), a2 = unpack_bf16x2(u[it].z), a3 = unpack_bf16x2(u[it].w);
+    v[it][0] = a0.x; v[it][1] = a0.y; v[it][2] = a1.x; v[it][3] = a1.y;
+    v[it][4] = a2.x; v[it][5] = a2.y; v[it][6] = a3.x; v[it][7] = a3.y;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s += v[it][e];          // padding lanes hold zeros
+  }
+  const float mean = warp_sum(s) / (float)cols;
+  float s2 = 0.f;
+#pragma unroll
+  for (int it = 0; it < kV; ++it) {
+    if (lane + it * 32 < nvec) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { const float dlt = v[it][e] - mean; s2 += dlt * dlt; }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(s2) / (float)cols + eps);
+  uint4* orow = reinterpret_cast<uint4*>(out + (size_t)row * cols);
+#pragma unroll
+  for (int it = 0; it < kV; ++it) {
+    const int c = lane + it * 32;
+    if (c < nvec) {
+      const uint4 wu = *reinterpret_cast<const uint4*>(w + (size_t)c * 8);
+      const uint4 bu = *reinterpret_cast<const uint4*>(b + (size_t)c * 8);
+      const uint32_t ww[4] = {wu.x, wu.y, wu.z, wu.w}, bw[4] = {bu.x, bu.y, bu.z, bu.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 wf = unpack_bf16x2(ww[e]), bf = unpack_bf16x2(bw[e]);
+        o[e] = pack_bf16x2((v[it][2 * e] - mean) * rstd * wf.x + bf.x, (v[it][2 * e + 1] - mean) * rstd * wf.y + bf.y);
+      }
+      st_v4(orow + c, make_uint4(o[0], o[1], o[2], o[3]));
+    }
+  }
+}
+
 int op_rmsnorm(const bf16* x, const bf16* w, bf16* out, int rows, int cols, float eps, cudaStream_t st) {
   AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= kNormThreads * kNormMaxVec * 8, "rmsnorm: bad shape");
   return launch_pdl(norm_kernel<false>, dim3(rows), dim3(kNormThreads), 0, st, x, w, (const bf16*)nullptr, out, cols, eps);
@@ -337,6 +395,8 @@ int op_rmsnorm(const bf16* x, const bf16* w, bf16* out, int rows, int cols, floa
 
 int op_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* out, int rows, int cols, float eps, cudaStream_t st) {
   AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= kNormThreads * kNormMaxVec * 8, "layernorm: bad shape");
+  if (rows >= 1024 && cols <= 32 * 5 * 8)   // many short rows: warp per row
+    return launch_pdl(layernorm_warp_kernel<5>, dim3((rows + 7) / 8), dim3(256), 0, st, x, w, b, out, rows, cols, eps);
   return launch_pdl(norm_kernel<true>, dim3(rows), dim3(kNormThreads), 0, st, x, w, b, out, cols, eps);
 }
 

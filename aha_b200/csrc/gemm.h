@@ -59,6 +59,7 @@ struct GemmWorkspace {
 };
 
 int gemm_workspace_create(GemmWorkspace* w, int device);
+bool aha_sm_shared();   // aha_set_sm_sharing(1) is in effect
 // Per-stream split scratch of the default workspace: 64 MB of fp32 partials and 2 x kCounters zeroed arrival counters
 // (the GEMM uses counters [0, kCounters), the attention merge [kCounters, 2 * kCounters)).
 int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out);

@@ -950,6 +950,7 @@ int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out) {
 
 static int g_sm_shared = 0;
 extern "C" int aha_set_sm_sharing(int shared) { g_sm_shared = shared != 0; return AHA_OK; }
+bool aha_sm_shared() { return g_sm_shared != 0; }
 
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
@@ -1039,6 +1040,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
       if (splits > 8) splits = 8;
     }
   }
+  // Split CTAs wait for their siblings.  Two grids of waiting CTAs on two streams could starve each other of SM slots, so
+  // while the streams share the SMs only the decoder's weight-streaming GEMMs (skinny orientation) may split.
+  if (g_sm_shared && !swap && c.force_splits == 0) splits = 1;
   if (splits > kb_total) splits = kb_total;
   int kb_per = (kb_total + splits - 1) / splits;
   splits = (kb_total + kb_per - 1) / kb_per;  // no empty splits

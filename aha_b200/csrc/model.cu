@@ -287,6 +287,7 @@ int vision_forward(aha_model_s* m, const uint8_t* frames_u8, const bf16* pixels,
   ap.n_blocks = d.v_heads; ap.nq_rows = P; ap.group = 1; ap.d = m->v_hd; ap.d_pad = m->v_hd_pad;
   ap.scale = 1.0f / sqrtf((float)m->v_hd);
   ap.out = m->ws_vattn; ap.out_ld = C;
+  ap.no_split = aha_sm_shared() ? 1 : 0;   // the decoder stream owns the waiting-split kernels while the SMs are shared
   for (int l = 0; l < d.v_layers; ++l) {
     const VisionLayerW& w = m->vl[l];
     TRY(op_layernorm(m->ws_vx, w.ln1_w, w.ln1_b, m->ws_vh, M, C, d.v_eps, st));

@@ -32,7 +32,7 @@ def test_rmsnorm(cuda, rows, cols):
     assert (out.cpu() != ref).float().mean().item() < 0.01
 
 
-@pytest.mark.parametrize("rows,cols", [(729, 1152), (81, 144), (10, 4304 - 4304 % 8)])
+@pytest.mark.parametrize("rows,cols", [(729, 1152), (81, 144), (10, 4304 - 4304 % 8), (5832, 1152), (1031, 72), (2048, 1280)])
 def test_layernorm(cuda, rows, cols):
     torch.manual_seed(1)
     x = (torch.randn(rows, cols) * 3 + 0.5).bfloat16()
