@@ -79,13 +79,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint8_t* sV = smem + AttnSmem::v_off(DB);
   uint8_t* sP = smem + AttnSmem::p_off(DB);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AttnSmem::bar_off(DB));
+  // K and V have their own rings: a K stage is free again as soon as its Q.K^T has completed (one whole softmax period
+  // before the matching P.V), so its refill has two softmax periods to land instead of one
   uint64_t* q_full = bars;             // 1
-  uint64_t* kv_full = bars + 1;        // kStagesKV
-  uint64_t* kv_empty = bars + 3;       // kStagesKV
+  uint64_t* k_full = bars + 1;         // kStagesKV
+  uint64_t* k_empty = bars + 3;        // kStagesKV
   uint64_t* s_full = bars + 5;         // 2
   uint64_t* p_full = bars + 7;         // 1 (128 arrivals)
   uint64_t* pv_done = bars + 8;        // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* v_full = bars + 9;         // kStagesKV
+  uint64_t* v_empty = bars + 11;       // kStagesKV
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned long long* ts = (p.dbg_ts && threadIdx.x == 128 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg_ts : nullptr;
@@ -103,7 +107,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   if (warp == 0 && lane == 0) { prefetch_tensormap(&tmap_q); prefetch_tensormap(&tmap_k); prefetch_tensormap(&tmap_v); }
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
-    for (int s = 0; s < kStagesKV; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    for (int s = 0; s < kStagesKV; ++s) {
+      mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
+    }
     mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
     mbar_init(p_full, 128);
     mbar_init(pv_done, 1);
@@ -142,21 +148,32 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         mbar_arrive_expect_tx(q_full, stage_bytes);
         for (int b = 0; b < DB; ++b) tma_load_2d(sQ + b * kAtomBytes, &tmap_q, q_full, q_col + b * 64, q_row);
         const int k_row = seg.k_row0 + blk * p.k_head_rows, k_col = p.k_col0 + blk * p.k_col_step;
-        const int v_row = seg.v_row0 + blk * p.k_head_rows, v_col = p.v_col0 + blk * p.v_col_step;
         for (int it = 0; it < nkt; ++it) {
           const int s = it % kStagesKV;
           const uint32_t ph = (it / kStagesKV) & 1;
-          mbar_wait(&kv_empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&kv_full[s], 2 * stage_bytes);
+          mbar_wait(&k_empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&k_full[s], stage_bytes);
           const int key0 = (kt0 + it) * kTile;
-          for (int b = 0; b < DB; ++b) {
-            tma_load_2d(sK + s * stage_bytes + b * kAtomBytes, &tmap_k, &kv_full[s], k_col + b * 64, k_row + key0);
-            tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, &tmap_v, &kv_full[s], v_col + b * 64, v_row + key0);
-          }
+          for (int b = 0; b < DB; ++b)
+            tma_load_2d(sK + s * stage_bytes + b * kAtomBytes, &tmap_k, &k_full[s], k_col + b * 64, k_row + key0);
         }
         if (!p.pf_early)
           l2_prefetch_slice(p.pf, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
                             gridDim.x * gridDim.y * gridDim.z);
+      }
+    } else if (warp == 3) {
+      // ===================== TMA producer of the V ring =====================
+      if (elect_one()) {
+        const int v_row = seg.v_row0 + blk * p.k_head_rows, v_col = p.v_col0 + blk * p.v_col_step;
+        for (int it = 0; it < nkt; ++it) {
+          const int s = it % kStagesKV;
+          const uint32_t ph = (it / kStagesKV) & 1;
+          mbar_wait(&v_empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&v_full[s], stage_bytes);
+          const int key0 = (kt0 + it) * kTile;
+          for (int b = 0; b < DB; ++b)
+            tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, &tmap_v, &v_full[s], v_col + b * 64, v_row + key0);
+        }
       }
     } else if (warp == 1) {
       // ===================== MMA issuer =====================
@@ -166,7 +183,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int ksteps = p.d_pad >> 4;
         auto issue_qk = [&](int it) {
           const int s = it % kStagesKV;
-          mbar_wait(&kv_full[s], (it / kStagesKV) & 1);
+          mbar_wait(&k_full[s], (it / kStagesKV) & 1);
           tc_fence_after();
           const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + s * stage_bytes);
           for (int ks = 0; ks < ksteps; ++ks) {
@@ -174,15 +191,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             umma_f16_ss(tmem_base + ((it & 1) ? kColS1 : kColS0), make_kmajor_sw128_desc(qa + o),
                         make_kmajor_sw128_desc(ka + o), idesc_qk, ks != 0);
           }
+          umma_commit(&k_empty[s]);      // the K stage is free once these MMAs have read it
           umma_commit(&s_full[it & 1]);
         };
         mbar_wait(q_full, 0);
         issue_qk(0);
         for (int it = 0; it < nkt; ++it) {
           if (it + 1 < nkt) issue_qk(it + 1);
+          const int s = it % kStagesKV;
+          mbar_wait(&v_full[s], (it / kStagesKV) & 1);
           mbar_wait(p_full, it & 1);
           tc_fence_after();
-          const int s = it % kStagesKV;
           const uint32_t pa = smem_u32(sP), va = smem_u32(sV + s * stage_bytes);
           for (int ks = 0; ks < kTile / 16; ++ks) {
             const uint64_t da = make_kmajor_sw128_desc(pa + (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32);
@@ -190,7 +209,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const uint64_t db = make_mnmajor_sw128_desc(va + (uint32_t)ks * 2048, kAtomBytes, 1024);
             umma_f16_ss(tmem_base + kColO, da, db, idesc_pv, (it | ks) != 0);
           }
-          umma_commit(&kv_empty[s]);
+          umma_commit(&v_empty[s]);
           umma_commit(pv_done);
         }
       }
@@ -205,6 +224,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
         dbg_stamp(ts, 3 + 2 * min(it, 1));
+        if (it == 2) { dbg_stamp(ts, 8); }
         const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0);
         uint32_t sv[kTile];
         tmem_ld_32x32b_x32p(s_addr, sv);
@@ -212,6 +232,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tmem_ld_32x32b_x32p(s_addr + 64, sv + 64);
         tmem_ld_32x32b_x32p(s_addr + 96, sv + 96);
         tmem_ld_wait();
+        if (it == 2) { dbg_stamp(ts, 13); }
         if (all_visible && kt * kTile + kTile > seg.klen) {
           // ragged last tile without a causal limit (SigLIP's 729 keys, a full cache): only slots >= klen are masked
           const int nvalid = seg.klen - kt * kTile;
@@ -240,7 +261,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           rescale = true;
         }
         // P smem and O are owned by the tensor pipe until P.V of the previous tile has completed
+        if (it == 2) { dbg_stamp(ts, 14); }
         if (it > 0) mbar_wait(pv_done, (it - 1) & 1);
+        if (it == 2) { dbg_stamp(ts, 15); }
         if (it > 0 && __any_sync(0xffffffffu, rescale)) {
           tc_fence_after();
 #pragma unroll 1
@@ -281,6 +304,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tc_fence_before();
         mbar_arrive(p_full);
         dbg_stamp(ts, 4 + 2 * min(it, 1));
+        if (it == 2) { dbg_stamp(ts, 9); }
+        if (it == 1) { dbg_stamp(ts, 10); }
       }
       mbar_wait(pv_done, (nkt - 1) & 1);   // O complete
       tc_fence_after();

@@ -7,9 +7,10 @@
 Differences that are the point of the rewrite: frame embeddings stay on the device (the reference parks them in host
 RAM, test/inference.py:185,213); the three per-frame scores are written by the heads kernel into a device score buffer
 and read back once per stream instead of three `.item()` syncs per frame (:222-227) - unless a response threshold is
-active, in which case one read per frame is needed, exactly where the reference needs its decision; and
-`input_video_stream` only ENQUEUES the SigLIP batches, on a second CUDA stream, so the tensor-bound vision tower of
-later batches runs underneath the HBM-bound decoder steps of earlier ones (`inference()` waits per batch on an event).
+active, in which case one read per frame is needed, exactly where the reference needs its decision.  With
+`overlap_vision=True`, `input_video_stream` only ENQUEUES the SigLIP batches, on a second CUDA stream, so the
+tensor-bound vision tower of later batches runs underneath the HBM-bound decoder steps of earlier ones (`inference()`
+waits per batch on an event); off by default, see DESIGN.md section 3.
 Response generation ("next" row N1) runs when the driver is given `added_stream_generation_ids` (the reference gets them
 from its tokenizer's chat template): a fired threshold then calls `_generate_response` (greedy decode against the same
 cache, aha_b200/generate.py) and the token ids are recorded in `model_response_list`; without them the frame is only
@@ -45,7 +46,7 @@ class LiveInferForBenchmark:
                  alt_cache: str = "default_sink", window_length: int = 2048, num_sink_tokens: int = 32,
                  frame_fps: float = 2.0, score_heads=("relevance_score", "informative_score"),
                  stream_end_prob_threshold: Optional[float] = None, stream_end_score_sum_threshold: Optional[float] = None,
-                 running_list_length: int = 20, max_frames: int = 4096, overlap_vision: bool = True,
+                 running_list_length: int = 20, max_frames: int = 4096, overlap_vision: bool = False,
                  added_stream_generation_ids: Optional[torch.Tensor] = None, eos_token_id: Optional[int] = None,
                  repetition_penalty: Optional[float] = None, remove_assistant_turns: bool = False,
                  max_new_tokens: int = 200):

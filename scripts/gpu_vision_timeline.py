@@ -22,5 +22,6 @@ print("vision batch of 32 frames: %.3f ms  (%.3f ms per frame)" % (e0.elapsed_ti
 a = (ctypes.c_ulonglong * 16)()
 A._lib.check(A._lib.load().aha_debug_attention_timeline(a))
 t = list(a)
-names = ["entry", "setup", "pdl_wait", "S0 ready", "P0 written", "S(last) ready", "P(last) written", "O done", "-", "-", "-", "-", "exit"]
+names = ["entry", "setup", "pdl_wait", "S0 ready", "P0 written", "S(last) ready", "P(last) written", "O done", "it2 S ready",
+         "it2 P written", "it1 P written", "-", "exit", "it2 tmem loaded", "it2 max done", "it2 pv_done seen"]
 print({n: round((x - t[0]) / 1.965e3, 2) for n, x in zip(names, t) if x})

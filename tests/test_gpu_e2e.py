@@ -175,3 +175,23 @@ def test_forward_api_errors(cuda):
         model(inputs_embeds=torch.zeros(1, 64, cfg.hidden_size, dtype=torch.bfloat16, device=cuda), past_key_values=c)
     with pytest.raises(TypeError):
         model(inputs_embeds=x.float(), past_key_values=c)
+
+
+@pytest.mark.gpu
+def test_overlapped_vision_stream_matches_serial(cuda):
+    """overlap_vision=True (vision batches on a second stream, decoder on the high-priority stream, SM-sharing kernel
+    variants) gives the same scores as the serial path up to the bf16 noise of a different split order."""
+    dims, cfg = o.dims_preset("micro72"), A.config_preset("micro72")
+    w = o.init_weights(dims, seed=0, dtype=torch.bfloat16)
+    model = A.VideoHeadLiveLlavaQwenForCausalLM(cfg, w, device=cuda, max_tokens=64, max_frames=4, logits_mode="none")
+    frames = o.synthetic_frames_varied(11, image=cfg.vision.image_size, seed=4).to(cuda)
+    start = torch.arange(3, 13).reshape(1, -1)
+    outs = []
+    for ov in (False, True):
+        live = A.LiveInferForBenchmark(model, start, window_length=64, num_sink_tokens=8, frame_fps=1.0, overlap_vision=ov)
+        live.input_video_stream(frames, batch_size=4)
+        outs.append(live.inference())
+        assert len(outs[-1]) == 11 and live.past_key_values.get_seq_length() == 64
+    for a, b in zip(*outs):
+        for k in ("informative_score", "relevance_score", "uncertainty_score"):
+            assert abs(a[k] - b[k]) <= 2e-2 * max(1.0, abs(b[k])), (k, a[k], b[k])     # the log-variance head is O(10)
