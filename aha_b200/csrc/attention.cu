@@ -357,20 +357,25 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const size_t cta_floats = (size_t)kTile * p.d_pad + 2 * kTile;
       float* mine = p.ws_partial + ((size_t)group_lin * splits + split) * cta_floats;
 #pragma unroll 1
-      for (int cc = 0; cc < p.d_pad; cc += 16) {
-        uint32_t r[16];
+      for (int cc = 0; cc < p.d_pad; cc += 32) {     // 32 columns per TMEM round trip (d_pad is a multiple of 16)
+        uint32_t r[32];
+        const bool two = cc + 32 <= p.d_pad;
         if (nkt > 0) {
-          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+          if (two) tmem_ld_32x32b_x32p(lane_addr + kColO + cc, r);
+          else { uint32_t h[16]; tmem_ld_32x32b_x16(lane_addr + kColO + cc, h);
+#pragma unroll
+                 for (int t = 0; t < 16; ++t) r[t] = h[t]; }
           tmem_ld_wait();
         } else {
 #pragma unroll
-          for (int t = 0; t < 16; ++t) r[t] = 0u;
+          for (int t = 0; t < 32; ++t) r[t] = 0u;
         }
         float4* dst = reinterpret_cast<float4*>(mine + (size_t)row * p.d_pad + cc);
 #pragma unroll
-        for (int v4 = 0; v4 < 4; ++v4)
-          __stcg(dst + v4, make_float4(__uint_as_float(r[4 * v4]), __uint_as_float(r[4 * v4 + 1]),
-                                       __uint_as_float(r[4 * v4 + 2]), __uint_as_float(r[4 * v4 + 3])));
+        for (int v4 = 0; v4 < 8; ++v4)
+          if (v4 < 4 || two)
+            __stcg(dst + v4, make_float4(__uint_as_float(r[4 * v4]), __uint_as_float(r[4 * v4 + 1]),
+                                         __uint_as_float(r[4 * v4 + 2]), __uint_as_float(r[4 * v4 + 3])));
       }
       __stcg(mine + (size_t)kTile * p.d_pad + row, m_used);
       __stcg(mine + (size_t)kTile * p.d_pad + kTile + row, l_sum);
@@ -390,7 +395,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       __threadfence();
       dbg_stamp(ts, 9);
       const float* grp = p.ws_partial + (size_t)group_lin * splits * cta_floats;
-      // all loads of a step are issued before the first use (splits beyond `splits` alias split 0 with weight 0)
+      // all loads of a step are issued before the first use (splits beyond `splits` alias split 0 with weight 0); the O
+      // pieces of this CTA's first chunk are requested together with the statistics: one L2 round trip, not two
+      float4 v[8][4];
+      if (split < (p.d_pad >> 4)) {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + split * 16);
+#pragma unroll
+          for (int v4 = 0; v4 < 4; ++v4) v[s][v4] = __ldcg(peer + v4);
+        }
+      }
       float ms[8], ls[8];
 #pragma unroll
       for (int s = 0; s < 8; ++s) {
@@ -413,12 +428,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll 1
       for (int c = split; c < (p.d_pad >> 4); c += splits) {
         const int cc = c * 16;
-        float4 v[8][4];
+        if (c != split) {
 #pragma unroll
-        for (int s = 0; s < 8; ++s) {
-          const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + cc);
+          for (int s = 0; s < 8; ++s) {
+            const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + cc);
 #pragma unroll
-          for (int v4 = 0; v4 < 4; ++v4) v[s][v4] = __ldcg(peer + v4);
+            for (int v4 = 0; v4 < 4; ++v4) v[s][v4] = __ldcg(peer + v4);
+          }
         }
         float acc[16];
 #pragma unroll
