@@ -29,7 +29,9 @@ class _LayerView:
     def __len__(self):
         return self._c._populated_layers()
 
-    def __getitem__(self, layer: int):
+    def __getitem__(self, layer):
+        if isinstance(layer, slice):                 # the reference's key_cache is a plain list
+            return [self[i] for i in range(*layer.indices(len(self)))]
         if layer < 0:
             layer += len(self)
         if not 0 <= layer < len(self):
