@@ -215,10 +215,11 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
     m->wstream.add(w.down_w, (size_t)H * d.inter * 2);
   }
   {
-    // rolling L2 prefetch window in MB (AHA_PF_MB).  OFF by default: on B200 it measured no gain (the skinny GEMMs are
-    // bound by their latency chain, not by where their bytes come from; profiles/r01_l2_prefetch_sweep.txt)
+    // rolling L2 prefetch window in MB (AHA_PF_MB, 0 disables).  Measured on B200 at 7B with the current kernels
+    // (profiles/r01_l2_prefetch_sweep.txt): GEMM-tail prefetch of 16-28 MB is worth 2.4 % of a decoder step (3.56 ->
+    // 3.47 ms), 64 MB and more costs time, prefetching from the attention kernel brings nothing.
     const char* e = getenv("AHA_PF_MB");
-    m->wstream.cap = (size_t)(e ? std::max(0, atoi(e)) : 0) << 20;
+    m->wstream.cap = (size_t)(e ? std::max(0, atoi(e)) : 20) << 20;
   }
   // Qwen2RotaryEmbedding: inv_freq = 1 / theta^(arange(0, d, 2) / d), float32 like torch
   {
@@ -388,7 +389,7 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
       const bool ring = c->policy != AHA_POLICY_STATIC && p.klen <= c->W;
       sg.ring_S = c->S; sg.ring_R = ring ? c->R : 0; sg.ring_base = p.new_base;
       sg.out_row0 = s * q;
-      static const int pf_attn = getenv("AHA_PF_ATTN") ? atoi(getenv("AHA_PF_ATTN")) : 1;
+      static const int pf_attn = getenv("AHA_PF_ATTN") ? atoi(getenv("AHA_PF_ATTN")) : 0;
       ap.pf = pf_attn ? wsm.take(wsm.end_of(4 * l)) : L2Prefetch{};
       ap.pf_early = pf_attn == 2;
       if (!(skip & 4)) TRY(op_attention(ap, st));
