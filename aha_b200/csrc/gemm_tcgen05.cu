@@ -318,6 +318,49 @@ __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t ta
   const int ob0 = (kAct == GEMM_ACT_SILU_MUL) ? (b0 >> 1) : b0;
   const int n_out = (kAct == GEMM_ACT_SILU_MUL) ? (p.Nb >> 1) : p.Nb;
   bf16* out = reinterpret_cast<bf16*>(p.out);
+  // Interior tiles (all 32 rows and all columns valid, 16-byte aligned rows): branch-free, kBatch pieces per lane in
+  // flight - the residual read is a dependent global round trip and with four epilogue warps per SM only the number of
+  // loads in flight per lane hides it (the residual GEMMs of the SigLIP tower were epilogue-bound at 4 in flight).
+  const bool interior = a0 + ew * 32 + 32 <= p.Ma && ob0 + kOutCols <= n_out && (p.ldo & 7) == 0 &&
+                        (reinterpret_cast<uintptr_t>(out) & 15) == 0 && (ob0 & 7) == 0 &&
+                        (!p.residual || ((p.ldr & 7) == 0 && (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0));
+  if (interior) {
+    constexpr int kPieces = 32 * kChunksPerRow / 32;     // pieces per lane
+    constexpr int kB = (kPieces % 8 == 0) ? 8 : (kPieces % 4 == 0) ? 4 : kPieces;
+    static_assert(kPieces % kB == 0 && kB <= 12, "piece count per lane");
+#pragma unroll 1
+    for (int base = 0; base < kPieces; base += kB) {
+      uint4 u[kB], ru[kB];
+      size_t off[kB];
+#pragma unroll
+      for (int j = 0; j < kB; ++j) {
+        const int idx = (base + j) * 32 + lane;
+        const int rr_w = idx / kChunksPerRow, ch = idx % kChunksPerRow;
+        const int token = a0 + ew * 32 + rr_w;
+        u[j] = *reinterpret_cast<const uint4*>(stage_warp + rr_w * kPitch + ch * 16);
+        off[j] = (size_t)token * p.ldo + ob0 + ch * 8;
+        if (p.residual) {
+          const int rr = p.res_mod > 0 ? (token % p.res_mod) : token;
+          ru[j] = *reinterpret_cast<const uint4*>(p.residual + (size_t)rr * p.ldr + ob0 + ch * 8);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < kB; ++j) {
+        if (p.residual) {
+          uint32_t w[4] = {u[j].x, u[j].y, u[j].z, u[j].w};
+          const uint32_t rw[4] = {ru[j].x, ru[j].y, ru[j].z, ru[j].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 a = unpack_bf16x2(w[e]), b = unpack_bf16x2(rw[e]);
+            w[e] = pack_bf16x2(b.x + a.x, b.y + a.y);
+          }
+          u[j] = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        st_v4(out + off[j], u[j]);
+      }
+    }
+    return;
+  }
 #pragma unroll 4
   for (int idx = lane; idx < 32 * kChunksPerRow; idx += 32) {
     const int rrow_in_warp = idx / kChunksPerRow, ch = idx % kChunksPerRow;
@@ -594,14 +637,19 @@ struct PCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   // BN = 128 is the variant that shares the SM with a weight-streaming decoder CTA of another stream: 256 TMEM columns,
   // ~115 KB of shared memory (its epilogue stages 64 columns at a time)
-  static constexpr int kEpiBN = (BN == 128) ? 64 : BN;
+  // EIGHT epilogue warps: warps w and w + 4 share the TMEM lanes 32*(w & 3).. and take one half of the tile's columns
+  // each (with four warps - one per scheduler, nothing to hide their latencies - the GELU and residual GEMMs of the
+  // SigLIP tower were epilogue-bound: 8-9 us of epilogue against 5-8 us of main loop per tile)
+  static constexpr int kEpiWarps = 8;
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
+  static constexpr int kEpiBN = BN / 2;
   static constexpr int kEpiWarpBytes = 32 * (kEpiBN * 2 + 16);
   static constexpr int kTmemCols = (BN <= 128) ? 256 : 512;   // two accumulators of BN columns, power of two
-  static constexpr int kSmemBytes = kStages * kStageBytes + 4 * kEpiWarpBytes + 1024 + 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiWarpBytes + 1024 + 256;
 };
 
 template <int BN, int kAct>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(PCfg<BN>::kThreads, 1)
 gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                             const GemmParams p, const int tiles_m, const int tiles_n) {
   using C = PCfg<BN>;
@@ -610,7 +658,7 @@ gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + C::kStages * C::kABytes;
   uint8_t* smem_epi = smem + C::kStages * C::kStageBytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_epi + 4 * C::kEpiWarpBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_epi + C::kEpiWarps * C::kEpiWarpBytes);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full = empty_bar + C::kStages;     // [2]
   uint64_t* tmem_empty = tmem_full + 2;             // [2]
@@ -624,7 +672,7 @@ gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     prefetch_tensormap(&tmap_a);
     prefetch_tensormap(&tmap_b);
     for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], C::kEpiWarps); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
@@ -676,19 +724,21 @@ gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 of both accumulators =====
-    const int ew = warp & 3;
+    // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 of both accumulators, column half (w - 4) / 4 =====
+    const int ew = warp & 3, half = (warp - 4) >> 2;
     uint32_t tl = 0;
+    unsigned long long* ts = (p.dbg_ts && threadIdx.x == 128 && blockIdx.x == 0) ? p.dbg_ts : nullptr;
+    dbg_stamp(ts, 0);
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
       const int a0 = (t / tiles_n) * kBlockM, b0 = (t % tiles_n) * BN;
       const uint32_t buf = tl & 1;
       mbar_wait(&tmem_full[buf], (tl >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(ew * 32) << 16);
-#pragma unroll 1
-      for (int h = 0; h < BN; h += C::kEpiBN)
-        epi_tall_staged<C::kEpiBN, kAct>(p, taddr + h, smem_epi + ew * C::kEpiWarpBytes, a0, b0 + h, ew, lane,
-                                         (h + C::kEpiBN >= BN) ? &tmem_empty[buf] : nullptr);
+      if (tl < 7) dbg_stamp(ts, 1 + 2 * tl);
+      const uint32_t taddr = tmem_base + buf * BN + half * C::kEpiBN + ((uint32_t)(ew * 32) << 16);
+      epi_tall_staged<C::kEpiBN, kAct>(p, taddr, smem_epi + (warp - 4) * C::kEpiWarpBytes, a0, b0 + half * C::kEpiBN, ew, lane,
+                                       &tmem_empty[buf]);
+      if (tl < 7) dbg_stamp(ts, 2 + 2 * tl);
     }
     tc_fence_before();
   }
@@ -867,7 +917,7 @@ int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
     attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(std::min(tiles_m * tiles_n, sm_count)); cfg.blockDim = dim3(kThreads);
+  cfg.gridDim = dim3(std::min(tiles_m * tiles_n, sm_count)); cfg.blockDim = dim3(C::kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -984,7 +1034,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
       }
       const int tm = (p.Ma + kBlockM - 1) / kBlockM, tn = (p.Nb + pbn - 1) / pbn;
       if ((long)tm * tn >= 2L * w->sm_count || c.force_bn != 0) {
-        p.splits = 1; p.kb_per_split = (p.K + kBlockK - 1) / kBlockK; p.dbg = 0; p.dbg_ts = nullptr;
+        p.splits = 1; p.kb_per_split = (p.K + kBlockK - 1) / kBlockK; p.dbg = 0; p.dbg_ts = gemm_ts_slot(dim3(148, 1, 1));
         CUtensorMap ta, tb;
         int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
         rc = get_tmap(b, p.Nb, p.K, ldb, pbn, &tb); if (rc) return rc;

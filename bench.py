@@ -260,41 +260,66 @@ def run_ours(args):
     side = model.vision_stream() if overlap else None
     embeds = [[None] * ns, [None] * ns]            # double buffer: batch b lives in slot b % 2
     ready = [torch.cuda.Event(), torch.cuda.Event()]
-    state = dict(frame=0, overlap=overlap)
+    # vision batches: `start`/`n` = the batch the decoder is consuming (slot `slot`), `next_n` = frames of the batch already
+    # enqueued ahead (overlap only), `stop_at` = frame at which the timed region ends
+    state = dict(frame=0, overlap=overlap, start=0, n=0, slot=1, next_n=0, stop_at=None)
 
-    def vision_batch(slot):
-        """SigLIP -> projector -> pooling for the next VISION_BATCH frames of every stream.  With overlap it is enqueued on
-        the vision stream one batch AHEAD of the decoder, so it runs underneath the decoder steps of the current batch."""
+    def vision_batch(slot, n):
+        """SigLIP -> projector -> pooling for the next n (<= VISION_BATCH) frames of every stream.  With overlap it is
+        enqueued on the vision stream one batch AHEAD of the decoder, so it runs underneath the decoder steps of the
+        current batch."""
         cur = torch.cuda.current_stream()
         if not state["overlap"]:
             for s in range(ns):
-                embeds[slot][s] = model.visual_embed(pool_dev).view(VISION_BATCH, q, cfg.hidden_size)
+                embeds[slot][s] = model.visual_embed(pool_dev[:n]).view(n, q, cfg.hidden_size)
             return
         side.wait_stream(cur)                      # the slot's previous embeddings have been consumed on `cur`
         with torch.cuda.stream(side):
             for s in range(ns):
-                e = model.visual_embed(pool_dev)
+                e = model.visual_embed(pool_dev[:n])
                 e.record_stream(cur)
-                embeds[slot][s] = e.view(VISION_BATCH, q, cfg.hidden_size)
+                embeds[slot][s] = e.view(n, q, cfg.hidden_size)
             ready[slot].record(side)
+
+    def batch_size(first):
+        """Frames in the vision batch that starts at frame `first`: VISION_BATCH, cut so that a batch ends exactly where
+        the timed region ends and nothing is computed ahead for frames beyond it - the K timed frames then carry exactly
+        K frames of SigLIP work whatever K is."""
+        stop = state["stop_at"]
+        if stop is None:
+            return VISION_BATCH
+        return max(0, min(VISION_BATCH, stop - first))
 
     def step():
         """one frame of every resident stream, inputs already in HBM"""
         f = state["frame"]
-        b, i = divmod(f, VISION_BATCH)
-        slot = b % 2
-        if i == 0:
-            if b == 0 or not state["overlap"]:
-                vision_batch(slot)
+        if f == state["start"] + state["n"]:        # the current batch is used up (or this is the first frame)
+            slot = 1 - state["slot"]
+            if state["overlap"] and state["next_n"]:
+                n = state["next_n"]
+            else:
+                n = batch_size(f) or VISION_BATCH
+                vision_batch(slot, n)
             if state["overlap"]:
                 torch.cuda.current_stream().wait_event(ready[slot])
-                vision_batch(1 - slot)             # the NEXT batch: one vision batch per VISION_BATCH decoder steps
+            state.update(start=f, n=n, slot=slot, next_n=0)
+            if state["overlap"]:
+                nn = batch_size(f + n)
+                if nn:
+                    vision_batch(1 - slot, nn)     # the NEXT batch: one vision batch per VISION_BATCH decoder steps
+                state["next_n"] = nn
+        slot, i = state["slot"], f - state["start"]
         if f == 0:
             x = torch.cat([model.assemble_chunk(start_ids, embeds[slot][s][i]) for s in range(ns)], 0)
         else:
             x = torch.stack([embeds[slot][s][i] for s in range(ns)], 0) if ns > 1 else embeds[slot][0][i:i + 1]
         model(inputs_embeds=x, past_key_values=caches, scores_out=scores[f])
         state["frame"] = f + 1
+
+    def begin_region(frames):
+        """Start a fresh vision batch at the next frame and end the last one `frames` later (None: open-ended)."""
+        state.update(n=state["frame"] - state["start"], next_n=0,
+                     stop_at=None if frames is None else state["frame"] + frames)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -310,9 +335,6 @@ def run_ours(args):
         lib.aha_set_sm_sharing(1)
     for _ in range(prime):       # untimed priming: fills the cache so every timed frame runs the steady-state eviction path
         step()
-    # align the timed region to a vision-batch boundary so K frames carry K/32 vision batches
-    while state["frame"] % VISION_BATCH != (VISION_BATCH - (W % VISION_BATCH)) % VISION_BATCH:
-        step()
     for _ in range(W):
         step()
     assert all(c.get_seq_length() == (args.window if args.cache != "static" else c.get_seq_length()) for c in caches)
@@ -322,11 +344,13 @@ def run_ours(args):
         sampler.start()
     launches0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    begin_region(K)              # the timed frames carry exactly their own K frames of vision work
     e0.record()
     for _ in range(K):
         step()
     e1.record()
     barrier()
+    begin_region(None)
     ms = e0.elapsed_time(e1)
     launches = _lib.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
@@ -336,7 +360,8 @@ def run_ours(args):
         ms = float(t.item())
     fps = world * ns * K / (ms / 1e3)
     return dict(rank=rank, world=world, dev=dev, model=model, caches=caches, cfg=cfg, ms=ms, fps=fps, launches=launches,
-                clocks=clocks, pool_host=pool_host, start_ids=start_ids, step=step, state=state, scores=scores, dist=dist,
+                clocks=clocks, pool_host=pool_host, start_ids=start_ids, step=step, state=state, begin_region=begin_region,
+                scores=scores, dist=dist,
                 lib=lib, K=K, W=W, ns=ns)
 
 
@@ -345,20 +370,17 @@ def roofline_leg(r, args, peaks):
     import ctypes
     import torch
     lib, cfg = r["lib"], r["cfg"]
-    n = min(64, r["K"])
-    n -= n % VISION_BATCH if n >= VISION_BATCH else 0
-    n = max(n, 1)
+    n = max(1, min(64, r["K"]))
     # kernel quality, not stream sharing: this pass runs the vision batches on the decoder's stream (no concurrent kernels)
     torch.cuda.synchronize(r["dev"])
     lib.aha_set_sm_sharing(0)
     was, r["state"]["overlap"] = r["state"]["overlap"], False
-    while r["state"]["frame"] % VISION_BATCH:
-        r["step"]()
-    torch.cuda.synchronize(r["dev"])
+    r["begin_region"](n)
     lib.aha_profile_gemm(1)
     for _ in range(n):
         r["step"]()
     torch.cuda.synchronize(r["dev"])
+    r["begin_region"](None)
     r["state"]["overlap"] = was
     out = {}
     for cls, name in ((0, "skinny"), (1, "tall"), (2, "rerot")):
@@ -468,8 +490,7 @@ def main():
     r = run_ours(args)
     if os.environ.get("AHA_NCU"):
         r["state"]["overlap"] = False
-        while r["state"]["frame"] % VISION_BATCH:
-            r["step"]()
+        r["begin_region"](None)
         # profiling aid (never a bench value): one vision batch + 32 steady-state frames inside a cudaProfiler range,
         # for `ncu --profile-from-start off`
         torch.cuda.synchronize()
