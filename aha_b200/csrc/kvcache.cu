@@ -71,6 +71,27 @@ __global__ void rerot_table_kernel(const bf16* __restrict__ cos_t, const bf16* _
 //      Algorithmic bytes per key: 2*d read + 2*d written (+ the shared table rows, which stay in L2).
 struct RerotLayers { bf16* k[64]; };
 
+// Two elements of the low half (l) and the matching two of the high half (h) of one key, with their table entries:
+//   low'  = bf16(bf16(l * c_lo) + bf16(-h * s_lo))      (rotate_half = -high on the low half)
+//   high' = bf16(bf16(h * c_hi) + bf16( l * s_hi))      (rotate_half =  low  on the high half)
+// The product of two bf16 values is exact in fp32, so the packed bf16 multiply (one RNE rounding of the exact product)
+// gives the bits torch's "fp32 multiply, round to bf16" gives; the sums stay fp32-then-round like torch's (a packed bf16
+// add would round the exact sum once, which is not the same thing), and their rounding is the final pack.  The
+// single-value F2F conversions this replaces ran on the XU pipe (16 lanes per clock) and bounded the kernel: ncu showed
+// 83 % XU utilisation against 28 % DRAM.
+__device__ __forceinline__ uint32_t mul_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ void rerot_pair(uint32_t l, uint32_t h, uint32_t c_lo, uint32_t c_hi, uint32_t s_lo,
+                                           uint32_t s_hi, uint32_t& out_lo, uint32_t& out_hi) {
+  const float2 lc = unpack_bf16x2(mul_bf16x2(l, c_lo)), hs = unpack_bf16x2(mul_bf16x2(h, s_lo));
+  const float2 hc = unpack_bf16x2(mul_bf16x2(h, c_hi)), ls = unpack_bf16x2(mul_bf16x2(l, s_hi));
+  out_lo = pack_bf16x2(lc.x - hs.x, lc.y - hs.y);
+  out_hi = pack_bf16x2(hc.x + ls.x, hc.y + ls.y);
+}
+
 // Thread = (kept key r, 16-byte column chunk c) of one layer: its cos/sin entries are loaded once and applied to the key
 // of every kv head, so a thread has 2 * kvh independent 16-byte HBM loads in flight (8 at 7B) before the first use.
 __global__ void __launch_bounds__(256, 3) rerotate_kernel(RerotLayers ls, const bf16* __restrict__ rerot, int kvh, int d,
@@ -110,18 +131,7 @@ __global__ void __launch_bounds__(256, 3) rerotate_kernel(RerotLayers ls, const 
         const uint32_t l[4] = {lo[u].x, lo[u].y, lo[u].z, lo[u].w}, hh[4] = {hi[u].x, hi[u].y, hi[u].z, hi[u].w};
         uint32_t ol[4], oh[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 a = unpack_bf16x2(l[e]), b = unpack_bf16x2(hh[e]);
-          const float2 ca = unpack_bf16x2(cl[e]), cb = unpack_bf16x2(ch[e]);
-          const float2 sa = unpack_bf16x2(sl[e]), sb = unpack_bf16x2(sh[e]);
-          // low half: rotate_half = -high ; high half: rotate_half = low
-          const float lx = bf16r(bf16r(a.x * ca.x) + bf16r(-b.x * sa.x));
-          const float ly = bf16r(bf16r(a.y * ca.y) + bf16r(-b.y * sa.y));
-          const float hx = bf16r(bf16r(b.x * cb.x) + bf16r(a.x * sb.x));
-          const float hy = bf16r(bf16r(b.y * cb.y) + bf16r(a.y * sb.y));
-          ol[e] = pack_bf16x2(lx, ly);
-          oh[e] = pack_bf16x2(hx, hy);
-        }
+        for (int e = 0; e < 4; ++e) rerot_pair(l[e], hh[e], cl[e], ch[e], sl[e], sh[e], ol[e], oh[e]);
         bf16* row = K + ((size_t)(h0 + u) * cap + slot) * d + c * 8;
         st_v4(row, make_uint4(ol[0], ol[1], ol[2], ol[3]));
         st_v4(row + half, make_uint4(oh[0], oh[1], oh[2], oh[3]));
@@ -189,18 +199,7 @@ __global__ void __launch_bounds__(kRrThreads, 4) rerotate_tma_kernel(RerotLayers
       const uint32_t l[4] = {lo.x, lo.y, lo.z, lo.w}, hh[4] = {hi.x, hi.y, hi.z, hi.w};
       uint32_t ol[4], oh[4];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 a = unpack_bf16x2(l[e]), b = unpack_bf16x2(hh[e]);
-        const float2 ca = unpack_bf16x2(cl[e]), cb = unpack_bf16x2(ch[e]);
-        const float2 sa = unpack_bf16x2(sl[e]), sb = unpack_bf16x2(sh[e]);
-        // low half: rotate_half = -high ; high half: rotate_half = low (same op order and rounding as rerotate_kernel)
-        const float lx = bf16r(bf16r(a.x * ca.x) + bf16r(-b.x * sa.x));
-        const float ly = bf16r(bf16r(a.y * ca.y) + bf16r(-b.y * sa.y));
-        const float hx = bf16r(bf16r(b.x * cb.x) + bf16r(a.x * sb.x));
-        const float hy = bf16r(bf16r(b.y * cb.y) + bf16r(a.y * sb.y));
-        ol[e] = pack_bf16x2(lx, ly);
-        oh[e] = pack_bf16x2(hx, hy);
-      }
+      for (int e = 0; e < 4; ++e) rerot_pair(l[e], hh[e], cl[e], ch[e], sl[e], sh[e], ol[e], oh[e]);
       *plo = make_uint4(ol[0], ol[1], ol[2], ol[3]);
       *phi = make_uint4(oh[0], oh[1], oh[2], oh[3]);
     }
