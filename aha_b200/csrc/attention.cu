@@ -31,7 +31,7 @@ namespace {
 constexpr int kTile = 128;          // query rows per CTA == keys per tile
 constexpr int kAtomBytes = 16384;   // one [128 rows][64 bf16] swizzled box
 constexpr int kStagesKV = 2;
-constexpr int kAttnThreads = 256;
+constexpr int kAttnThreads = 384;   // warps 0-3: TMA / MMA / TMEM, warps 4-11: softmax (two threads per query row)
 constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
@@ -42,7 +42,8 @@ struct AttnSmem {
   static __host__ __device__ int v_off(int DB) { return DB * kAtomBytes * (1 + kStagesKV); }
   static __host__ __device__ int p_off(int DB) { return DB * kAtomBytes * (1 + 2 * kStagesKV); }
   static __host__ __device__ int bar_off(int DB) { return p_off(DB) + 2 * kAtomBytes; }
-  static __host__ __device__ int total(int DB) { return bar_off(DB) + 256 + 1024; }
+  static __host__ __device__ int xch_off(int DB) { return bar_off(DB) + 256; }      // float [2][2][128] row-statistics exchange
+  static __host__ __device__ int total(int DB) { return xch_off(DB) + 2048 + 1024; }
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -90,6 +91,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint64_t* v_full = bars + 9;         // kStagesKV
   uint64_t* v_empty = bars + 11;       // kStagesKV
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  float* xch = reinterpret_cast<float*>(smem + AttnSmem::xch_off(DB));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned long long* ts = (p.dbg_ts && threadIdx.x == 128 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg_ts : nullptr;
@@ -111,7 +113,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
     }
     mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
-    mbar_init(p_full, 128);
+    mbar_init(p_full, 256);
     mbar_init(pv_done, 1);
     fence_barrier_init();
   }
@@ -130,8 +132,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   pdl_launch_dependents();
   dbg_stamp(ts, 2);
 
-  // softmax-thread state (meaningful in warps 4-7)
+  // softmax-thread state (meaningful in warps 4-11).  A query row is shared by two threads, lane l of warps w and w + 4
+  // (same TMEM lane quadrant): `half` picks the 64 of the tile's 128 key columns the thread owns, and the 16-column
+  // blocks of O it rescales / stores.  With one thread per row the four softmax warps - one per scheduler, every
+  // latency exposed - were the critical path of the kernel (2.2 us per key tile against 0.3 us of tensor work).
   const int ew = warp & 3;
+  const int half = warp >= 8 ? 1 : 0;
   const int row = ew * 32 + lane;            // tile row == TMEM lane
   const int m = qt * kTile + row;            // query row inside the (segment, block)
   const bool row_valid = m < p.nq_rows;
@@ -225,25 +231,24 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tc_fence_after();
         dbg_stamp(ts, 3 + 2 * min(it, 1));
         if (it == 2) { dbg_stamp(ts, 8); }
-        const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0);
-        uint32_t sv[kTile];
+        const int col0 = half * 64;
+        const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0) + col0;
+        uint32_t sv[64];
         tmem_ld_32x32b_x32p(s_addr, sv);
         tmem_ld_32x32b_x32p(s_addr + 32, sv + 32);
-        tmem_ld_32x32b_x32p(s_addr + 64, sv + 64);
-        tmem_ld_32x32b_x32p(s_addr + 96, sv + 96);
         tmem_ld_wait();
         if (it == 2) { dbg_stamp(ts, 13); }
         if (all_visible && kt * kTile + kTile > seg.klen) {
           // ragged last tile without a causal limit (SigLIP's 729 keys, a full cache): only slots >= klen are masked
-          const int nvalid = seg.klen - kt * kTile;
+          const int nvalid = seg.klen - kt * kTile - col0;
 #pragma unroll
-          for (int t = 0; t < kTile; ++t)
+          for (int t = 0; t < 64; ++t)
             if (t >= nvalid) sv[t] = 0xff800000u;   // -inf
         } else if (!all_visible) {
           // slow path (growing cache: causal limit through the ring geometry): knock masked scores out before the statistics
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const uint32_t vm = visible_mask32(seg, kt * kTile + c * 32, limit);
+          for (int c = 0; c < 2; ++c) {
+            const uint32_t vm = visible_mask32(seg, kt * kTile + col0 + c * 32, limit);
 #pragma unroll
             for (int t = 0; t < 32; ++t)
               if (!((vm >> t) & 1u)) sv[c * 32 + t] = 0xff800000u;   // -inf
@@ -251,7 +256,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         float tmax = -INFINITY;
 #pragma unroll
-        for (int t = 0; t < kTile; ++t) tmax = fmaxf(tmax, __uint_as_float(sv[t]));
+        for (int t = 0; t < 64; ++t) tmax = fmaxf(tmax, __uint_as_float(sv[t]));
+        {
+          // row maximum over both halves: the two threads of a row then take identical rescale decisions.  The slots
+          // alternate with the tile parity; the pair barrier of tile it + 1 orders their reuse at tile it + 2.
+          float* x = xch + (it & 1) * 256;
+          x[half * 128 + row] = tmax;
+          asm volatile("bar.sync %0, 64;" ::"r"(2 + ew) : "memory");
+          tmax = fmaxf(tmax, x[(half ^ 1) * 128 + row]);
+        }
         tmax *= sl2;                                 // scale > 0: max commutes with the scaling
         float alpha = 1.f;
         bool rescale = false;
@@ -267,7 +280,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (it > 0 && __any_sync(0xffffffffu, rescale)) {
           tc_fence_after();
 #pragma unroll 1
-          for (int cc = 0; cc < p.d_pad; cc += 16) {
+          for (int cc = half * 16; cc < p.d_pad; cc += 32) {
             uint32_t r[16];
             tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
             tmem_ld_wait();
@@ -282,7 +295,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const float mref = (m_used == -INFINITY) ? 0.f : m_used;
         float acc_l = 0.f;
 #pragma unroll
-        for (int cc = 0; cc < kTile; cc += 32) {
+        for (int cc = 0; cc < 64; cc += 32) {
           uint32_t pk[16];
 #pragma unroll
           for (int t = 0; t < 32; t += 2) {
@@ -291,8 +304,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             acc_l += x0 + x1;
             pk[t >> 1] = pack_bf16x2(x0, x1);
           }
-          uint8_t* base = prow + (cc >> 6) * kAtomBytes;
-          const int chunk0 = (cc & 63) >> 3;
+          uint8_t* base = prow + half * kAtomBytes;      // key columns 64*half .. +63 are one swizzle atom of P
+          const int chunk0 = cc >> 3;
 #pragma unroll
           for (int ch = 0; ch < 4; ++ch) {
             const int sw = (chunk0 + ch) ^ (row & 7);
@@ -307,6 +320,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (it == 2) { dbg_stamp(ts, 9); }
         if (it == 1) { dbg_stamp(ts, 10); }
       }
+      {
+        // row sum = half 0's partial + half 1's partial, added in that order by both threads
+        float* x = xch + (nkt & 1) * 256;
+        x[half * 128 + row] = l_sum;
+        asm volatile("bar.sync %0, 64;" ::"r"(2 + ew) : "memory");
+        l_sum = x[row] + x[128 + row];
+      }
       mbar_wait(pv_done, (nkt - 1) & 1);   // O complete
       tc_fence_after();
       dbg_stamp(ts, 7);
@@ -319,7 +339,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
       bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
 #pragma unroll 1
-      for (int cc = 0; cc < p.d_pad; cc += 16) {
+      for (int cc = half * 16; cc < p.d_pad; cc += 32) {
         uint32_t r[16];
         if (nkt > 0) {
           tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
@@ -357,7 +377,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const size_t cta_floats = (size_t)kTile * p.d_pad + 2 * kTile;
       float* mine = p.ws_partial + ((size_t)group_lin * splits + split) * cta_floats;
 #pragma unroll 1
-      for (int cc = 0; cc < p.d_pad; cc += 32) {     // 32 columns per TMEM round trip (d_pad is a multiple of 16)
+      for (int cc = half * 32; cc < p.d_pad; cc += 64) {   // 32 columns per TMEM round trip (d_pad is a multiple of 16)
         uint32_t r[32];
         const bool two = cc + 32 <= p.d_pad;
         if (nkt > 0) {
@@ -377,12 +397,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             __stcg(dst + v4, make_float4(__uint_as_float(r[4 * v4]), __uint_as_float(r[4 * v4 + 1]),
                                          __uint_as_float(r[4 * v4 + 2]), __uint_as_float(r[4 * v4 + 3])));
       }
-      __stcg(mine + (size_t)kTile * p.d_pad + row, m_used);
-      __stcg(mine + (size_t)kTile * p.d_pad + kTile + row, l_sum);
+      if (half == 0) {
+        __stcg(mine + (size_t)kTile * p.d_pad + row, m_used);
+        __stcg(mine + (size_t)kTile * p.d_pad + kTile + row, l_sum);
+      }
       tc_fence_before();
       dbg_stamp(ts, 8);
       __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       int* cnt = p.ws_counters + 2 * group_lin;
       if (threadIdx.x == 128) {
         atomicAdd(cnt, 1);
@@ -391,19 +413,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           if (++spins > (1u << 24)) { printf("aha_b200: attention split arrival wait timed out (group %d)\n", group_lin); __trap(); }
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       __threadfence();
       dbg_stamp(ts, 9);
       const float* grp = p.ws_partial + (size_t)group_lin * splits * cta_floats;
       // all loads of a step are issued before the first use (splits beyond `splits` alias split 0 with weight 0); the O
       // pieces of this CTA's first chunk are requested together with the statistics: one L2 round trip, not two
-      float4 v[8][4];
+      // (a 16-column chunk is shared by the two threads of a row: 8 columns each)
+      float4 v[8][2];
       if (split < (p.d_pad >> 4)) {
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
-          const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + split * 16);
+          const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + split * 16 + half * 8);
 #pragma unroll
-          for (int v4 = 0; v4 < 4; ++v4) v[s][v4] = __ldcg(peer + v4);
+          for (int v4 = 0; v4 < 2; ++v4) v[s][v4] = __ldcg(peer + v4);
         }
       }
       float ms[8], ls[8];
@@ -427,22 +450,22 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
 #pragma unroll 1
       for (int c = split; c < (p.d_pad >> 4); c += splits) {
-        const int cc = c * 16;
+        const int cc = c * 16 + half * 8;
         if (c != split) {
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
             const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + cc);
 #pragma unroll
-            for (int v4 = 0; v4 < 4; ++v4) v[s][v4] = __ldcg(peer + v4);
+            for (int v4 = 0; v4 < 2; ++v4) v[s][v4] = __ldcg(peer + v4);
           }
         }
-        float acc[16];
+        float acc[8];
 #pragma unroll
-        for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+        for (int t = 0; t < 8; ++t) acc[t] = 0.f;
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
 #pragma unroll
-          for (int v4 = 0; v4 < 4; ++v4) {
+          for (int v4 = 0; v4 < 2; ++v4) {
             acc[4 * v4 + 0] += wgt[s] * v[s][v4].x;
             acc[4 * v4 + 1] += wgt[s] * v[s][v4].y;
             acc[4 * v4 + 2] += wgt[s] * v[s][v4].z;
@@ -450,22 +473,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           }
         }
         if (row_valid) {
-          if (cc + 16 <= p.d && ((reinterpret_cast<uintptr_t>(orow + cc) & 15) == 0)) {
+          if (cc + 8 <= p.d && ((reinterpret_cast<uintptr_t>(orow + cc) & 15) == 0)) {
 #pragma unroll
-            for (int t = 0; t < 16; ++t) acc[t] *= inv;
+            for (int t = 0; t < 8; ++t) acc[t] *= inv;
             st_v4(orow + cc, make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
                                         pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7])));
-            st_v4(orow + cc + 8, make_uint4(pack_bf16x2(acc[8], acc[9]), pack_bf16x2(acc[10], acc[11]),
-                                            pack_bf16x2(acc[12], acc[13]), pack_bf16x2(acc[14], acc[15])));
           } else {
 #pragma unroll 4
-            for (int t = 0; t < 16; ++t)
+            for (int t = 0; t < 8; ++t)
               if (cc + t < p.d) orow[cc + t] = f2b(acc[t] * inv);
           }
         }
       }
       dbg_stamp(ts, 10);
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (threadIdx.x == 128 && atomicAdd(cnt + 1, 1) == splits - 1) { cnt[0] = 0; cnt[1] = 0; }   // last one out re-arms
     }
   }

@@ -112,6 +112,14 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
   return __bfloat1622float2(v);
 }
 
+// bf16 rounding of two values at once.  A single-value conversion (F2F.BF16.F32) issues on the XU pipe, 16 lanes per
+// clock per SM, and bounds any kernel that rounds after every op; the packed conversion (F2FP) does not.
+__device__ __forceinline__ void bf16r2(float& a, float& b) {
+  const uint32_t p = pack_bf16x2(a, b);
+  a = __uint_as_float(p << 16);
+  b = __uint_as_float(p & 0xffff0000u);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

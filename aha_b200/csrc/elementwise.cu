@@ -73,7 +73,11 @@ __global__ void __launch_bounds__(kNormThreads) norm_kernel(const bf16* __restri
         for (int e = 0; e < 8; ++e) o[e] = (v[it][e] - mean) * rstd * wv[e] + bv[e];
       } else {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] = wv[e] * bf16r(v[it][e] * rstd);
+        for (int e = 0; e < 8; e += 2) {
+          float n0 = v[it][e] * rstd, n1 = v[it][e + 1] * rstd;
+          bf16r2(n0, n1);                        // the reference casts the normalised row to bf16 before the weight
+          o[e] = wv[e] * n0; o[e + 1] = wv[e + 1] * n1;
+        }
       }
       uint4 ou;
       ou.x = pack_bf16x2(o[0], o[1]); ou.y = pack_bf16x2(o[2], o[3]);

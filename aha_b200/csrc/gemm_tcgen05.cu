@@ -96,9 +96,10 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
                                            float (&acc)[16]) {
   const bool round_out = !p.out_f32 || p.round_bf16;
 #pragma unroll
-  for (int t = 0; t < 16; ++t) {
-    acc[t] += bias;
-    if (round_out) acc[t] = bf16r(acc[t]);
+  for (int t = 0; t < 16; ++t) acc[t] += bias;
+  if (round_out) {
+#pragma unroll
+    for (int t = 0; t < 16; t += 2) bf16r2(acc[t], acc[t + 1]);
   }
   const int ntok = min(16, p.Nb - tok0);
   if (kAct == GEMM_ACT_SILU_MUL) {
@@ -106,16 +107,22 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
     bf16* o = reinterpret_cast<bf16*>(p.out) + (feat >> 1) + (size_t)tok0 * p.ldo;
     const bool writer = (i & 1) == 0 && fvalid;
 #pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const float up = __shfl_down_sync(0xffffffffu, acc[t], 1);
-      const float x = bf16r(fast_silu(acc[t])) * up;
-      if (writer && t < ntok) o[(size_t)t * p.ldo] = f2b(x);
+    for (int t = 0; t < 16; t += 2) {
+      const float up0 = __shfl_down_sync(0xffffffffu, acc[t], 1), up1 = __shfl_down_sync(0xffffffffu, acc[t + 1], 1);
+      float s0 = fast_silu(acc[t]), s1 = fast_silu(acc[t + 1]);
+      bf16r2(s0, s1);
+      const uint32_t x = pack_bf16x2(s0 * up0, s1 * up1);
+      if (writer && t < ntok) *reinterpret_cast<uint16_t*>(o + (size_t)t * p.ldo) = (uint16_t)(x & 0xffffu);
+      if (writer && t + 1 < ntok) *reinterpret_cast<uint16_t*>(o + (size_t)(t + 1) * p.ldo) = (uint16_t)(x >> 16);
     }
     return;
   }
   if (kAct != GEMM_ACT_NONE) {
 #pragma unroll
-    for (int t = 0; t < 16; ++t) acc[t] = bf16r(apply_act<kAct>(acc[t]));
+    for (int t = 0; t < 16; t += 2) {
+      acc[t] = apply_act<kAct>(acc[t]); acc[t + 1] = apply_act<kAct>(acc[t + 1]);
+      bf16r2(acc[t], acc[t + 1]);
+    }
   }
   if (!fvalid) return;
   if (p.residual) {
@@ -128,7 +135,10 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
       r[t] = (t < ntok) ? b2f(p.residual[(size_t)rrow * p.ldr + feat]) : 0.f;
     }
 #pragma unroll
-    for (int t = 0; t < 16; ++t) acc[t] = bf16r(r[t] + acc[t]);
+    for (int t = 0; t < 16; t += 2) {
+      acc[t] = r[t] + acc[t]; acc[t + 1] = r[t + 1] + acc[t + 1];
+      bf16r2(acc[t], acc[t + 1]);
+    }
   }
   if (p.out_f32) {
     float* o = reinterpret_cast<float*>(p.out) + feat + (size_t)tok0 * p.ldo;
@@ -136,10 +146,13 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
     for (int t = 0; t < 16; ++t)
       if (t < ntok) o[(size_t)t * p.ldo] = acc[t];
   } else {
-    bf16* o = reinterpret_cast<bf16*>(p.out) + feat + (size_t)tok0 * p.ldo;
+    uint16_t* o = reinterpret_cast<uint16_t*>(p.out) + feat + (size_t)tok0 * p.ldo;
 #pragma unroll
-    for (int t = 0; t < 16; ++t)
-      if (t < ntok) o[(size_t)t * p.ldo] = f2b(acc[t]);
+    for (int t = 0; t < 16; t += 2) {
+      const uint32_t x = pack_bf16x2(acc[t], acc[t + 1]);
+      if (t < ntok) o[(size_t)t * p.ldo] = (uint16_t)(x & 0xffffu);
+      if (t + 1 < ntok) o[(size_t)(t + 1) * p.ldo] = (uint16_t)(x >> 16);
+    }
   }
 }
 
@@ -153,18 +166,28 @@ __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* 
   constexpr int kFeat = (kAct == GEMM_ACT_SILU_MUL) ? 16 : 32;
   constexpr int kPitch = kFeat * 2 + 16;
   constexpr int kPieces = kFeat / 8;            // 16-byte pieces per token
-#pragma unroll
-  for (int t = 0; t < 16; ++t) acc[t] = bf16r(acc[t] + bias);
+  // every rounding is a packed conversion of a token pair (see bf16r2)
   if (kAct == GEMM_ACT_SILU_MUL) {
 #pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const float up = __shfl_down_sync(0xffffffffu, acc[t], 1);
-      const float x = bf16r(fast_silu(acc[t])) * up;
-      if ((lane & 1) == 0) *reinterpret_cast<bf16*>(stage_warp + t * kPitch + (lane >> 1) * 2) = f2b(x);
+    for (int t = 0; t < 16; t += 2) {
+      float g0 = acc[t] + bias, g1 = acc[t + 1] + bias;
+      bf16r2(g0, g1);
+      const float up0 = __shfl_down_sync(0xffffffffu, g0, 1), up1 = __shfl_down_sync(0xffffffffu, g1, 1);
+      float s0 = fast_silu(g0), s1 = fast_silu(g1);
+      bf16r2(s0, s1);
+      const uint32_t x = pack_bf16x2(s0 * up0, s1 * up1);
+      if ((lane & 1) == 0) {
+        *reinterpret_cast<uint16_t*>(stage_warp + t * kPitch + (lane >> 1) * 2) = (uint16_t)(x & 0xffffu);
+        *reinterpret_cast<uint16_t*>(stage_warp + (t + 1) * kPitch + (lane >> 1) * 2) = (uint16_t)(x >> 16);
+      }
     }
   } else {
 #pragma unroll
-    for (int t = 0; t < 16; ++t) *reinterpret_cast<bf16*>(stage_warp + t * kPitch + lane * 2) = f2b(acc[t]);
+    for (int t = 0; t < 16; t += 2) {
+      const uint32_t x = pack_bf16x2(acc[t] + bias, acc[t + 1] + bias);
+      *reinterpret_cast<uint16_t*>(stage_warp + t * kPitch + lane * 2) = (uint16_t)(x & 0xffffu);
+      *reinterpret_cast<uint16_t*>(stage_warp + (t + 1) * kPitch + lane * 2) = (uint16_t)(x >> 16);
+    }
   }
   __syncwarp();
   const int ntok = min(16, p.Nb - tok0);
@@ -214,25 +237,36 @@ __device__ __forceinline__ void epi_tall16(const GemmParams& p, int token, int f
   }
   if (round_out) {
 #pragma unroll
-    for (int t = 0; t < 16; ++t) acc[t] = bf16r(acc[t]);
+    for (int t = 0; t < 16; t += 2) bf16r2(acc[t], acc[t + 1]);
   }
   if (kAct == GEMM_ACT_SILU_MUL) {
-    bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)token * p.ldo + (f0 >> 1);
+    uint16_t* o = reinterpret_cast<uint16_t*>(p.out) + (size_t)token * p.ldo + (f0 >> 1);
 #pragma unroll
-    for (int t = 0; t < 8; ++t)
-      if (2 * t + 1 < nvalid) o[t] = f2b(bf16r(fast_silu(acc[2 * t])) * acc[2 * t + 1]);
+    for (int t = 0; t < 8; t += 2) {
+      float s0 = fast_silu(acc[2 * t]), s1 = fast_silu(acc[2 * t + 2]);
+      bf16r2(s0, s1);
+      const uint32_t x = pack_bf16x2(s0 * acc[2 * t + 1], s1 * acc[2 * t + 3]);
+      if (2 * t + 1 < nvalid) o[t] = (uint16_t)(x & 0xffffu);
+      if (2 * t + 3 < nvalid) o[t + 1] = (uint16_t)(x >> 16);
+    }
     return;
   }
   if (kAct != GEMM_ACT_NONE) {
 #pragma unroll
-    for (int t = 0; t < 16; ++t) acc[t] = bf16r(apply_act<kAct>(acc[t]));
+    for (int t = 0; t < 16; t += 2) {
+      acc[t] = apply_act<kAct>(acc[t]); acc[t + 1] = apply_act<kAct>(acc[t + 1]);
+      bf16r2(acc[t], acc[t + 1]);
+    }
   }
   if (p.residual) {
     const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
     const bf16* r = p.residual + (size_t)rrow * p.ldr + f0;
 #pragma unroll
-    for (int t = 0; t < 16; ++t)
-      if (t < nvalid) acc[t] = bf16r(b2f(r[t]) + acc[t]);
+    for (int t = 0; t < 16; t += 2) {
+      if (t < nvalid) acc[t] = b2f(r[t]) + acc[t];
+      if (t + 1 < nvalid) acc[t + 1] = b2f(r[t + 1]) + acc[t + 1];
+      bf16r2(acc[t], acc[t + 1]);
+    }
   }
   if (p.out_f32) {
     float* o = reinterpret_cast<float*>(p.out) + (size_t)token * p.ldo + f0;
@@ -248,8 +282,11 @@ __device__ __forceinline__ void epi_tall16(const GemmParams& p, int token, int f
                               pack_bf16x2(acc[14], acc[15])));
     } else {
 #pragma unroll
-      for (int t = 0; t < 16; ++t)
-        if (t < nvalid) o[t] = f2b(acc[t]);
+      for (int t = 0; t < 16; t += 2) {
+        const uint32_t x = pack_bf16x2(acc[t], acc[t + 1]);
+        if (t < nvalid) reinterpret_cast<uint16_t*>(o)[t] = (uint16_t)(x & 0xffffu);
+        if (t + 1 < nvalid) reinterpret_cast<uint16_t*>(o)[t + 1] = (uint16_t)(x >> 16);
+      }
     }
   }
 }
@@ -290,13 +327,18 @@ __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t ta
         for (int t = 0; t < 32; ++t) v[t] += (f0 + t < p.Nb) ? b2f(p.bias[f0 + t]) : 0.f;
       }
     }
+    if (kAct != GEMM_ACT_NONE) {    // (no activation: the pack below is the rounding of the linear output)
 #pragma unroll
-    for (int t = 0; t < 32; ++t) v[t] = bf16r(v[t]);
+      for (int t = 0; t < 32; t += 2) bf16r2(v[t], v[t + 1]);
+    }
     if (kAct == GEMM_ACT_SILU_MUL) {
       uint32_t pk[8];
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
-        pk[t] = pack_bf16x2(bf16r(fast_silu(v[4 * t])) * v[4 * t + 1], bf16r(fast_silu(v[4 * t + 2])) * v[4 * t + 3]);
+      for (int t = 0; t < 8; ++t) {
+        float s0 = fast_silu(v[4 * t]), s1 = fast_silu(v[4 * t + 2]);
+        bf16r2(s0, s1);
+        pk[t] = pack_bf16x2(s0 * v[4 * t + 1], s1 * v[4 * t + 3]);
+      }
       *reinterpret_cast<uint4*>(my + jc) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       *reinterpret_cast<uint4*>(my + jc + 16) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
     } else {

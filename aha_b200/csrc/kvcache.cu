@@ -320,13 +320,7 @@ __global__ void __launch_bounds__(256) rope_append_kernel(const bf16* __restrict
     const uint32_t sl[4] = {slo.x, slo.y, slo.z, slo.w}, sh[4] = {shi.x, shi.y, shi.z, shi.w};
     uint32_t ol[4], oh[4];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float2 x = unpack_bf16x2(l[e]), y = unpack_bf16x2(hh[e]);
-      const float2 ca = unpack_bf16x2(cl[e]), cb = unpack_bf16x2(ch[e]);
-      const float2 sa = unpack_bf16x2(sl[e]), sb = unpack_bf16x2(sh[e]);
-      ol[e] = pack_bf16x2(bf16r(bf16r(x.x * ca.x) + bf16r(-y.x * sa.x)), bf16r(bf16r(x.y * ca.y) + bf16r(-y.y * sa.y)));
-      oh[e] = pack_bf16x2(bf16r(bf16r(y.x * cb.x) + bf16r(x.x * sb.x)), bf16r(bf16r(y.y * cb.y) + bf16r(x.y * sb.y)));
-    }
+    for (int e = 0; e < 4; ++e) rerot_pair(l[e], hh[e], cl[e], ch[e], sl[e], sh[e], ol[e], oh[e]);   // same formula as re-rotation
     *reinterpret_cast<uint4*>(dst + c * 8) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
     *reinterpret_cast<uint4*>(dst + half + c * 8) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
   }

@@ -56,20 +56,33 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms DURING the timed region (B200_PROFILING.md).  The
+    process is started - and its first sample awaited - BEFORE the warm-up steps: attaching nvidia-smi to the GPU stalls
+    kernel launches for tens of milliseconds, which used to land inside the timed region (a 10 % error at K = 64).
+    `mark()` is called where the timed region starts; only samples taken after it are reported."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.first = index, None, [], 0
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE, text=True)
-            threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+
+            def pump():
+                for ln in self.proc.stdout:
+                    self.lines.append(ln)
+            threading.Thread(target=pump, daemon=True).start()
+            t0 = time.time()
+            while not self.lines and time.time() - t0 < 10.0 and self.proc.poll() is None:
+                time.sleep(0.01)
         except Exception:
             self.proc = None
+
+    def mark(self):
+        self.first = len(self.lines)
 
     def stop(self):
         if self.proc is None:
@@ -82,7 +95,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        lines = self.lines[self.first:] or self.lines[-1:]      # a region shorter than the sampling period: nearest sample
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
                 continue
@@ -335,13 +349,14 @@ def run_ours(args):
         lib.aha_set_sm_sharing(1)
     for _ in range(prime):       # untimed priming: fills the cache so every timed frame runs the steady-state eviction path
         step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()          # before the warm-up: nvidia-smi's start-up perturbs the GPU, its steady sampling does not
     for _ in range(W):
         step()
     assert all(c.get_seq_length() == (args.window if args.cache != "static" else c.get_seq_length()) for c in caches)
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    sampler.mark()
     launches0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     begin_region(K)              # the timed frames carry exactly their own K frames of vision work
