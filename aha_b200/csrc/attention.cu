@@ -237,7 +237,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tmem_ld_32x32b_x32p(s_addr, sv);
         tmem_ld_32x32b_x32p(s_addr + 32, sv + 32);
         tmem_ld_wait();
-        if (it == 2) { dbg_stamp(ts, 13); }
         if (all_visible && kt * kTile + kTile > seg.klen) {
           // ragged last tile without a causal limit (SigLIP's 729 keys, a full cache): only slots >= klen are masked
           const int nvalid = seg.klen - kt * kTile - col0;
@@ -274,9 +273,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           rescale = true;
         }
         // P smem and O are owned by the tensor pipe until P.V of the previous tile has completed
-        if (it == 2) { dbg_stamp(ts, 14); }
         if (it > 0) mbar_wait(pv_done, (it - 1) & 1);
-        if (it == 2) { dbg_stamp(ts, 15); }
         if (it > 0 && __any_sync(0xffffffffu, rescale)) {
           tc_fence_after();
 #pragma unroll 1
@@ -338,9 +335,45 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // epilogue straight from TMEM: O / l -> bf16 -> out[token, (blk*group + r)*d + c]
       const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
       bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
+      // Staged form (head_dim a multiple of 8, 16-byte aligned rows): the quadrant's 32 x d tile goes through shared
+      // memory (the K ring, idle by now) and leaves as 16-byte pieces in row order - d/8 consecutive pieces per output
+      // row.  One 32-byte store per lane straight from TMEM is 32 separate lines per instruction and cost 2.9 us per CTA.
+      const bool staged = nkt > 0 && (p.d & 7) == 0 && (p.out_ld & 7) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
+      if (staged) {
+        const int pitch = p.d_pad * 2 + 16;
+        uint8_t* tile = sK + ew * 32 * pitch;
+        dbg_stamp(ts, 13);
+#pragma unroll 1
+        for (int cc = half * 16; cc < p.d_pad; cc += 32) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+          tmem_ld_wait();
+          uint32_t w[8];
+#pragma unroll
+          for (int t = 0; t < 8; ++t) w[t] = pack_bf16x2(__uint_as_float(r[2 * t]) * inv, __uint_as_float(r[2 * t + 1]) * inv);
+          uint4* dst = reinterpret_cast<uint4*>(tile + lane * pitch + cc * 2);
+          dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+          dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+        dbg_stamp(ts, 14);
+        asm volatile("bar.sync %0, 64;" ::"r"(2 + ew) : "memory");
+        const int ppr = p.d >> 3;                      // 16-byte pieces per output row
+        for (int i = half * 32 + lane; i < 32 * ppr; i += 64) {
+          const int r_in = i / ppr, pc = i - r_in * ppr;
+          const int mm = qt * kTile + ew * 32 + r_in;
+          if (mm < p.nq_rows) {
+            const int tk = mm / p.group;
+            bf16* o = p.out + (size_t)(seg.out_row0 + tk) * p.out_ld + (size_t)(blk * p.group + (mm - tk * p.group)) * p.d + pc * 8;
+            st_v4(o, *reinterpret_cast<const uint4*>(tile + r_in * pitch + pc * 16));
+          }
+        }
+        dbg_stamp(ts, 11);
+        tc_fence_before();
+      } else {
 #pragma unroll 1
       for (int cc = half * 16; cc < p.d_pad; cc += 32) {
         uint32_t r[16];
+        if (cc == 0) dbg_stamp(ts, 13);
         if (nkt > 0) {
           tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
           tmem_ld_wait();
@@ -348,6 +381,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
           for (int t = 0; t < 16; ++t) r[t] = 0u;
         }
+        if (cc == 0) dbg_stamp(ts, 14);
+        if (cc == 32) dbg_stamp(ts, 15);
         if (row_valid) {
           float v[16];
 #pragma unroll
@@ -364,12 +399,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           }
         }
       }
+      dbg_stamp(ts, 11);
       tc_fence_before();
+      }
     }
   } else {
     // ---- key-split merge through an L2-resident workspace, deterministic split order ----
     // (DSMEM moved these 72 KB per CTA at ~4 B/clk; L2 does it an order of magnitude faster and needs no cluster.)
-    // Every split parks its unnormalised O (fp32 [128][d_pad]) and (m, l), arrives at the counter of its
+    // Every split parks its unnormalised O (fp32, column-major [d_pad][128]) and (m, l), arrives at the counter of its
     // (segment, block, query tile), waits for the other splits - the host keeps the grid co-resident - and then merges
     // the 16-column chunks c with c mod splits == split.
     if (warp >= 4) {
@@ -390,12 +427,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
           for (int t = 0; t < 32; ++t) r[t] = 0u;
         }
-        float4* dst = reinterpret_cast<float4*>(mine + (size_t)row * p.d_pad + cc);
+        // parked column-major ([d_pad][128 rows]): a warp's store (and the merge's load) of one column is one contiguous
+        // 128-byte segment; row-major float4 pieces were 32 separate lines per instruction and cost 2.7 us per CTA
+        float* dst = mine + (size_t)cc * kTile + row;
 #pragma unroll
-        for (int v4 = 0; v4 < 8; ++v4)
-          if (v4 < 4 || two)
-            __stcg(dst + v4, make_float4(__uint_as_float(r[4 * v4]), __uint_as_float(r[4 * v4 + 1]),
-                                         __uint_as_float(r[4 * v4 + 2]), __uint_as_float(r[4 * v4 + 3])));
+        for (int j = 0; j < 32; ++j)
+          if (j < 16 || two) __stcg(dst + (size_t)j * kTile, __uint_as_float(r[j]));
       }
       if (half == 0) {
         __stcg(mine + (size_t)kTile * p.d_pad + row, m_used);
@@ -420,13 +457,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // all loads of a step are issued before the first use (splits beyond `splits` alias split 0 with weight 0); the O
       // pieces of this CTA's first chunk are requested together with the statistics: one L2 round trip, not two
       // (a 16-column chunk is shared by the two threads of a row: 8 columns each)
-      float4 v[8][2];
+      float v[8][8];
       if (split < (p.d_pad >> 4)) {
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
-          const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + split * 16 + half * 8);
+          const float* peer = grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)(split * 16 + half * 8) * kTile + row;
 #pragma unroll
-          for (int v4 = 0; v4 < 2; ++v4) v[s][v4] = __ldcg(peer + v4);
+          for (int j = 0; j < 8; ++j) v[s][j] = __ldcg(peer + (size_t)j * kTile);
         }
       }
       float ms[8], ls[8];
@@ -454,9 +491,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (c != split) {
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
-            const float4* peer = reinterpret_cast<const float4*>(grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)row * p.d_pad + cc);
+            const float* peer = grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)cc * kTile + row;
 #pragma unroll
-            for (int v4 = 0; v4 < 2; ++v4) v[s][v4] = __ldcg(peer + v4);
+            for (int j = 0; j < 8; ++j) v[s][j] = __ldcg(peer + (size_t)j * kTile);
           }
         }
         float acc[8];
@@ -465,12 +502,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
 #pragma unroll
-          for (int v4 = 0; v4 < 2; ++v4) {
-            acc[4 * v4 + 0] += wgt[s] * v[s][v4].x;
-            acc[4 * v4 + 1] += wgt[s] * v[s][v4].y;
-            acc[4 * v4 + 2] += wgt[s] * v[s][v4].z;
-            acc[4 * v4 + 3] += wgt[s] * v[s][v4].w;
-          }
+          for (int j = 0; j < 8; ++j) acc[j] += wgt[s] * v[s][j];
         }
         if (row_valid) {
           if (cc + 8 <= p.d && ((reinterpret_cast<uintptr_t>(orow + cc) & 15) == 0)) {
@@ -562,8 +594,18 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
+  // per-launch timing for bench.py's roofline leg: class 3 = many-tile batched attention (SigLIP), 4 = chunk versus cache
+  ProfSlot* slot = prof_begin(ctas >= sm_count ? 3 : 4, st);
   AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));
   ++g_aha_launch_count;
+  if (slot) {
+    double flops = 0, bytes = 0;
+    for (int i = 0; i < p.n_segs; ++i) {
+      flops += 4.0 * p.n_blocks * (double)p.nq_rows * p.segs[i].klen * p.d;
+      bytes += 2.0 * p.n_blocks * (2.0 * p.nq_rows + 2.0 * p.segs[i].klen) * p.d;
+    }
+    prof_end(slot, st, bytes, flops);
+  }
   AHA_CHECK_LAUNCH();
   return AHA_OK;
 }

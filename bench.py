@@ -398,7 +398,7 @@ def roofline_leg(r, args, peaks):
     r["begin_region"](None)
     r["state"]["overlap"] = was
     out = {}
-    for cls, name in ((0, "skinny"), (1, "tall"), (2, "rerot")):
+    for cls, name in ((0, "skinny"), (1, "tall"), (2, "rerot"), (3, "vattn"), (4, "cattn")):
         ms, cnt, by, fl = ctypes.c_double(), ctypes.c_longlong(), ctypes.c_double(), ctypes.c_double()
         lib.aha_profile_gemm_read(cls, ctypes.byref(ms), ctypes.byref(cnt), ctypes.byref(by), ctypes.byref(fl))
         out[name] = dict(ms=ms.value, launches=cnt.value, bytes=by.value, flops=fl.value)
@@ -425,6 +425,17 @@ def roofline_leg(r, args, peaks):
         tf = tall["flops"] / (tall["ms"] / 1e3) / 1e12
         roof["vision_gemm"] = dict(bound="tensor", achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s",
                                    frac=tf / peaks["tf_sustained"], launches=tall["launches"], ms_per_frame=tall["ms"] / n)
+    va, ca = out["vattn"], out["cattn"]
+    if va["ms"] > 0 and va["launches"]:
+        tf = va["flops"] / (va["ms"] / 1e3) / 1e12
+        roof["vision_attention"] = dict(bound="tensor", kernel="attention_kernel (SigLIP: 729 x 729 x 72, 16 heads x 32 frames per launch)",
+                                        achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s", frac=tf / peaks["tf_sustained"],
+                                        launches=va["launches"], avg_launch_us=va["ms"] * 1e3 / va["launches"],
+                                        ms_per_frame=va["ms"] / n)
+    if ca["ms"] > 0 and ca["launches"]:
+        roof["chunk_attention"] = dict(kernel="attention_kernel (49-token frame chunk x 7 query heads per kv head against the cache, key-split)",
+                                       launches=ca["launches"], avg_launch_us=ca["ms"] * 1e3 / ca["launches"],
+                                       achieved=ca["bytes"] / (ca["ms"] / 1e3) / 1e9, unit="GB/s", ms_per_frame=ca["ms"] / n)
     return roof
 
 

@@ -23,5 +23,5 @@ a = (ctypes.c_ulonglong * 16)()
 A._lib.check(A._lib.load().aha_debug_attention_timeline(a))
 t = list(a)
 names = ["entry", "setup", "pdl_wait", "S0 ready", "P0 written", "S(last) ready", "P(last) written", "O done", "it2 S ready",
-         "it2 P written", "it1 P written", "-", "exit", "it2 tmem loaded", "it2 max done", "it2 pv_done seen"]
+         "it2 P written", "it1 P written", "epilogue stores issued", "exit", "epilogue begins", "O block 0 loaded", "O block 2 loaded"]
 print({n: round((x - t[0]) / 1.965e3, 2) for n, x in zip(names, t) if x})
