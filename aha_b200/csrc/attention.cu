@@ -410,6 +410,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     // (segment, block, query tile), waits for the other splits - the host keeps the grid co-resident - and then merges
     // the 16-column chunks c with c mod splits == split.
     if (warp >= 4) {
+      {   // zero this CTA's slice of the other counter bank (the next split launch on the stream counts in it)
+        const int ncta = gridDim.x * gridDim.y * gridDim.z, cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        for (int z = cta * 256 + (int)threadIdx.x - 128; z < p.ws_zero_n; z += ncta * 256) p.ws_zero[z] = 0;
+      }
       const int group_lin = (seg_idx * gridDim.y + blk) * gridDim.x + qt;
       const size_t cta_floats = (size_t)kTile * p.d_pad + 2 * kTile;
       float* mine = p.ws_partial + ((size_t)group_lin * splits + split) * cta_floats;
@@ -442,7 +446,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       dbg_stamp(ts, 8);
       __threadfence();
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      int* cnt = p.ws_counters + 2 * group_lin;
+      int* cnt = p.ws_counters + group_lin;
       if (threadIdx.x == 128) {
         atomicAdd(cnt, 1);
         uint32_t spins = 0;
@@ -518,8 +522,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
       }
       dbg_stamp(ts, 10);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (threadIdx.x == 128 && atomicAdd(cnt + 1, 1) == splits - 1) { cnt[0] = 0; cnt[1] = 0; }   // last one out re-arms
     }
   }
 
@@ -579,11 +581,13 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
     splits = (max_tiles + per - 1) / per;       // no empty splits for the longest segment
   }
   if (splits > 1) {
-    GemmSplitScratch sc;
-    rc = aha_split_scratch(st, &sc); if (rc) return rc;
     const size_t need = (size_t)ctas * splits * ((size_t)kTile * p.d_pad + 2 * kTile) * sizeof(float);
     if (need > GemmWorkspace::kPartialBytes || ctas > GemmWorkspace::kCounters) splits = 1;
-    p.ws_partial = sc.partial; p.ws_counters = sc.counters;
+  }
+  if (splits > 1) {
+    GemmSplitScratch sc;
+    rc = aha_split_scratch(st, &sc); if (rc) return rc;     // advances the stream's counter bank: only for a real split launch
+    p.ws_partial = sc.partial; p.ws_counters = sc.bank; p.ws_zero = sc.zero; p.ws_zero_n = sc.zero_n;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(q_tiles, p.n_blocks, p.n_segs * splits);

@@ -27,7 +27,9 @@ struct GemmParams {
   int dbg;              // bring-up knob (AHA_GEMM_DBG): 1 = return at entry, 2 = skip epilogue math/stores
   int ring, ring_deep, ring_shallow;   // operand-ring stages actually used (0 = all the kernel variant has)
   float* ws_partial;    // split-K workspace: [tile][split][BN][128] fp32 partial tiles
-  int* ws_counters;     // split-K arrival counter per tile (zero between launches)
+  int* ws_counters;     // split-K arrival counter per tile, in this launch's counter bank (zero on entry)
+  int* ws_zero;         // the OTHER counter bank, ws_zero_n ints: this launch zeroes it for the next split launch
+  int ws_zero_n;
   unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
   L2Prefetch pf;        // weights of LATER kernels to request into L2 once this CTA's own loads are in flight
 };
@@ -49,19 +51,30 @@ struct GemmCall {
 };
 
 // Split-K scratch is per CUDA stream (launches on one stream are ordered; two streams must not share counters).
-struct GemmSplitScratch { float* partial = nullptr; int* counters = nullptr; };
+// Arrival counters live in two banks that successive split launches of a stream (GEMM or attention) alternate between:
+// a launch counts arrivals in its bank and zeroes the other one for its successor, so no CTA has to find out that it
+// is the last one out (that took an atomic with a return value - a full L2 round trip at the very end of every
+// split kernel, in front of the dependent launch).  Inside a bank the GEMM uses [0, kCounters), attention the rest.
+struct GemmSplitScratch {
+  float* partial = nullptr;
+  int* counters = nullptr;       // all banks (allocation base)
+  int* bank = nullptr;           // this launch's bank
+  int* zero = nullptr;           // the bank to zero
+  int zero_n = 0;
+  unsigned long long seq = 0;    // split launches so far on this stream
+};
 struct GemmWorkspace {
   int sm_count = 148;
   static constexpr size_t kPartialBytes = 64u << 20;
-  static constexpr int kCounters = 8192;
+  static constexpr int kCounters = 1024;
   std::map<cudaStream_t, GemmSplitScratch> scratch;
   std::mutex mu;
 };
 
 int gemm_workspace_create(GemmWorkspace* w, int device);
 bool aha_sm_shared();   // aha_set_sm_sharing(1) is in effect
-// Per-stream split scratch of the default workspace: 64 MB of fp32 partials and 2 x kCounters zeroed arrival counters
-// (the GEMM uses counters [0, kCounters), the attention merge [kCounters, 2 * kCounters)).
+// Per-stream split scratch of the default workspace for ONE split launch (every call advances the stream's bank
+// sequence: call it only when the split kernel is really launched).  out->bank points at the attention half.
 int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out);
 void gemm_workspace_destroy(GemmWorkspace* w);
 // Enqueues the GEMM on `stream`. Returns AHA_OK or a negative error code.

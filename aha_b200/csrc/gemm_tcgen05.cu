@@ -91,9 +91,22 @@ __device__ __forceinline__ float apply_act(float x) {   // x is already bf16-rou
 
 // Skinny orientation, 16 tokens of one feature row (thread = feature).  Lanes hold consecutive features, so every
 // per-token access of a warp is one contiguous 64-byte (bf16) or 128-byte (fp32) segment.
+// raw bf16 bits: converting at the load would make the loading thread wait for the data right there
+__device__ __forceinline__ void load_residual16(const GemmParams& p, int feat, int tok0, uint16_t (&r)[16]) {
+  const int ntok = min(16, p.Nb - tok0);
+  const uint16_t* res = reinterpret_cast<const uint16_t*>(p.residual);
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const int token = tok0 + t;
+    const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
+    r[t] = (t < ntok) ? res[(size_t)rrow * p.ldr + feat] : (uint16_t)0;
+  }
+}
+
+// `pre_res`: the 16 residual values when the caller has already requested them (split-K: during the arrival wait)
 template <int kAct>
 __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool fvalid, float bias, int i, int tok0,
-                                           float (&acc)[16]) {
+                                           float (&acc)[16], const uint16_t* pre_res = nullptr) {
   const bool round_out = !p.out_f32 || p.round_bf16;
 #pragma unroll
   for (int t = 0; t < 16; ++t) acc[t] += bias;
@@ -127,13 +140,16 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
   if (!fvalid) return;
   if (p.residual) {
     // all loads first (they may alias the output elements written below, by this same thread only)
+    uint16_t raw[16];
+    if (pre_res) {
+#pragma unroll
+      for (int t = 0; t < 16; ++t) raw[t] = pre_res[t];
+    } else {
+      load_residual16(p, feat, tok0, raw);
+    }
     float r[16];
 #pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const int token = tok0 + t;
-      const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
-      r[t] = (t < ntok) ? b2f(p.residual[(size_t)rrow * p.ldr + feat]) : 0.f;
-    }
+    for (int t = 0; t < 16; ++t) r[t] = __uint_as_float((uint32_t)raw[t] << 16);
 #pragma unroll
     for (int t = 0; t < 16; t += 2) {
       acc[t] = r[t] + acc[t]; acc[t + 1] = r[t + 1] + acc[t + 1];
@@ -215,6 +231,21 @@ __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* 
     }
   }
   __syncwarp();
+}
+
+// Split-K merge of one 16-column chunk: the partials of all S splits are requested before the first use (one L2 round
+// trip whatever S is) and added in split order, which keeps the result deterministic.
+template <int S>
+__device__ __forceinline__ void reduce_splits16(const float* base, size_t split_stride, float (&acc)[16]) {
+  float v[S][16];
+#pragma unroll
+  for (int sp = 0; sp < S; ++sp)
+#pragma unroll
+    for (int t = 0; t < 16; ++t) v[sp][t] = __ldcg(base + (size_t)sp * split_stride + t * kBlockM);
+#pragma unroll
+  for (int sp = 0; sp < S; ++sp)
+#pragma unroll
+    for (int t = 0; t < 16; ++t) acc[t] += v[sp][t];
 }
 
 // the staged skinny epilogue needs a fully valid feature tile and 16-byte aligned bf16 rows
@@ -599,6 +630,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       // 128-byte line), then the last CTA to arrive at the tile's counter reduces in split order.
       const int tile_lin = blockIdx.y * gridDim.x + blockIdx.x;
       const int ncols = min(BN, p.Nb - b0);
+      {   // zero this CTA's slice of the other counter bank (the next split launch on the stream counts in it)
+        const int ncta = gridDim.x * gridDim.y * gridDim.z, cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        for (int z = cta * 128 + (int)threadIdx.x - 128; z < p.ws_zero_n; z += ncta * 128) p.ws_zero[z] = 0;
+      }
       float* part = p.ws_partial + ((size_t)tile_lin * p.splits + split) * (size_t)(BN * kBlockM) + i;
 #pragma unroll 1
       for (int jc = 0; jc < ncols; jc += 16) {
@@ -609,13 +644,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         for (int t = 0; t < 16; ++t) __stcg(part + (jc + t) * kBlockM, __uint_as_float(r[t]));
       }
       dbg_stamp(ts, 4);
+      const int feat = a0 + i;
+      const bool fvalid = feat < p.Ma;
+      uint16_t res[16];
+      const bool pre_res = kSwap && p.residual != nullptr && fvalid && split * 16 < ncols;
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      int* cnt = p.ws_counters + 2 * tile_lin;
+      int* cnt = p.ws_counters + tile_lin;
+      if (threadIdx.x == 128) atomicAdd(cnt, 1);   // arrive (result unused: a fire-and-forget reduction)
+      // the residual of this split's first chunk does not depend on the other splits: its loads fly during the wait
+      // (after the arrival - the fence in front of it would have waited for them)
+      if (pre_res) load_residual16(p, feat, b0 + split * 16, res);
       if (threadIdx.x == 128) {
-        // arrive, then wait for the other splits of this tile.  All CTAs of a split grid are co-resident (the host keeps
+        // wait for the other splits of this tile.  All CTAs of a split grid are co-resident (the host keeps
         // tiles*splits within the device's resident-CTA capacity), so the wait cannot deadlock; it is bounded anyway.
-        atomicAdd(cnt, 1);
         uint32_t spins = 0;
         while (*reinterpret_cast<volatile int*>(cnt) < p.splits) {
           if (++spins > (1u << 24)) { printf("aha_b200: split-K arrival wait timed out (tile %d)\n", tile_lin); __trap(); }
@@ -626,29 +668,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       dbg_stamp(ts, 5);
       // 16-column chunk c is reduced (in split order 0..s-1: deterministic) and finished by split (c mod splits)
       const float* base = p.ws_partial + (size_t)tile_lin * p.splits * (size_t)(BN * kBlockM) + i;
-      const int feat = a0 + i;
-      const bool fvalid = feat < p.Ma;
       const float bias = (kSwap && p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
-      const bool staged = kSwap && swap_staged_ok(p, a0);
+      constexpr size_t kSplitStride = (size_t)BN * kBlockM;
 #pragma unroll 1
       for (int jc = split * 16; jc < ncols; jc += 16 * p.splits) {
         float acc[16];
 #pragma unroll
         for (int t = 0; t < 16; ++t) acc[t] = 0.f;
-#pragma unroll 4
-        for (int sp = 0; sp < p.splits; ++sp) {
-          const float* pp = base + (size_t)sp * (BN * kBlockM) + jc * kBlockM;
-          float v[16];
-#pragma unroll
-          for (int t = 0; t < 16; ++t) v[t] = __ldcg(pp + t * kBlockM);
-#pragma unroll
-          for (int t = 0; t < 16; ++t) acc[t] += v[t];
+        const float* pp = base + jc * kBlockM;
+        switch (p.splits) {
+          case 2: reduce_splits16<2>(pp, kSplitStride, acc); break;
+          case 3: reduce_splits16<3>(pp, kSplitStride, acc); break;
+          case 4: reduce_splits16<4>(pp, kSplitStride, acc); break;
+          case 5: reduce_splits16<5>(pp, kSplitStride, acc); break;
+          case 6: reduce_splits16<6>(pp, kSplitStride, acc); break;
+          default:
+#pragma unroll 1
+            for (int sp = 0; sp < p.splits; sp += 4) {     // four splits in flight at a time
+              if (sp + 4 <= p.splits) reduce_splits16<4>(pp + (size_t)sp * kSplitStride, kSplitStride, acc);
+              else for (int q = sp; q < p.splits; ++q) reduce_splits16<1>(pp + (size_t)q * kSplitStride, kSplitStride, acc);
+            }
         }
-        if (kSwap) epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+        if (kSwap) epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc, (pre_res && jc == split * 16) ? res : nullptr);
         else epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (threadIdx.x == 128 && atomicAdd(cnt + 1, 1) == p.splits - 1) { cnt[0] = 0; cnt[1] = 0; }   // last one out re-arms
     }
     tc_fence_before();
     dbg_stamp(ts, 6);
@@ -1025,7 +1068,12 @@ static int split_scratch(GemmWorkspace* w, cudaStream_t st, GemmSplitScratch* ou
     AHA_CUDA(cudaMemsetAsync(s.counters, 0, 4 * GemmWorkspace::kCounters * sizeof(int), st));
     it = w->scratch.emplace(st, s).first;
   }
-  *out = it->second;
+  GemmSplitScratch& s = it->second;
+  const int bank = (int)(s.seq++ & 1);
+  *out = s;
+  out->bank = s.counters + bank * 2 * GemmWorkspace::kCounters;
+  out->zero = s.counters + (bank ^ 1) * 2 * GemmWorkspace::kCounters;
+  out->zero_n = 2 * GemmWorkspace::kCounters;
   return AHA_OK;
 }
 
@@ -1036,7 +1084,7 @@ int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out) {
   if (!w) return rc;
   rc = split_scratch(w, st, out);
   if (rc) return rc;
-  out->counters += 2 * GemmWorkspace::kCounters;
+  out->bank += GemmWorkspace::kCounters;
   return AHA_OK;
 }
 
@@ -1156,7 +1204,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   if (splits > 1) {
     GemmSplitScratch sc;
     int src = split_scratch(w, stream, &sc); if (src) return src;
-    p.ws_partial = sc.partial; p.ws_counters = sc.counters;
+    p.ws_partial = sc.partial; p.ws_counters = sc.bank; p.ws_zero = sc.zero; p.ws_zero_n = sc.zero_n;
   }
   CUtensorMap ta, tb;
   int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;

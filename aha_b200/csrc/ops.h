@@ -54,7 +54,9 @@ struct AttnProblem {
   L2Prefetch pf;            // weights of later kernels to request into L2 (common.cuh)
   unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
   float* ws_partial;        // key-split scratch (filled in by op_attention): per CTA [128][d_pad] fp32 O, then m[128], l[128]
-  int* ws_counters;         // arrival / departure counter pair per (segment, block, query tile)
+  int* ws_counters;         // arrival counter per (segment, block, query tile) in this launch's bank (see gemm.h)
+  int* ws_zero;             // the other counter bank, zeroed by this launch
+  int ws_zero_n;
   int no_split;             // 1: never split the key axis (the kernel's splits wait for each other; see gemm_bf16)
   int pf_early;             // 1: request them at kernel entry, 0: after this CTA's own K/V loads are in flight
   int n_segs;
