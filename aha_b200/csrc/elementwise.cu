@@ -392,6 +392,64 @@ __global__ void __launch_bounds__(256) layernorm_warp_kernel(const bf16* __restr
   }
 }
 
+// ---- folded RMSNorm helpers (see GemmCall in gemm.h) ----
+// row copy + sum of squares of the copied row (the residual stream entering layer 0): block per row
+__global__ void __launch_bounds__(256) copy_sumsq_kernel(const bf16* __restrict__ x, bf16* __restrict__ out,
+                                                         float* __restrict__ sumsq, int cols) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ float red[8];
+  const uint4* src = reinterpret_cast<const uint4*>(x + (size_t)blockIdx.x * cols);
+  uint4* dst = reinterpret_cast<uint4*>(out + (size_t)blockIdx.x * cols);
+  float s = 0.f;
+  for (int c = threadIdx.x; c < (cols >> 3); c += blockDim.x) {
+    const uint4 u = src[c];
+    dst[c] = u;
+    const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), d = unpack_bf16x2(u.z), e = unpack_bf16x2(u.w);
+    s += a.x * a.x + a.y * a.y + b.x * b.x + b.y * b.y + d.x * d.x + d.y * d.y + e.x * e.x + e.y * e.y;
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+    sumsq[blockIdx.x] = t;
+  }
+}
+
+// W[r][c] = bf16(W[r][c] * v[c]): the norm weight folded into the columns of the matrix that consumes the normalised row
+__global__ void fold_columns_kernel(bf16* __restrict__ w, const bf16* __restrict__ v, long long rows, int cols) {
+  const long long n = rows * (long long)(cols >> 3);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % (cols >> 3));
+    uint4 u = reinterpret_cast<uint4*>(w)[i];
+    const uint4 s = reinterpret_cast<const uint4*>(v)[c];
+    uint32_t a[4] = {u.x, u.y, u.z, u.w};
+    const uint32_t b[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(a[e]), y = unpack_bf16x2(b[e]);
+      a[e] = pack_bf16x2(x.x * y.x, x.y * y.y);
+    }
+    reinterpret_cast<uint4*>(w)[i] = make_uint4(a[0], a[1], a[2], a[3]);
+  }
+}
+
+int op_copy_sumsq(const bf16* x, bf16* out, float* sumsq, int rows, int cols, cudaStream_t st) {
+  AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0, "copy_sumsq: bad shape");
+  return launch_pdl(copy_sumsq_kernel, dim3(rows), dim3(256), 0, st, x, out, sumsq, cols);
+}
+
+int op_fold_columns(bf16* w, const bf16* v, long long rows, int cols, cudaStream_t st) {
+  AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0, "fold_columns: bad shape");
+  const long long n = rows * (long long)(cols >> 3);
+  const int blocks = (int)std::min<long long>((n + 255) / 256, 148 * 8);
+  fold_columns_kernel<<<blocks, 256, 0, st>>>(w, v, rows, cols);
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
 int op_rmsnorm(const bf16* x, const bf16* w, bf16* out, int rows, int cols, float eps, cudaStream_t st) {
   AHA_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= kNormThreads * kNormMaxVec * 8, "rmsnorm: bad shape");
   return launch_pdl(norm_kernel<false>, dim3(rows), dim3(kNormThreads), 0, st, x, w, (const bf16*)nullptr, out, cols, eps);

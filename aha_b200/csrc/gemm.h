@@ -32,6 +32,12 @@ struct GemmParams {
   int ws_zero_n;
   unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
   L2Prefetch pf;        // weights of LATER kernels to request into L2 once this CTA's own loads are in flight
+  // RMSNorm folded around the GEMMs (skinny orientation only, see GemmCall):
+  const float* rs_partials;   // consumer: sum over i < rs_n of rs_partials[i * rs_ld + token] = sum of squares of the row
+  int rs_n, rs_ld;
+  float rs_eps, rs_inv_cols;  // out = rsqrt(sumsq * rs_inv_cols + rs_eps) * (x . W^T) (+ bias ...)
+  float* sumsq_out;           // producer: sumsq_out[feature_tile * sumsq_ld + token] = sum of out[token, f]^2 over the tile
+  int sumsq_ld;
 };
 
 // Description of one GEMM call as the model layers see it:  out[tokens, features] = X[tokens, K] . W[features, K]^T
@@ -48,6 +54,14 @@ struct GemmCall {
   int force_splits;  // 0 auto
   int force_deep;    // -1 auto, 0 two CTAs per SM, 1 one CTA per SM with the deep operand ring (skinny only)
   L2Prefetch pf;     // see common.cuh (all zero: nothing to prefetch)
+  // RMSNorm without a kernel of its own (tokens <= 256, no GELU: the skinny orientation).  The norm's per-token factor
+  // commutes with the GEMM that consumes the normalised row, so the CONSUMER multiplies its accumulators by
+  // rsqrt(mean(x^2) + eps) in the epilogue (its weight matrix has the norm weight folded into its columns) and reads the
+  // raw residual stream; the sum of squares comes from the PRODUCER of that stream, whose epilogue adds up the squares
+  // of the bf16 values it stores, one partial per 128-feature tile (summed in tile order: deterministic).
+  const float* rs_partials; int rs_n; int rs_ld; float rs_eps;   // consumer side (rs_partials null: off); mean over K
+  float* sumsq_out; int sumsq_ld;                                // producer side (null: off)
+  int* sumsq_tiles;                                              // out: partial rows the producer writes per token
 };
 
 // Split-K scratch is per CUDA stream (launches on one stream are ordered; two streams must not share counters).

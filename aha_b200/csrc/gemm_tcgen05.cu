@@ -233,6 +233,23 @@ __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* 
   __syncwarp();
 }
 
+// Producer side of the folded RMSNorm: acc holds the 16 bf16 values (as floats) this thread has just stored for its
+// feature; their squares are summed over the tile's 128 features (shuffles, then the four warps through shared memory)
+// and the tile's partial goes to sumsq_out[feature tile][token].  Called by all four epilogue warps together.
+__device__ __forceinline__ void emit_sumsq16(const GemmParams& p, float (*sq_red)[16], const float (&acc)[16], bool fvalid,
+                                             int ew, int lane, int tok0) {
+  const int ntok = min(16, p.Nb - tok0);
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const float s = warp_sum(fvalid ? acc[t] * acc[t] : 0.f);
+    if (lane == 0) sq_red[ew][t] = s;
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  if (ew == 0 && lane < ntok)
+    p.sumsq_out[(size_t)blockIdx.x * p.sumsq_ld + tok0 + lane] = sq_red[0][lane] + sq_red[1][lane] + sq_red[2][lane] + sq_red[3][lane];
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+}
+
 // Split-K merge of one 16-column chunk: the partials of all S splits are requested before the first use (one L2 round
 // trip whatever S is) and added in split order, which keeps the result deterministic.
 template <int S>
@@ -482,6 +499,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     const GemmParams p) {
   using C = Cfg<BN, kDeep>;
   extern __shared__ uint8_t smem_raw[];
+  __shared__ float rstd_s[kSwap ? BN : 1];    // folded RMSNorm: per-token factor of this CTA's token columns
+  __shared__ float sq_red[4][16];             // folded RMSNorm: cross-warp sum of squares
   // SWIZZLE_128B tiles need 1024-byte alignment.
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
@@ -583,6 +602,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     dbg_stamp(ts, 1);
     pdl_wait();   // the epilogue reads residuals and writes outputs that earlier kernels may still be using
     dbg_stamp(ts, 2);
+    if (kSwap && p.rs_partials) {
+      // per-token RMSNorm factor of this CTA's token columns, while the main loop streams the weights
+      for (int t = threadIdx.x - 128; t < BN; t += 128) {
+        const int token = b0 + t;
+        float sum = 0.f;
+        if (token < p.Nb)
+          for (int r = 0; r < p.rs_n; ++r) sum += __ldcg(p.rs_partials + (size_t)r * p.rs_ld + token);
+        rstd_s[t] = rsqrtf(sum * p.rs_inv_cols + p.rs_eps);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     mbar_wait(accum_bar, 0);
     tc_fence_after();
     dbg_stamp(ts, 3);
@@ -593,7 +623,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const int feat = a0 + i;
         const bool fvalid = feat < p.Ma;
         const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
-        const bool staged = swap_staged_ok(p, a0);
+        const bool staged = swap_staged_ok(p, a0) && !p.sumsq_out;
         // the operand ring is idle by now (accum_bar fired after the last MMA read it): 2 KB of it per warp stage the stores
         uint8_t* stage_warp = smem + ew * 2048;
 #pragma unroll 1
@@ -606,8 +636,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           float acc[16];
 #pragma unroll
           for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
+          if (p.rs_partials) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] *= rstd_s[jc + t];
+          }
           if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
           else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+          if (p.sumsq_out) emit_sumsq16(p, sq_red, acc, fvalid, ew, lane, b0 + jc);
           dbg_stamp(ts, 9 + (jc >> 4) * 2);
         }
       } else if (p.out_f32) {
@@ -689,8 +724,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
               else for (int q = sp; q < p.splits; ++q) reduce_splits16<1>(pp + (size_t)q * kSplitStride, kSplitStride, acc);
             }
         }
+        if (kSwap && p.rs_partials) {
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] *= rstd_s[jc + t];
+        }
         if (kSwap) epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc, (pre_res && jc == split * 16) ? res : nullptr);
         else epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
+        if (kSwap && p.sumsq_out) emit_sumsq16(p, sq_red, acc, fvalid, ew, lane, b0 + jc);
       }
     }
     tc_fence_before();
@@ -1103,6 +1143,13 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   p.K = c.K; p.swap = swap;
   p.out = c.out; p.ldo = c.ldo; p.out_f32 = c.out_f32; p.round_bf16 = c.round_bf16; p.act = c.act;
   p.bias = c.bias; p.residual = c.residual; p.ldr = c.ldr; p.res_mod = c.res_mod;
+  if (c.rs_partials || c.sumsq_out) {
+    AHA_REQUIRE(swap && c.act != GEMM_ACT_GELU_TANH && c.act != GEMM_ACT_GELU_ERF, "folded RMSNorm needs the skinny orientation (tokens <= 256)");
+    AHA_REQUIRE(!c.rs_partials || (c.rs_n > 0 && c.rs_ld >= c.tokens), "folded RMSNorm: bad partial-sum layout");
+    AHA_REQUIRE(!c.sumsq_out || (c.sumsq_ld >= c.tokens && !c.out_f32 && c.act == GEMM_ACT_NONE), "folded RMSNorm: bad sum-of-squares output");
+    p.rs_partials = c.rs_partials; p.rs_n = c.rs_n; p.rs_ld = c.rs_ld; p.rs_eps = c.rs_eps; p.rs_inv_cols = 1.0f / (float)c.K;
+    p.sumsq_out = c.sumsq_out; p.sumsq_ld = c.sumsq_ld;
+  }
   p.pf = c.pf;
   const void* a; const void* b; int lda, ldb;
   if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
@@ -1151,6 +1198,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM;
   const int tiles_b = (p.Nb + bn - 1) / bn;
   const int tiles = tiles_a * tiles_b;
+  if (c.sumsq_tiles) *c.sumsq_tiles = tiles_a;
   const int kb_total = (p.K + kBlockK - 1) / kBlockK;
   int splits = c.force_splits;
   int deep = c.force_deep;

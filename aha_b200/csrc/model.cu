@@ -81,6 +81,14 @@ struct aha_model_s {
   // decoder workspaces (max_tokens)
   bf16 *ws_x = nullptr, *ws_h = nullptr, *ws_qkv = nullptr, *ws_qbuf = nullptr, *ws_attn = nullptr, *ws_act = nullptr,
        *ws_cos = nullptr, *ws_sin = nullptr, *ws_hn = nullptr;
+  // RMSNorm folded around the decoder GEMMs (gemm.h, GemmCall): the norm weights are folded into the columns of the
+  // qkv and gate|up matrices at load time; `ones` is the weight of the stand-alone norm kernel that the tall
+  // orientation (more than 256 tokens per call) still runs, ws_ss_a / ws_ss_b hold the per-tile sums of squares of
+  // the residual stream in front of the attention / the MLP block ([kSsTiles][max_tokens] floats each)
+  bool fold_norm = false;
+  bf16* ones = nullptr;
+  float *ws_ss_a = nullptr, *ws_ss_b = nullptr;
+  static constexpr int kSsTiles = 64;
 };
 
 namespace {
@@ -179,6 +187,17 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
   TRY(copy_w(m, wt, "relevance_head.weight", 1, H, &m->w_rel));
   TRY(copy_w(m, wt, "uncertainty_head.weight", 1, H, &m->w_unc));
   const int qd = d.heads * d.head_dim, kd = d.kv_heads * d.head_dim;
+  {
+    static const int fold_env = getenv("AHA_FOLD_NORM") ? atoi(getenv("AHA_FOLD_NORM")) : 1;
+    m->fold_norm = fold_env != 0 && H % 128 == 0 && H / 128 <= aha_model_s::kSsTiles;
+    if (m->fold_norm) {
+      std::vector<uint16_t> one(H, (uint16_t)0x3F80);    // bf16 1.0
+      TRY(dev_alloc_t(m, &m->ones, (size_t)H));
+      AHA_CUDA(cudaMemcpy(m->ones, one.data(), (size_t)H * 2, cudaMemcpyHostToDevice));
+      TRY(dev_alloc_t(m, &m->ws_ss_a, (size_t)aha_model_s::kSsTiles * d.max_tokens));
+      TRY(dev_alloc_t(m, &m->ws_ss_b, (size_t)aha_model_s::kSsTiles * d.max_tokens));
+    }
+  }
   m->dl.resize(d.layers);
   for (int l = 0; l < d.layers; ++l) {
     const std::string p = "model.layers." + std::to_string(l) + ".";
@@ -196,6 +215,7 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
     AHA_CUDA(cudaMemcpy(w.qkv_b, qb, (size_t)qd * 2, cudaMemcpyDeviceToDevice));
     AHA_CUDA(cudaMemcpy(w.qkv_b + qd, kb, (size_t)kd * 2, cudaMemcpyDeviceToDevice));
     AHA_CUDA(cudaMemcpy(w.qkv_b + qd + kd, vb, (size_t)kd * 2, cudaMemcpyDeviceToDevice));
+    if (m->fold_norm) TRY(op_fold_columns(w.qkv_w, w.in_ln, m->qkv_cols, H, 0));
     TRY(copy_w(m, wt, p + "self_attn.o_proj.weight", H, qd, &w.o_w));
     TRY(copy_w(m, wt, p + "post_attention_layernorm.weight", 1, H, &w.post_ln));
     // gate / up rows interleaved (gate f -> row 2f, up f -> row 2f+1): the SiLU*mul epilogue then finds both
@@ -205,6 +225,7 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
     TRY(dev_alloc_t(m, &w.gu_w, (size_t)2 * d.inter * H));
     TRY(op_copy_rows(gw, H, w.gu_w, H, d.inter, H, 0, 2, 0));
     TRY(op_copy_rows(uw, H, w.gu_w, H, d.inter, H, 1, 2, 0));
+    if (m->fold_norm) TRY(op_fold_columns(w.gu_w, w.post_ln, 2LL * d.inter, H, 0));
     TRY(copy_w(m, wt, p + "mlp.down_proj.weight", H, d.inter, &w.down_w));
   }
   for (int l = 0; l < d.layers; ++l) {
@@ -257,9 +278,12 @@ int build_model(aha_model_s* m, const WeightTable& wt) {
 
 namespace {
 
+// folded RMSNorm arguments of one GEMM (gemm.h): consumer side (rs, rs_n) and / or producer side (ss_out, ss_tiles)
+struct NormFold { const float* rs; int rs_n; float* ss_out; int* ss_tiles; int ld; float eps; };
+
 int linear(const bf16* x, int tokens, int ldx, const bf16* w, int features, int K, void* out, int ldo, int act,
            const bf16* bias, const bf16* residual, int ldr, int res_mod, int out_f32, cudaStream_t st,
-           const L2Prefetch* pf = nullptr) {
+           const L2Prefetch* pf = nullptr, const NormFold* nf = nullptr) {
   int rc;
   GemmWorkspace* ws = aha_default_workspace(&rc);
   if (!ws) return rc;
@@ -268,6 +292,10 @@ int linear(const bf16* x, int tokens, int ldx, const bf16* w, int features, int 
   c.out = out; c.ldo = ldo; c.out_f32 = out_f32; c.round_bf16 = out_f32; c.act = act; c.bias = bias;
   c.residual = residual; c.ldr = ldr; c.res_mod = res_mod; c.force_swap = -1; c.force_bn = 0; c.force_splits = 0; c.force_deep = -1;
   if (pf) c.pf = *pf;
+  if (nf) {
+    c.rs_partials = nf->rs; c.rs_n = nf->rs_n; c.rs_ld = nf->ld; c.rs_eps = nf->eps;
+    c.sumsq_out = nf->ss_out; c.sumsq_ld = nf->ld; c.sumsq_tiles = nf->ss_tiles;
+  }
   return gemm_bf16(c, ws, st);
 }
 
@@ -346,7 +374,12 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
     for (int l = 0; l < d.layers; ++l) TRY(cache_compact(c, l, plans[s], st));
     TRY(cache_rerotate(c, 0, d.layers, plans[s], st));   // every layer's kept keys in one launch
   }
-  AHA_CUDA(cudaMemcpyAsync(m->ws_x, x_in, (size_t)M * H * sizeof(bf16), cudaMemcpyDeviceToDevice, st));
+  // RMSNorm folded around the GEMMs when the call runs in the skinny orientation (at most 256 tokens)
+  const bool fold = m->fold_norm && M <= 256;
+  int ss_na = 1, ss_nb = 1;          // partial rows per token in ws_ss_a / ws_ss_b
+  if (fold) TRY(op_copy_sumsq(x_in, m->ws_x, m->ws_ss_a, M, H, st));
+  else AHA_CUDA(cudaMemcpyAsync(m->ws_x, x_in, (size_t)M * H * sizeof(bf16), cudaMemcpyDeviceToDevice, st));
+  const int ss_ld = d.max_tokens;
   AttnProblem ap{};
   ap.q = m->ws_qbuf; ap.q_rows_total = M * nh; ap.q_ld = hd;
   ap.q_col0 = ap.k_col0 = ap.v_col0 = 0; ap.q_col_step = ap.k_col_step = ap.v_col_step = 0;
@@ -360,12 +393,15 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
   static const int skip = getenv("AHA_SKIP") ? atoi(getenv("AHA_SKIP")) : 0;
   for (int l = 0; l < d.layers; ++l) {
     const DecoderLayerW& w = m->dl[l];
-    if (!(skip & 1)) TRY(op_rmsnorm(m->ws_x, w.in_ln, m->ws_h, M, H, d.rms_eps, st));
+    if (!fold && !(skip & 1)) TRY(op_rmsnorm(m->ws_x, m->fold_norm ? m->ones : w.in_ln, m->ws_h, M, H, d.rms_eps, st));
     WeightStream& wsm = m->wstream;
     static const int pf_gemm = getenv("AHA_PF_GEMM") ? atoi(getenv("AHA_PF_GEMM")) : 1;
     auto take_g = [&](int seg) { return pf_gemm ? wsm.take(wsm.end_of(seg)) : L2Prefetch{}; };
     L2Prefetch pf = take_g(4 * l);
-    if (!(skip & 8)) TRY(linear(m->ws_h, M, H, w.qkv_w, m->qkv_cols, H, m->ws_qkv, m->qkv_cols, GEMM_ACT_NONE, w.qkv_b, nullptr, 0, 0, 0, st, &pf));
+    const NormFold nf_qkv{m->ws_ss_a, ss_na, nullptr, nullptr, ss_ld, d.rms_eps};
+    const NormFold nf_o{nullptr, 0, m->ws_ss_b, &ss_nb, ss_ld, d.rms_eps};
+    const NormFold nf_down{nullptr, 0, m->ws_ss_a, &ss_na, ss_ld, d.rms_eps};
+    if (!(skip & 8)) TRY(linear(fold ? m->ws_x : m->ws_h, M, H, w.qkv_w, m->qkv_cols, H, m->ws_qkv, m->qkv_cols, GEMM_ACT_NONE, w.qkv_b, nullptr, 0, 0, 0, st, &pf, fold ? &nf_qkv : nullptr));
     RopeAppendArgs aa{};
     int cap = caches[0]->cap;
     for (int s = 0; s < ns; ++s) {
@@ -395,12 +431,13 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
       if (!(skip & 4)) TRY(op_attention(ap, st));
     }
     pf = take_g(4 * l + 1);
-    if (!(skip & 16)) TRY(linear(m->ws_attn, M, qd, w.o_w, H, qd, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf));
-    if (!(skip & 1)) TRY(op_rmsnorm(m->ws_x, w.post_ln, m->ws_h, M, H, d.rms_eps, st));
+    if (!(skip & 16)) TRY(linear(m->ws_attn, M, qd, w.o_w, H, qd, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf, fold ? &nf_o : nullptr));
+    if (!fold && !(skip & 1)) TRY(op_rmsnorm(m->ws_x, m->fold_norm ? m->ones : w.post_ln, m->ws_h, M, H, d.rms_eps, st));
     pf = take_g(4 * l + 2);
-    if (!(skip & 32)) TRY(linear(m->ws_h, M, H, w.gu_w, 2 * d.inter, H, m->ws_act, d.inter, GEMM_ACT_SILU_MUL, nullptr, nullptr, 0, 0, 0, st, &pf));
+    const NormFold nf_gu2{m->ws_ss_b, ss_nb, nullptr, nullptr, ss_ld, d.rms_eps};
+    if (!(skip & 32)) TRY(linear(fold ? m->ws_x : m->ws_h, M, H, w.gu_w, 2 * d.inter, H, m->ws_act, d.inter, GEMM_ACT_SILU_MUL, nullptr, nullptr, 0, 0, 0, st, &pf, fold ? &nf_gu2 : nullptr));
     pf = take_g(4 * l + 3);
-    if (!(skip & 64)) TRY(linear(m->ws_act, M, d.inter, w.down_w, H, d.inter, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf));
+    if (!(skip & 64)) TRY(linear(m->ws_act, M, d.inter, w.down_w, H, d.inter, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf, fold ? &nf_down : nullptr));
   }
   m->wstream.end_step();
   bf16* hn = hidden_out ? hidden_out : m->ws_hn;

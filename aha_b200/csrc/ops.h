@@ -5,6 +5,9 @@
 
 // ---- elementwise.cu ----
 int op_rmsnorm(const bf16* x, const bf16* w, bf16* out, int rows, int cols, float eps, cudaStream_t st);
+// folded RMSNorm (gemm.h, GemmCall): out = x and sumsq[row] = sum of x[row, :]^2 ; W[:, c] *= v[c]
+int op_copy_sumsq(const bf16* x, bf16* out, float* sumsq, int rows, int cols, cudaStream_t st);
+int op_fold_columns(bf16* w, const bf16* v, long long rows, int cols, cudaStream_t st);
 int op_layernorm(const bf16* x, const bf16* w, const bf16* b, bf16* out, int rows, int cols, float eps, cudaStream_t st);
 int op_preprocess(const uint8_t* in, bf16* out, long long n, cudaStream_t st);
 // frames [n,3,image,image] (u8 if frames_u8 else bf16 pixel values) -> patches [n*side*side, kpad] bf16, (c,ky,kx) order
