@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-NCU_TRAFFIC_BYTES_PER_LAUNCH = (33.48e6 + 26.45e6 + 278.97e6 + 142.56e6) / 4
+NCU_TRAFFIC_BYTES_PER_LAUNCH = (33.48e6 + 26.48e6 + 275.48e6 + 141.32e6) / 4
 VISION_BATCH = 32   # the reference embeds frames in batches of 32 (test/inference.py:181)
 
 
@@ -406,7 +406,8 @@ def roofline_leg(r, args, peaks):
     sk, tall, rr = out["skinny"], out["tall"], out["rerot"]
     achieved = sk["bytes"] / (sk["ms"] / 1e3) / 1e9 if sk["ms"] > 0 else 0.0
     # DRAM traffic per launch from the committed `ncu --set full` capture of the same four launches
-    # (profiles/r01_ncu_full_decoder_v3.txt: qkv 33.5, o_proj 26.5, gate|up 272.0 + 7.0, down 138.1 + 4.5 MB read + write)
+    # (profiles/r01_ncu_full_decoder_v5.txt, capture with AHA_PF_MB=0 so that a launch is charged its own bytes only:
+    # qkv 33.5, o_proj 26.5, gate|up 272.0 + 3.5, down 138.1 + 3.2 MB read + write)
     traffic = NCU_TRAFFIC_BYTES_PER_LAUNCH if (args.preset == "7b" and args.streams_per_gpu == 1) else None
     roof = dict(bound="hbm", kernel="gemm_tcgen05_kernel (decoder weight-streaming launches: qkv, o_proj, gate|up, down)",
                 achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"], traffic=traffic,
