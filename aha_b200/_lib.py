@@ -36,6 +36,7 @@ SIGNATURES = {
     "aha_set_sm_sharing": (c_int, [c_int]),
     "aha_debug_attention_timeline": (c_int, [POINTER(c_ulonglong)]),
     "aha_debug_gemm_timeline": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_ulonglong)]),
+    "aha_debug_gemm_tails": (c_int, [c_int, POINTER(c_ulonglong)]),
     "aha_profile_gemm": (c_int, [c_int]),
     "aha_profile_gemm_read": (c_int, [c_int, POINTER(c_double), POINTER(c_longlong), POINTER(c_double), POINTER(c_double)]),
     "aha_model_create": (c_int, [POINTER(ModelDesc), POINTER(WeightEntry), c_int, c_int, POINTER(P)]),

@@ -123,6 +123,22 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   if (warp == 3 && lane == 0 && p.pf_early)
     l2_prefetch_slice(p.pf, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
                       gridDim.x * gridDim.y * gridDim.z);
+  // Chunk versus cache (key-split launches): this CTA's K / V tiles are a frame old - in HBM, not in L2 - except for the
+  // rows the kernel in front of this one is writing right now.  Requesting the tiles into L2 BEFORE griddepcontrol.wait
+  // overlaps their HBM latency with that kernel (the new rows land in the same L2 lines, so the TMA loads after the wait
+  // read current data).
+  static_assert(kStagesKV >= 1, "");
+  if (warp == 3 && lane == 0 && splits > 1 && p.kv_prefetch) {
+    const int k_row = seg.k_row0 + blk * p.k_head_rows, k_col = p.k_col0 + blk * p.k_col_step;
+    const int v_row = seg.v_row0 + blk * p.k_head_rows, v_col = p.v_col0 + blk * p.v_col_step;
+    for (int it = 0; it < nkt; ++it) {
+      const int key0 = (kt0 + it) * kTile;
+      for (int b = 0; b < DB; ++b) {
+        tma_prefetch_2d(&tmap_k, k_col + b * 64, k_row + key0);
+        tma_prefetch_2d(&tmap_v, v_col + b * 64, v_row + key0);
+      }
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -598,6 +614,7 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
+  { static const int kvpf = getenv("AHA_KV_PF") ? atoi(getenv("AHA_KV_PF")) : 1; p.kv_prefetch = kvpf; }
   // per-launch timing for bench.py's roofline leg: class 3 = many-tile batched attention (SigLIP), 4 = chunk versus cache
   ProfSlot* slot = prof_begin(ctas >= sm_count ? 3 : 4, st);
   AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));

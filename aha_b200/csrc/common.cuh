@@ -92,6 +92,11 @@ __device__ __forceinline__ void l2_prefetch_slice(const L2Prefetch& pf, unsigned
 
 #ifdef __CUDACC__
 // bring-up aid (AHA_TS=1): one CTA of a kernel stamps its phases with the SM cycle counter
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void dbg_stamp(unsigned long long* ts, int slot) {
   if (ts) ts[slot] = (unsigned long long)clock64();
 }

@@ -31,6 +31,7 @@ struct GemmParams {
   int* ws_zero;         // the OTHER counter bank, ws_zero_n ints: this launch zeroes it for the next split launch
   int ws_zero_n;
   unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
+  unsigned long long* dbg_all;  // bring-up: (accumulator complete, exit) of every CTA on the global ns timer, or null
   L2Prefetch pf;        // weights of LATER kernels to request into L2 once this CTA's own loads are in flight
   // RMSNorm folded around the GEMMs (skinny orientation only, see GemmCall):
   const float* rs_partials;   // consumer: sum over i < rs_n of rs_partials[i * rs_ld + token] = sum of squares of the row

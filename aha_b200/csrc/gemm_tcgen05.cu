@@ -521,6 +521,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
   if (p.dbg == 1) return;
   unsigned long long* ts = (p.dbg_ts && threadIdx.x == 128 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg_ts : nullptr;
+  // bring-up (AHA_TS=1): every CTA's "accumulator complete" and "exit" on the global nanosecond timer (tail skew of a grid)
+  unsigned long long* ts_all = (p.dbg_all && threadIdx.x == 128)
+      ? p.dbg_all + 2 * (((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) : nullptr;
   dbg_stamp(ts, 0);
 
   // The weight operand (A when skinny, B when tall) does not depend on any earlier kernel: its first ring of tiles is
@@ -616,6 +619,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     mbar_wait(accum_bar, 0);
     tc_fence_after();
     dbg_stamp(ts, 3);
+    if (ts_all) ts_all[0] = global_timer_ns();
     const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
     if (p.dbg == 2) {
     } else if (p.splits == 1) {
@@ -743,6 +747,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     tmem_dealloc<C::kTmemCols>(tmem_base);
   }
   dbg_stamp(ts, 7);
+  if (ts_all) ts_all[1] = global_timer_ns();
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -1068,6 +1073,9 @@ int dispatch_persistent(int act, const CUtensorMap& ta, const CUtensorMap& tb, c
 // ---- bring-up: phase stamps (SM cycles) of CTA (0,0,0) of the most recent launch of each (grid.x, grid.z) class ----
 static unsigned long long* g_gemm_ts = nullptr;   // [64 slots][8]
 static std::map<std::pair<int, int>, int> g_gemm_ts_slot;
+static unsigned long long* g_gemm_ts_all = nullptr;   // [64 slots][kTsAllCtas][2]
+constexpr int kTsAllCtas = 512;
+static unsigned long long* gemm_ts_all_slot(dim3 grid);
 static unsigned long long* gemm_ts_slot(dim3 grid) {
   static const bool want = getenv("AHA_TS") && atoi(getenv("AHA_TS")) == 1;
   if (!want) return nullptr;
@@ -1076,6 +1084,21 @@ static unsigned long long* gemm_ts_slot(dim3 grid) {
   auto it = g_gemm_ts_slot.find(key);
   if (it == g_gemm_ts_slot.end()) { if (g_gemm_ts_slot.size() >= 64) return nullptr; it = g_gemm_ts_slot.emplace(key, (int)g_gemm_ts_slot.size()).first; }
   return g_gemm_ts + it->second * 16;
+}
+static unsigned long long* gemm_ts_all_slot(dim3 grid) {
+  if (!gemm_ts_slot(grid) || (long)grid.x * grid.y * grid.z > kTsAllCtas) return nullptr;
+  if (!g_gemm_ts_all) {
+    if (cudaMalloc(&g_gemm_ts_all, (size_t)64 * kTsAllCtas * 2 * 8) != cudaSuccess) return nullptr;
+    cudaMemset(g_gemm_ts_all, 0, (size_t)64 * kTsAllCtas * 2 * 8);
+  }
+  return g_gemm_ts_all + (size_t)g_gemm_ts_slot[std::make_pair((int)grid.x, (int)grid.z)] * kTsAllCtas * 2;
+}
+// per-CTA (accumulator complete, exit) nanosecond stamps of the most recent launch of slot `slot` (aha_debug_gemm_timeline order)
+extern "C" int aha_debug_gemm_tails(int slot, unsigned long long* out /*[512*2]*/) {
+  if (!g_gemm_ts_all || slot < 0 || slot >= 64) { aha_set_error("ValueError: run with AHA_TS=1"); return AHA_ERR_VALUE; }
+  AHA_CUDA(cudaDeviceSynchronize());
+  AHA_CUDA(cudaMemcpy(out, g_gemm_ts_all + (size_t)slot * kTsAllCtas * 2, (size_t)kTsAllCtas * 2 * 8, cudaMemcpyDeviceToHost));
+  return AHA_OK;
 }
 extern "C" int aha_debug_gemm_timeline(int* n_out, int* grid_x, int* grid_z, unsigned long long* out /*[64*16]*/) {
   if (!g_gemm_ts) { aha_set_error("ValueError: run with AHA_TS=1"); return AHA_ERR_VALUE; }
@@ -1259,6 +1282,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   rc = get_tmap(b, p.Nb, p.K, ldb, bn, &tb); if (rc) return rc;
   dim3 grid(tiles_a, tiles_b, splits);
   p.dbg_ts = gemm_ts_slot(grid);
+  p.dbg_all = gemm_ts_all_slot(grid);
   if (deep < 0) deep = (swap && !g_sm_shared && (long)tiles * splits <= w->sm_count) ? 1 : 0;   // <= one CTA per SM: give it the whole SM
   if (deep && splits > 1 && (long)tiles * splits > w->sm_count) deep = 0;       // split CTAs must stay co-resident
   ProfSlot* slot = prof_begin(swap ? 0 : 1, stream);

@@ -77,6 +77,8 @@ int aha_set_sm_sharing(int shared);
  * of the most recent GEMM launch per (grid.x, grid.z) class.  Not part of the reference-facing surface. */
 int aha_debug_attention_timeline(unsigned long long* out16);
 int aha_debug_gemm_timeline(int* n_out, int* grid_x /*[64]*/, int* grid_z /*[64]*/, unsigned long long* out /*[64*16]*/);
+/* AHA_TS=1: (accumulator complete, exit) of every CTA (up to 512) of the most recent launch of timeline slot `slot`, ns */
+int aha_debug_gemm_tails(int slot, unsigned long long* out /*[512*2]*/);
 
 /* Optional CUDA-event timing of every GEMM launch (bench.py's roofline leg): enable, run, then read the summed launch
  * durations [ms], launch count, algorithmic bytes and FLOPs of class 0 (weight-streaming GEMM, tokens <= 256), 1 (tall

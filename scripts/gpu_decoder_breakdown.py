@@ -49,3 +49,16 @@ if os.environ.get("AHA_TS") == "1":
     for i in range(n.value):
         t = list(out[i * 16:(i + 1) * 16])
         print(f"gemm grid.x={gx[i]} splits={gz[i]} us since entry:", {k: round((x - t[0]) / GHZ / 1e3, 2) for k, x in zip(gn, t) if x})
+    # tail skew of each GEMM grid: when the accumulators of its CTAs complete and when the CTAs exit, relative to the first
+    import numpy as np
+    for i in range(n.value):
+        buf = (ctypes.c_ulonglong * 1024)()
+        A._lib.check(lib.aha_debug_gemm_tails(i, buf))
+        a = np.array(list(buf), dtype=np.int64).reshape(512, 2)
+        a = a[a[:, 0] > 0]
+        if not len(a):
+            continue
+        t0 = a[:, 0].min()
+        acc, ex = (a[:, 0] - t0) / 1e3, (a[:, 1] - t0) / 1e3
+        q = lambda v: [round(float(x), 2) for x in np.percentile(v, [0, 25, 50, 75, 100])]
+        print(f"gemm grid.x={gx[i]} splits={gz[i]} ({len(a)} CTAs) us after the first accumulator: accum done min/q1/med/q3/max {q(acc)}  exit {q(ex)}")
