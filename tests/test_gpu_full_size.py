@@ -109,3 +109,24 @@ def test_7b_width_decoder_matches_oracle(cuda):
         print(f"7b-width {name}: |cuda - oracle_bf16| = {err:.4f}, |oracle_bf16 - oracle_fp32| = {noise:.4f}, "
               f"|cuda - oracle_fp32| = {np.abs(a - c).max():.4f}")
         assert err <= max(2e-2, 2.0 ** -6 * np.abs(b).max(), 2.5 * noise), (name, err, noise)
+
+
+@pytest.mark.gpu
+def test_7b_width_two_streams_equal_single(cuda, wide):
+    """Two streams batched into one call (98 tokens: 128-token GEMM tiles, two 16-token merge chunks per split more than
+    the 49-token call) against the same stream alone: both run the folded-RMSNorm skinny path, with different tile and
+    split geometry, through a sink cache that evicts and re-rotates."""
+    cfg, model = wide
+    q, W, S = cfg.frame_num_tokens, 160, 16
+    torch.manual_seed(5)
+    caches = [model.new_cache("default_sink", W, S, max_chunk=q + 8) for _ in range(2)]
+    single = model.new_cache("default_sink", W, S, max_chunk=q + 8)
+    for t in range(6):
+        x = (torch.randn(2, q, cfg.hidden_size, device=cuda) * 0.05).bfloat16()
+        out = model(inputs_embeds=x, past_key_values=caches)
+        one = model(inputs_embeds=x[1:2].contiguous(), past_key_values=single)
+        a, b = out.frame_scores[1], one.frame_scores[0]
+        assert (a[:2] - b[:2]).abs().max().item() <= 2e-2, (t, a, b)
+        assert (a[2].log() - b[2].log()).abs().item() <= 0.1, (t, a, b)
+        assert caches[1].get_seq_length() == single.get_seq_length()
+    assert torch.equal(caches[1].provenance(0), single.provenance(0))
