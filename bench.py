@@ -395,14 +395,26 @@ def roofline_leg(r, args, peaks):
     for _ in range(n):
         r["step"]()
     torch.cuda.synchronize(r["dev"])
-    r["begin_region"](None)
-    r["state"]["overlap"] = was
     out = {}
     for cls, name in ((0, "skinny"), (1, "tall"), (2, "rerot"), (3, "vattn"), (4, "cattn")):
         ms, cnt, by, fl = ctypes.c_double(), ctypes.c_longlong(), ctypes.c_double(), ctypes.c_double()
         lib.aha_profile_gemm_read(cls, ctypes.byref(ms), ctypes.byref(cnt), ctypes.byref(by), ctypes.byref(fl))
         out[name] = dict(ms=ms.value, launches=cnt.value, bytes=by.value, flops=fl.value)
     lib.aha_profile_gemm(0)
+    # decoder-only step time WITHOUT the per-launch events (they break the overlap of a launch's prologue with the kernel in
+    # front of it): 24 consecutive frames of one vision batch, i.e. pure prefill steps
+    r["begin_region"](None)
+    r["step"]()                                   # computes the batch's embeddings
+    d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(r["dev"])
+    d0.record()
+    for _ in range(24):
+        r["step"]()
+    d1.record()
+    torch.cuda.synchronize(r["dev"])
+    decoder_ms = d0.elapsed_time(d1) / 24
+    r["begin_region"](None)
+    r["state"]["overlap"] = was
     sk, tall, rr = out["skinny"], out["tall"], out["rerot"]
     achieved = sk["bytes"] / (sk["ms"] / 1e3) / 1e9 if sk["ms"] > 0 else 0.0
     # DRAM traffic per launch from the committed `ncu --set full` capture of the same four launches
@@ -416,6 +428,12 @@ def roofline_leg(r, args, peaks):
                 avg_launch_us=(sk["ms"] * 1e3 / sk["launches"]) if sk["launches"] else None,
                 algorithmic_bytes_per_launch=(sk["bytes"] / sk["launches"]) if sk["launches"] else None,
                 ms_per_frame=sk["ms"] / n)
+    if sk["launches"] and decoder_ms > 0:
+        # every byte the prefill step has to move (weights + activations of the four GEMMs of every layer) over the WHOLE
+        # decoder step - attention, RoPE / append, eviction, heads and kernel boundaries included
+        gbs = (sk["bytes"] / n) / (decoder_ms / 1e3) / 1e9
+        roof["decoder_step"] = dict(bound="hbm", what="GEMM bytes of one frame / duration of the whole prefill step (all kernels)",
+                                    achieved=gbs, peak=peaks["hbm"], unit="GB/s", frac=gbs / peaks["hbm"], ms_per_frame=decoder_ms)
     if rr["ms"] > 0 and rr["launches"]:
         gbs = rr["bytes"] / (rr["ms"] / 1e3) / 1e9
         roof["kv_eviction"] = dict(bound="hbm", kernel="rerotate_kernel (sink-cache eviction: every kept key of all layers, one launch)",

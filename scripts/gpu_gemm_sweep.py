@@ -53,6 +53,11 @@ cases += [dict(T=49, F=3584, K=3584, res=True), dict(T=49, F=128, K=64, splits=1
           dict(T=392, F=37888, K=3584, act=3), dict(T=392, F=3584, K=18944, res=True), dict(T=392, F=4608, K=3584),
           dict(T=23328, F=1152, K=1152), dict(T=23328, F=3840, K=1152), dict(T=23328, F=4304, K=1152, act=1),
           dict(T=23328, F=1152, K=4304, res=True), dict(T=23328, F=3584, K=3584), dict(T=729, F=1152, K=1152)]
+if len(sys.argv) > 1 and sys.argv[1] == "splits":     # split-K factor of the three split decoder GEMMs (0 = the host's choice)
+    cases = []
+    for shape in (dict(T=49, F=4608, K=3584), dict(T=49, F=3584, K=3584, res=True), dict(T=49, F=3584, K=18944, res=True)):
+        for sp in (0, 2, 3, 4, 5, 6, 8, 10):
+            cases.append(dict(shape, splits=sp))
 res = []
 for c in cases:
     try:
