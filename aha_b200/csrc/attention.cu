@@ -6,18 +6,23 @@
 //     per (stream, kv head) the q*group query rows (GQA heads folded into the M dimension) against the cache's
 //     physical ring slots; the reference's mask rule allowed(i, j) <=> logical(j) <= off + i is
 //     evaluated from the ring geometry, so keys are streamed in PHYSICAL order (softmax is order independent) and an
-//     eviction never has to move them.  A chunk has only a few query tiles, so the key axis is split over a thread-block
-//     cluster (flash-decoding style) and the partial (O, m, l) are merged through distributed shared memory in rank order.
+//     eviction never has to move them.  A chunk has only a few query tiles, so the key axis is split over up to 8 CTAs
+//     (flash-decoding style); the partial (O, m, l) are parked column-major in an L2-resident workspace, the splits
+//     meet at an arrival counter and merge the 16-column blocks c = split (mod splits) in split order (deterministic).
 //   * SigLIP self-attention (siglip_encoder.py:197-239): per (frame, head) 729 x 729, head_dim 72 padded to 80 columns.
 //
 // CTA = one 128-row query tile of one (segment, head block, key split).  Warp roles:
-//   warp 0    TMA producer: Q once, then a 2-stage ring of {K tile, V tile} (128 keys each)
+//   warp 0    TMA producer: Q once, then a 2-stage ring of K tiles (128 keys each)
+//   warp 3    TMA producer of the V ring (a K stage is free after Q.K^T, a V stage only after P.V)
 //   warp 1    MMA issuer (one elected lane): S[b] = Q.K^T for tile kt+1 is issued before P.V of tile kt, so the
 //             tensor pipe works on the next scores while the softmax warps are busy with the current ones
 //   warp 2    TMEM allocator (512 columns: S0 | S1 | O)
-//   warps 4-7 softmax / correction / epilogue: thread = query row = TMEM lane.  P is written to shared memory in the
-//             K-major 128B-swizzled layout the MMA expects; O is rescaled in TMEM only when the running maximum grows by
-//             more than 2^8 (lazy rescale), which keeps the correction off the critical path.
+//   warps 4-11 softmax / correction / epilogue: TWO threads per query row (lane l of warps w and w + 4 share TMEM lane
+//             quadrant w & 3 and own 64 of the tile's 128 key columns each; row maximum and sum are exchanged through
+//             shared memory).  P is written to shared memory in the K-major 128B-swizzled layout the MMA expects; O is
+//             rescaled in TMEM only when the running maximum grows by more than 2^8 (lazy rescale), which keeps the
+//             correction off the critical path.  The unsplit epilogue leaves through a shared-memory tile as 16-byte
+//             pieces in row order.
 #include "ops.h"
 #include "gemm.h"
 #include "ptx_sm100.cuh"
