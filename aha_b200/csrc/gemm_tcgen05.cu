@@ -309,11 +309,24 @@ __device__ __forceinline__ void epi_tall16(const GemmParams& p, int token, int f
   if (p.residual) {
     const int rrow = p.res_mod > 0 ? (token % p.res_mod) : token;
     const bf16* r = p.residual + (size_t)rrow * p.ldr + f0;
+    if (nvalid == 16 && (reinterpret_cast<uintptr_t>(r) & 15) == 0) {
+      // two 16-byte loads instead of sixteen 2-byte ones (every lane reads a different row: each load instruction costs
+      // 32 separate sectors either way)
+      const uint4 u0 = *reinterpret_cast<const uint4*>(r), u1 = *reinterpret_cast<const uint4*>(r + 8);
+      const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
-    for (int t = 0; t < 16; t += 2) {
-      if (t < nvalid) acc[t] = b2f(r[t]) + acc[t];
-      if (t + 1 < nvalid) acc[t + 1] = b2f(r[t + 1]) + acc[t + 1];
-      bf16r2(acc[t], acc[t + 1]);
+      for (int t = 0; t < 16; t += 2) {
+        const float2 f = unpack_bf16x2(w[t >> 1]);
+        acc[t] = f.x + acc[t]; acc[t + 1] = f.y + acc[t + 1];
+        bf16r2(acc[t], acc[t + 1]);
+      }
+    } else {
+#pragma unroll
+      for (int t = 0; t < 16; t += 2) {
+        if (t < nvalid) acc[t] = b2f(r[t]) + acc[t];
+        if (t + 1 < nvalid) acc[t + 1] = b2f(r[t + 1]) + acc[t + 1];
+        bf16r2(acc[t], acc[t + 1]);
+      }
     }
   }
   if (p.out_f32) {
@@ -1215,6 +1228,12 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   if (bn == 0) {
     if (swap) bn = p.Nb <= 32 ? 32 : p.Nb <= 64 ? 64 : p.Nb <= 128 ? 128 : 256;
     else bn = p.Nb <= 64 ? 64 : 128;
+    // Tall orientation with a short K and too few 128 x 128 tiles for the device (the one-frame SigLIP out_proj: 729 x 1152
+    // x 1152 = 54 tiles): 128 x 64 tiles, unsplit, beat 128 x 128 with split-K 4 - 10.6 against 18.3 us (scripts/
+    // gpu_gemm_sweep.py vision1) - because the tall split merge costs more than the 18 k-blocks it saves.
+    if (!swap && bn == 128 && c.force_splits == 0 && p.K <= 2048 &&
+        (long)((p.Ma + kBlockM - 1) / kBlockM) * ((p.Nb + 127) / 128) < w->sm_count)
+      bn = 64;
   }
   AHA_REQUIRE(bn == 32 || bn == 64 || bn == 128 || bn == 256, "unsupported GEMM BN tile (one-shot kernel: 32/64/128/256)");
   if (!swap && bn == 32) bn = 64;
@@ -1244,7 +1263,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     splits = 1;
     // tall orientation (measured on B200, profiles/r01_gemm_sweep.json): keep the grid within ~1.75 CTAs per SM
     const int target = (7 * w->sm_count) / 4;
-    if (tiles < target) {
+    if (tiles < target && !(bn == 64 && p.Nb > 64 && p.K <= 2048)) {   // (the short-K 128 x 64 case above stays unsplit)
       splits = target / tiles;
       const int max_by_k = kb_total / 4 > 0 ? kb_total / 4 : 1;  // at least 4 k-blocks per split
       if (splits > max_by_k) splits = max_by_k;

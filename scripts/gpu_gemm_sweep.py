@@ -58,6 +58,13 @@ if len(sys.argv) > 1 and sys.argv[1] == "splits":     # split-K factor of the th
     for shape in (dict(T=49, F=4608, K=3584), dict(T=49, F=3584, K=3584, res=True), dict(T=49, F=3584, K=18944, res=True)):
         for sp in (0, 2, 3, 4, 5, 6, 8, 10):
             cases.append(dict(shape, splits=sp))
+if len(sys.argv) > 1 and sys.argv[1] == "vision1":    # the four SigLIP GEMM shapes at ONE frame (729 tokens): tile width x split-K
+    cases = []
+    for shape in (dict(T=729, F=1152, K=1152, res=True), dict(T=729, F=1152, K=4304, res=True), dict(T=729, F=3840, K=1152),
+                  dict(T=729, F=4304, K=1152, act=1)):
+        for bn in (0, 64, 128, 192, 256):
+            for sp in ((0,) if bn in (0, 192, 256) else (1, 2, 4)):
+                cases.append(dict(shape, bn=bn, splits=sp, swap=0))
 res = []
 for c in cases:
     try:
