@@ -7,6 +7,7 @@ from .model import VideoHeadLiveLlavaQwenForCausalLM, VideoHeadCausalLMOutputWit
 from .postproc import find_ticks, find_ticks_batched
 from .highlight import (fuse_scores, fuse_scores_batched, knapsack_selection, knapsack_select_batched, highlight_indices,
                         highlight_mask_batched)
+from .ingest import ingest_frames, select_frames, load_video_for_testing, load_one_frame, fit_geometry
 from .live_infer import LiveInferForBenchmark, LiveInferForDemo, round_numbers
 from .weights import random_init_state_dict, synthetic_frames, merge_lora_state_dict
 
@@ -15,4 +16,5 @@ __all__ = ["AhaConfig", "VisionConfig", "config_preset", "SinkCache", "SlidingWi
            "build_model_from_state_dict", "find_ticks", "find_ticks_batched", "LiveInferForBenchmark", "LiveInferForDemo",
            "round_numbers", "random_init_state_dict", "synthetic_frames", "fuse_scores", "fuse_scores_batched",
            "knapsack_selection", "knapsack_select_batched", "highlight_indices", "highlight_mask_batched",
-           "merge_lora_state_dict"]
+           "merge_lora_state_dict", "ingest_frames", "select_frames", "load_video_for_testing", "load_one_frame",
+           "fit_geometry"]

@@ -61,6 +61,7 @@ SIGNATURES = {
     "aha_rmsnorm": (c_int, [P, P, P, c_int, c_int, c_float, P]),
     "aha_layernorm": (c_int, [P, P, P, P, c_int, c_int, c_float, P]),
     "aha_preprocess": (c_int, [P, P, c_longlong, P]),
+    "aha_ingest_frames": (c_int, [P, c_int, c_int, c_int, c_int, P, c_int, P]),
     "aha_pool": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, P]),
     "aha_rope_table": (c_int, [c_int, c_int, c_int, c_float, P, P, P]),
     "aha_attention": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_float, P]),

@@ -22,6 +22,12 @@ int aha_preprocess(const uint8_t* frames_u8, void* out_bf16, long long n, void* 
   return op_preprocess(frames_u8, (bf16*)out_bf16, n, (cudaStream_t)stream);
 }
 
+int aha_ingest_frames(const uint8_t* frames_hwc, int n_frames, int height, int width, int flavour, uint8_t* out_chw,
+                      int out_side, void* stream) {
+  AHA_REQUIRE(n_frames == 0 || (frames_hwc && out_chw), "aha_ingest_frames: NULL argument");
+  return op_ingest_frames(frames_hwc, n_frames, height, width, flavour, out_chw, out_side, (cudaStream_t)stream);
+}
+
 int aha_pool(const void* x, void* out, int frames, int side, int channels, int stride, int mode, void* stream) {
   AHA_REQUIRE(x && out, "aha_pool: NULL argument");
   return op_pool((const bf16*)x, (bf16*)out, frames, side, channels, stride, mode, (cudaStream_t)stream);

@@ -1,0 +1,229 @@
+// Frame ingest on the device: decoded frames [n, h, w, 3] uint8 -> the reference's
+// [n, 3, 384, 384] uint8 canvas (aspect-preserving resize, centred on black, CHW), bit-identical to
+//   flavour 0: test/inference.py:540-563          cv2.resize (8-bit INTER_LINEAR) + copyMakeBorder + COLOR_BGR2RGB
+//   flavour 1: test/live_infer_for_video.py:107-119  PIL Image.resize (BICUBIC, 8 bits per channel) + ImageOps.expand
+// The resampling arithmetic is OpenCV's / Pillow's (third-party, not under /root/reference).  Their coefficient tables
+// are functions of the geometry only: they are computed on the host in the libraries' own float / double evaluation
+// order (resize.cpp resizeGeneric_ setup; Resample.c precompute_coeffs + normalize_coeffs_8bpc), cached per geometry and
+// uploaded once; the kernels do the integer arithmetic.  HBM-bound byte work: every canvas byte is written once, by
+// consecutive threads along x of one colour plane; the source is read through L1/L2 only where taps land.
+#include "ops.h"
+#include <cmath>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+constexpr int kPilBits = 22;     // Resample.c PRECISION_BITS = 32 - 8 - 2
+
+struct IngestTables {            // device arrays of one (h, w, flavour, out) geometry
+  int h = 0, w = 0, flavour = -1, out = 0, device = -1;
+  int new_w = 0, new_h = 0, left = 0, top = 0, area_fast = 0, ksx = 0, ksy = 0;
+  int* x_lo = nullptr;  int* x_cnt = nullptr;  int* x_k = nullptr;   // [new_w], [new_w], [new_w, ksx]
+  int* y_lo = nullptr;  int* y_cnt = nullptr;  int* y_k = nullptr;   // cv2: y_lo = row0, y_cnt = row1
+  void* block = nullptr;
+};
+IngestTables g_tab;
+std::mutex g_tab_mutex;
+
+// ---- OpenCV 8-bit INTER_LINEAR: index + two 11-bit coefficients per destination coordinate
+void cv2_axis(int src, int dst, bool horizontal, std::vector<int>& lo, std::vector<int>& hi, std::vector<int>& k) {
+  const double scale = 1.0 / ((double)dst / (double)src);
+  lo.resize(dst); hi.resize(dst); k.resize(2 * (size_t)dst);
+  for (int d = 0; d < dst; ++d) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    if (horizontal) {                      // the fraction is reset at the borders on the x axis only
+      if (s < 0) { s = 0; f = 0.f; }
+      if (s >= src - 1) { s = src - 1; f = 0.f; }
+      lo[d] = s; hi[d] = s + 1 < src ? s + 1 : src - 1;
+    } else {
+      lo[d] = s < 0 ? 0 : (s > src - 1 ? src - 1 : s);
+      hi[d] = s + 1 < 0 ? 0 : (s + 1 > src - 1 ? src - 1 : s + 1);
+    }
+    k[2 * d] = (int)lrintf((1.f - f) * 2048.f);       // saturate_cast<short>(float): round half to even
+    k[2 * d + 1] = (int)lrintf(f * 2048.f);
+  }
+}
+
+// ---- Pillow bicubic (a = -0.5)
+double bicubic(double x) {
+  const double a = -0.5;
+  if (x < 0.0) x = -x;
+  if (x < 1.0) return ((a + 2.0) * x - (a + 3.0)) * x * x + 1;
+  if (x < 2.0) return (((x - 5) * x + 8) * x - 4) * a;
+  return 0.0;
+}
+int pil_axis(int src, int dst, std::vector<int>& lo, std::vector<int>& cnt, std::vector<int>& k) {
+  double scale = (double)src / (double)dst, filterscale = scale;
+  if (filterscale < 1.0) filterscale = 1.0;
+  const double support = 2.0 * filterscale;
+  const int ksize = (int)ceil(support) * 2 + 1;
+  lo.resize(dst); cnt.resize(dst); k.assign((size_t)dst * ksize, 0);
+  const double ss = 1.0 / filterscale;
+  std::vector<double> w(ksize);
+  for (int xx = 0; xx < dst; ++xx) {
+    const double center = (xx + 0.5) * scale;
+    int xmin = (int)(center - support + 0.5);
+    if (xmin < 0) xmin = 0;
+    int xmax = (int)(center + support + 0.5);
+    if (xmax > src) xmax = src;
+    xmax -= xmin;
+    double ww = 0.0;
+    for (int x = 0; x < xmax; ++x) { w[x] = bicubic((x + xmin - center + 0.5) * ss); ww += w[x]; }
+    for (int x = 0; x < xmax; ++x) {
+      const double v = ww != 0.0 ? w[x] / ww : w[x];
+      k[(size_t)xx * ksize + x] = v < 0 ? (int)(-0.5 + v * (1 << kPilBits)) : (int)(0.5 + v * (1 << kPilBits));
+    }
+    lo[xx] = xmin; cnt[xx] = xmax;
+  }
+  return ksize;
+}
+
+// ---- flavour 0.  One thread = four consecutive canvas pixels of one row, all three colour planes.
+__global__ void __launch_bounds__(384) ingest_cv2_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
+                                                         IngestTables t) {
+  const int X0 = threadIdx.x * 4, Y = blockIdx.x * blockDim.y + threadIdx.y, n = blockIdx.y;
+  if (X0 >= t.out || Y >= t.out) return;
+  const uint8_t* img = src + (size_t)n * t.h * t.w * 3;
+  const int dy = Y - t.top;
+  uint32_t px[3] = {0u, 0u, 0u};             // four packed bytes per output plane
+  if (dy >= 0 && dy < t.new_h) {
+    int r0, r1, b0, b1;
+    if (t.area_fast) { r0 = 2 * dy; r1 = 2 * dy + 1; b0 = b1 = 0; }
+    else { r0 = __ldg(t.y_lo + dy); r1 = __ldg(t.y_cnt + dy); b0 = __ldg(t.y_k + 2 * dy); b1 = __ldg(t.y_k + 2 * dy + 1); }
+    const uint8_t* row0 = img + (size_t)r0 * t.w * 3;
+    const uint8_t* row1 = img + (size_t)r1 * t.w * 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int dx = X0 + i - t.left;
+      if (dx < 0 || dx >= t.new_w) continue;
+      int c0, c1, a0, a1;
+      if (t.area_fast) { c0 = 2 * dx; c1 = 2 * dx + 1; a0 = a1 = 0; }
+      else { c0 = __ldg(t.x_lo + dx); c1 = __ldg(t.x_cnt + dx); a0 = __ldg(t.x_k + 2 * dx); a1 = __ldg(t.x_k + 2 * dx + 1); }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int s00 = __ldg(row0 + c0 * 3 + c), s01 = __ldg(row0 + c1 * 3 + c);
+        const int s10 = __ldg(row1 + c0 * 3 + c), s11 = __ldg(row1 + c1 * 3 + c);
+        int v;
+        if (t.area_fast) v = (s00 + s01 + s10 + s11 + 2) >> 2;
+        else {
+          const int S0 = s00 * a0 + s01 * a1, S1 = s10 * a0 + s11 * a1;       // HResizeLinear, exact in int32
+          v = (((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2;  // VResizeLinear<uchar, int, short>
+          v = v < 0 ? 0 : (v > 255 ? 255 : v);
+        }
+        px[2 - c] |= (uint32_t)v << (8 * i);     // BGR -> RGB: source channel c lands in plane 2 - c
+      }
+    }
+  }
+  const size_t plane = (size_t)t.out * t.out;
+  uint8_t* o = out + (size_t)n * 3 * plane + (size_t)Y * t.out + X0;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) *reinterpret_cast<uint32_t*>(o + c * plane) = px[c];
+}
+
+// ---- flavour 1.  One CTA = one canvas row of one frame: horizontal pass of the rows under the vertical taps into an
+// 8-bit shared-memory image (Pillow rounds to 8 bits between the passes), then the vertical pass.
+__global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
+                                                         IngestTables t) {
+  extern __shared__ uint8_t hor[];           // [ycnt][new_w * 3]
+  const int Y = blockIdx.x, n = blockIdx.y, dy = Y - t.top;
+  const size_t plane = (size_t)t.out * t.out;
+  uint8_t* orow = out + (size_t)n * 3 * plane + (size_t)Y * t.out;
+  const bool live = dy >= 0 && dy < t.new_h;
+  const int row_bytes = t.new_w * 3;
+  int ylo = 0, ycnt = 0;
+  if (live) {
+    ylo = __ldg(t.y_lo + dy); ycnt = __ldg(t.y_cnt + dy);
+    const uint8_t* img = src + (size_t)n * t.h * t.w * 3;
+    for (int j = threadIdx.x; j < row_bytes; j += blockDim.x) {
+      const int x = j / 3, c = j - 3 * x;
+      const int lo = __ldg(t.x_lo + x), cnt = __ldg(t.x_cnt + x);
+      const int* k = t.x_k + (size_t)x * t.ksx;
+      for (int r = 0; r < ycnt; ++r) {
+        const uint8_t* p = img + ((size_t)(ylo + r) * t.w + lo) * 3 + c;
+        int acc = 1 << (kPilBits - 1);
+        for (int i = 0; i < cnt; ++i) acc += (int)__ldg(p + 3 * i) * __ldg(k + i);
+        acc >>= kPilBits;
+        hor[r * row_bytes + j] = (uint8_t)(acc < 0 ? 0 : (acc > 255 ? 255 : acc));
+      }
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 3 * t.out; j += blockDim.x) {
+    const int c = j / t.out, X = j - c * t.out, x = X - t.left;
+    int v = 0;
+    if (live && x >= 0 && x < t.new_w) {
+      const int* k = t.y_k + (size_t)dy * t.ksy;
+      int acc = 1 << (kPilBits - 1);
+      for (int r = 0; r < ycnt; ++r) acc += (int)hor[r * row_bytes + x * 3 + c] * __ldg(k + r);
+      acc >>= kPilBits;
+      v = acc < 0 ? 0 : (acc > 255 ? 255 : acc);
+    }
+    orow[c * plane + X] = (uint8_t)v;
+  }
+}
+
+int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
+  int device = 0;
+  AHA_CUDA(cudaGetDevice(&device));
+  if (g_tab.h == h && g_tab.w == w && g_tab.flavour == flavour && g_tab.out == out && g_tab.device == device) return AHA_OK;
+  if (g_tab.block) { AHA_CUDA(cudaStreamSynchronize(st)); cudaFree(g_tab.block); g_tab = IngestTables{}; }
+  IngestTables t;
+  t.h = h; t.w = w; t.flavour = flavour; t.out = out; t.device = device;
+  // test/inference.py:540-545: the longer side becomes `out`, the other int((short / long) * out), in float64
+  if (w > h) { t.new_w = out; t.new_h = (int)(((double)h / (double)w) * out); }
+  else { t.new_h = out; t.new_w = (int)(((double)w / (double)h) * out); }
+  AHA_REQUIRE(t.new_w >= 1 && t.new_h >= 1, "ingest_frames: the aspect ratio leaves an empty image");
+  t.left = (out - t.new_w) / 2; t.top = (out - t.new_h) / 2;
+  std::vector<int> xl, xc, xk, yl, yc, yk;
+  if (flavour == 0) {
+    t.area_fast = (w == 2 * t.new_w && h == 2 * t.new_h) ? 1 : 0;   // resize.cpp: INTER_LINEAR at exactly 2 x 2 -> INTER_AREA
+    cv2_axis(w, t.new_w, true, xl, xc, xk);
+    cv2_axis(h, t.new_h, false, yl, yc, yk);
+    t.ksx = t.ksy = 2;
+  } else {
+    t.ksx = pil_axis(w, t.new_w, xl, xc, xk);
+    t.ksy = pil_axis(h, t.new_h, yl, yc, yk);
+  }
+  std::vector<int> host;
+  auto put = [&](const std::vector<int>& v) { size_t o = host.size(); host.insert(host.end(), v.begin(), v.end()); return o; };
+  const size_t o_xl = put(xl), o_xc = put(xc), o_xk = put(xk), o_yl = put(yl), o_yc = put(yc), o_yk = put(yk);
+  AHA_CUDA(cudaMalloc(&t.block, host.size() * sizeof(int)));
+  AHA_CUDA(cudaMemcpyAsync(t.block, host.data(), host.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  AHA_CUDA(cudaStreamSynchronize(st));     // `host` is pageable memory that dies with this frame
+  int* base = (int*)t.block;
+  t.x_lo = base + o_xl; t.x_cnt = base + o_xc; t.x_k = base + o_xk;
+  t.y_lo = base + o_yl; t.y_cnt = base + o_yc; t.y_k = base + o_yk;
+  g_tab = t;
+  return AHA_OK;
+}
+
+}  // namespace
+
+int op_ingest_frames(const uint8_t* src_hwc, int n, int h, int w, int flavour, uint8_t* out_chw, int out, cudaStream_t st) {
+  AHA_REQUIRE(flavour == 0 || flavour == 1, "ingest_frames: flavour must be 0 (cv2 bilinear, BGR) or 1 (PIL bicubic, RGB)");
+  AHA_REQUIRE(n >= 0 && h >= 1 && w >= 1 && h <= 16384 && w <= 16384, "ingest_frames: bad frame geometry");
+  AHA_REQUIRE(out >= 4 && out % 4 == 0 && out <= 1536, "ingest_frames: the canvas side must be a multiple of 4, at most 1536");
+  AHA_REQUIRE((reinterpret_cast<uintptr_t>(out_chw) & 3) == 0, "ingest_frames: the canvas must be 4-byte aligned");
+  if (n == 0) return AHA_OK;
+  AHA_REQUIRE(n <= 65535, "ingest_frames: at most 65535 frames per call");
+  std::lock_guard<std::mutex> lock(g_tab_mutex);
+  int rc = build_tables(h, w, flavour, out, st);
+  if (rc != AHA_OK) return rc;
+  const IngestTables t = g_tab;
+  if (flavour == 0) {
+    const int tx = out / 4, ty = tx <= 384 ? (384 / tx > 0 ? 384 / tx : 1) : 1;
+    ingest_cv2_kernel<<<dim3((out + ty - 1) / ty, n), dim3(tx, ty), 0, st>>>(src_hwc, out_chw, t);
+  } else {
+    const size_t smem = (size_t)t.ksy * t.new_w * 3;
+    AHA_REQUIRE(smem <= 200 * 1024, "ingest_frames: the down-scale factor needs more than 200 KB of shared memory per row");
+    if (smem > 48 * 1024)
+      AHA_CUDA(cudaFuncSetAttribute(ingest_pil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    ingest_pil_kernel<<<dim3(out, n), 384, smem, st>>>(src_hwc, out_chw, t);
+  }
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}

@@ -68,6 +68,10 @@ struct AttnProblem {
 };
 int op_attention(const AttnProblem& p, cudaStream_t st);
 
+// ---- ingest.cu ----
+// decoded frames [n, h, w, 3] u8 -> [n, 3, out, out] u8 canvas; flavour 0 = cv2 bilinear + BGR->RGB, 1 = PIL bicubic
+int op_ingest_frames(const uint8_t* src_hwc, int n, int h, int w, int flavour, uint8_t* out_chw, int out, cudaStream_t st);
+
 // ---- postproc.cu ----
 int op_find_ticks(const double* scores, int n_streams, int T, double prominence, int distance, const double* thresh,
                   int32_t* peaks, int max_peaks, int32_t* n_peaks, double* smoothed, double* thresh_out,

@@ -180,6 +180,16 @@ int aha_layernorm(const void* x, const void* weight, const void* bias, void* out
                   void* stream);
 /* SigLipImageProcessor.preprocess (siglip_encoder.py:47-67) + .to(bf16): uint8 [n] -> bf16 [n] */
 int aha_preprocess(const uint8_t* frames_u8, void* out_bf16, long long n, void* stream);
+/* Frame ingest: decoded frames [n, height, width, 3] u8 (device) -> the [n, 3, out_side, out_side] u8
+ * canvas the reference's loaders hand to the image processor: aspect-preserving resize (longer side = out_side, shorter
+ * int(short / long * out_side)), centred on black, CHW.  Bit-identical to
+ *   flavour 0: load_video_for_testing, test/inference.py:540-563 - cv2.resize (8-bit INTER_LINEAR; the exact 2 x 2 case
+ *              runs OpenCV's INTER_AREA fast path), cv2.copyMakeBorder, COLOR_BGR2RGB (input BGR, output RGB);
+ *   flavour 1: load_one_frame, test/live_infer_for_video.py:107-119 - PIL Image.resize (BICUBIC), ImageOps.expand (RGB).
+ * The coefficient tables of a geometry are built on the host and cached (first call of a geometry synchronises the
+ * stream once).  ValueError for a flavour / geometry outside the supported range. */
+int aha_ingest_frames(const uint8_t* frames_hwc, int n_frames, int height, int width, int flavour, uint8_t* out_chw,
+                      int out_side, void* stream);
 /* post_projector_pooling (video_head_live_llava_qwen.py:117-136): [frames, side*side, C] -> [frames, out*out, C] */
 int aha_pool(const void* x, void* out, int frames, int side, int channels, int stride, int mode, void* stream);
 /* Qwen2RotaryEmbedding: cos/sin [q, d] bf16 for positions pos0 .. pos0+q-1 */

@@ -1,0 +1,90 @@
+"""Frame-ingest kernels (through the C-ABI) against cv2's / PIL's / the reference loader's own outputs
+(tests/golden/ingest.npz) and against the oracle on seeded batches: bit-exact."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import aha_b200 as A
+from oracle import ingest_oracle as io
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ingest.npz"))
+
+
+def source_frame(w, h, seed):
+    return np.random.default_rng(seed).integers(0, 256, (h, w, 3), dtype=np.uint8)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize("i", range(len(G["geometries"])))
+def test_kernels_match_cv2_and_pil(cuda, i):
+    w, h = (int(v) for v in G["geometries"][i])
+    src = torch.from_numpy(source_frame(w, h, 100 + i)).to(cuda)
+    a = A.ingest_frames(src[None], "cv2")[0].cpu().numpy()
+    b = A.load_one_frame(src)[0].cpu().numpy()
+    assert sha(a) == str(G["cv2_sha256"][i]), f"cv2 flavour differs at {w}x{h}"
+    assert sha(b) == str(G["pil_sha256"][i]), f"PIL flavour differs at {w}x{h}"
+    if i == 0:
+        assert np.array_equal(a, G["full_cv2"]) and np.array_equal(b, G["full_pil"])
+
+
+def test_clip_through_load_video_for_testing(cuda):
+    clip = torch.from_numpy(np.random.default_rng(7).integers(0, 256, (45, 180, 320, 3), dtype=np.uint8))
+    frames, ofps, dur, kept = A.load_video_for_testing(clip, 29.97, output_fps=2, return_true_frames=True, device=cuda,
+                                                       batch=2)
+    assert kept == G["clip_kept"].tolist() and [ofps, dur] == G["clip_meta"].tolist()
+    assert frames.is_cuda and tuple(frames.shape) == (len(kept), 3, 384, 384)
+    assert sha(frames.cpu().numpy()) == str(G["clip_sha256"])
+    assert A.load_video_for_testing(clip[:0], 29.97, output_fps=2, device=cuda) == (None, None, None, None)
+
+
+@pytest.mark.parametrize("flavour", ["cv2", "pil"])
+def test_batch_against_oracle_and_geometry_switches(cuda, flavour):
+    # the table cache is per geometry: alternate geometries and flavours, batches of several frames
+    for seed, (n, w, h) in enumerate([(3, 427, 240), (2, 240, 427), (3, 427, 240), (1, 1024, 1024), (2, 768, 432)]):
+        src = np.random.default_rng(50 + seed).integers(0, 256, (n, h, w, 3), dtype=np.uint8)
+        out = A.ingest_frames(torch.from_numpy(src).to(cuda), flavour).cpu().numpy()
+        for k in range(n):
+            assert np.array_equal(out[k], io.ingest_frame(src[k], flavour)), (seed, k)
+
+
+@pytest.mark.parametrize("flavour", ["cv2", "pil"])
+def test_full_size_batch_properties(cuda, flavour):
+    """32 frames of 1920 x 1080: one frame against the oracle, the rest through size-independent properties."""
+    g = torch.Generator(device="cpu").manual_seed(3)
+    src = torch.randint(0, 256, (32, 1080, 1920, 3), dtype=torch.uint8, generator=g).to(cuda)
+    out = A.ingest_frames(src, flavour)
+    new_w, new_h, left, top = A.fit_geometry(1920, 1080)
+    assert (new_w, new_h, left, top) == (384, 216, 0, 84)
+    assert int(out[:, :, :top].max()) == 0 and int(out[:, :, top + new_h:].max()) == 0       # black border
+    assert np.array_equal(out[5].cpu().numpy(), io.ingest_frame(src[5].cpu().numpy(), flavour))
+    # channels are resampled independently: swapping source channels swaps output planes
+    assert torch.equal(A.ingest_frames(src[:4].flip(-1), flavour), out[:4].flip(1))
+    # frames are independent: a sub-batch gives the same bytes
+    assert torch.equal(A.ingest_frames(src[7:9], flavour), out[7:9])
+    # a constant image stays constant inside the frame (coefficients sum to one)
+    flat = torch.full((1, 1080, 1920, 3), 201, dtype=torch.uint8, device=cuda)
+    assert int(A.ingest_frames(flat, flavour)[0, :, top:top + new_h].min()) == 201
+
+
+def test_ingest_feeds_visual_embed(cuda):
+    """The canvas is what SigLipImageProcessor.preprocess receives: uint8 [n, 3, 384, 384]."""
+    src = torch.from_numpy(source_frame(640, 360, 100)).to(cuda)
+    canvas = A.ingest_frames(src[None], "cv2")
+    assert canvas.dtype == torch.uint8 and tuple(canvas.shape) == (1, 3, 384, 384) and canvas.is_contiguous()
+
+
+def test_errors(cuda):
+    with pytest.raises(ValueError):
+        A.ingest_frames(torch.zeros(1, 8, 8, 3, dtype=torch.uint8, device=cuda), "lanczos")
+    with pytest.raises(TypeError):
+        A.ingest_frames(torch.zeros(1, 8, 8, 3, dtype=torch.uint8), "cv2")
+    with pytest.raises(ValueError):
+        A.ingest_frames(torch.zeros(1, 8, 8, 4, dtype=torch.uint8, device=cuda), "cv2")
+    assert tuple(A.ingest_frames(torch.zeros(0, 8, 8, 3, dtype=torch.uint8, device=cuda), "pil").shape) == (0, 3, 384, 384)
