@@ -8,6 +8,7 @@
 // uploaded once; the kernels do the integer arithmetic.  HBM-bound byte work: every canvas byte is written once, by
 // consecutive threads along x of one colour plane; the source is read through L1/L2 only where taps land.
 #include "ops.h"
+#include <algorithm>
 #include <cmath>
 #include <mutex>
 #include <vector>
@@ -19,6 +20,7 @@ constexpr int kPilBits = 22;     // Resample.c PRECISION_BITS = 32 - 8 - 2
 struct IngestTables {            // device arrays of one (h, w, flavour, out) geometry
   int h = 0, w = 0, flavour = -1, out = 0, device = -1;
   int new_w = 0, new_h = 0, left = 0, top = 0, area_fast = 0, ksx = 0, ksy = 0;
+  int th = 1, tile_rows = 0;      // PIL flavour: canvas rows per CTA and the most source rows under one tile
   int* x_lo = nullptr;  int* x_cnt = nullptr;  int* x_k = nullptr;   // [new_w], [new_w], [new_w, ksx]
   int* y_lo = nullptr;  int* y_cnt = nullptr;  int* y_k = nullptr;   // cv2: y_lo = row0, y_cnt = row1
   void* block = nullptr;
@@ -123,45 +125,78 @@ __global__ void __launch_bounds__(384) ingest_cv2_kernel(const uint8_t* __restri
   for (int c = 0; c < 3; ++c) *reinterpret_cast<uint32_t*>(o + c * plane) = px[c];
 }
 
-// ---- flavour 1.  One CTA = one canvas row of one frame: horizontal pass of the rows under the vertical taps into an
-// 8-bit shared-memory image (Pillow rounds to 8 bits between the passes), then the vertical pass.
+// ---- flavour 1.  One CTA = `th` consecutive canvas rows of one frame.  Horizontal pass of every source row under the
+// tile's vertical taps into an 8-bit shared-memory image (Pillow rounds to 8 bits between the passes): a thread owns one
+// (x, channel) column and walks the rows eight at a time with the accumulators in registers, so a coefficient is loaded
+// once per eight multiplies.  Then the vertical pass, written plane by plane with consecutive threads along x.
 __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
                                                          IngestTables t) {
-  extern __shared__ uint8_t hor[];           // [ycnt][new_w * 3]
-  const int Y = blockIdx.x, n = blockIdx.y, dy = Y - t.top;
+  extern __shared__ uint8_t hor[];           // [rows under the tile][new_w * 3]
+  const int Y0 = blockIdx.x * t.th, n = blockIdx.y;
   const size_t plane = (size_t)t.out * t.out;
-  uint8_t* orow = out + (size_t)n * 3 * plane + (size_t)Y * t.out;
-  const bool live = dy >= 0 && dy < t.new_h;
   const int row_bytes = t.new_w * 3;
-  int ylo = 0, ycnt = 0;
-  if (live) {
-    ylo = __ldg(t.y_lo + dy); ycnt = __ldg(t.y_cnt + dy);
+  int d0 = Y0 - t.top, d1 = Y0 + t.th - t.top;          // destination rows [d0, d1) of the resized image
+  d0 = d0 < 0 ? 0 : d0; d1 = d1 > t.new_h ? t.new_h : d1;
+  int ybase = 0;
+  if (d0 < d1) {
+    ybase = __ldg(t.y_lo + d0);
+    const int nrows = __ldg(t.y_lo + d1 - 1) + __ldg(t.y_cnt + d1 - 1) - ybase;
     const uint8_t* img = src + (size_t)n * t.h * t.w * 3;
+    const size_t pitch = (size_t)t.w * 3;
     for (int j = threadIdx.x; j < row_bytes; j += blockDim.x) {
       const int x = j / 3, c = j - 3 * x;
       const int lo = __ldg(t.x_lo + x), cnt = __ldg(t.x_cnt + x);
       const int* k = t.x_k + (size_t)x * t.ksx;
-      for (int r = 0; r < ycnt; ++r) {
-        const uint8_t* p = img + ((size_t)(ylo + r) * t.w + lo) * 3 + c;
-        int acc = 1 << (kPilBits - 1);
-        for (int i = 0; i < cnt; ++i) acc += (int)__ldg(p + 3 * i) * __ldg(k + i);
-        acc >>= kPilBits;
-        hor[r * row_bytes + j] = (uint8_t)(acc < 0 ? 0 : (acc > 255 ? 255 : acc));
+      const uint8_t* p0 = img + ((size_t)ybase * t.w + lo) * 3 + c;
+      for (int r0 = 0; r0 < nrows; r0 += 8) {
+        int acc[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc[u] = 1 << (kPilBits - 1);
+        const uint8_t* p = p0 + (size_t)r0 * pitch;
+        if (r0 + 8 <= nrows) {
+          for (int i = 0; i < cnt; ++i) {
+            const int kv = __ldg(k + i);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc[u] += (int)__ldg(p + u * pitch + 3 * i) * kv;
+          }
+        } else {
+          for (int i = 0; i < cnt; ++i) {
+            const int kv = __ldg(k + i);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+              if (r0 + u < nrows) acc[u] += (int)__ldg(p + u * pitch + 3 * i) * kv;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (r0 + u < nrows) {
+            const int v = acc[u] >> kPilBits;
+            hor[(r0 + u) * row_bytes + j] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+          }
+        }
       }
     }
   }
   __syncthreads();
-  for (int j = threadIdx.x; j < 3 * t.out; j += blockDim.x) {
-    const int c = j / t.out, X = j - c * t.out, x = X - t.left;
-    int v = 0;
-    if (live && x >= 0 && x < t.new_w) {
-      const int* k = t.y_k + (size_t)dy * t.ksy;
-      int acc = 1 << (kPilBits - 1);
-      for (int r = 0; r < ycnt; ++r) acc += (int)hor[r * row_bytes + x * 3 + c] * __ldg(k + r);
-      acc >>= kPilBits;
-      v = acc < 0 ? 0 : (acc > 255 ? 255 : acc);
+  for (int Y = Y0; Y < Y0 + t.th && Y < t.out; ++Y) {
+    const int dy = Y - t.top;
+    const bool live = dy >= 0 && dy < t.new_h;
+    int roff = 0, ycnt = 0;
+    if (live) { roff = __ldg(t.y_lo + dy) - ybase; ycnt = __ldg(t.y_cnt + dy); }
+    const int* k = t.y_k + (size_t)(live ? dy : 0) * t.ksy;
+    uint8_t* orow = out + (size_t)n * 3 * plane + (size_t)Y * t.out;
+    for (int j = threadIdx.x; j < 3 * t.out; j += blockDim.x) {
+      const int c = j / t.out, X = j - c * t.out, x = X - t.left;
+      int v = 0;
+      if (live && x >= 0 && x < t.new_w) {
+        const uint8_t* hp = hor + roff * row_bytes + x * 3 + c;
+        int acc = 1 << (kPilBits - 1);
+        for (int r = 0; r < ycnt; ++r) acc += (int)hp[r * row_bytes] * __ldg(k + r);
+        acc >>= kPilBits;
+        v = acc < 0 ? 0 : (acc > 255 ? 255 : acc);
+      }
+      orow[c * plane + X] = (uint8_t)v;
     }
-    orow[c * plane + X] = (uint8_t)v;
   }
 }
 
@@ -186,6 +221,17 @@ int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
   } else {
     t.ksx = pil_axis(w, t.new_w, xl, xc, xk);
     t.ksy = pil_axis(h, t.new_h, yl, yc, yk);
+    // rows per CTA: the largest tile whose horizontal-pass image stays under 100 KB (two CTAs per SM)
+    for (int th = 16; th >= 1; th /= 2) {
+      int worst = 0;
+      for (int Y0 = 0; Y0 < out; Y0 += th) {
+        int d0 = Y0 - t.top, d1 = Y0 + th - t.top;
+        d0 = d0 < 0 ? 0 : d0; d1 = d1 > t.new_h ? t.new_h : d1;
+        if (d0 < d1) worst = std::max(worst, yl[d1 - 1] + yc[d1 - 1] - yl[d0]);
+      }
+      t.th = th; t.tile_rows = worst;
+      if ((size_t)worst * t.new_w * 3 <= 100 * 1024) break;
+    }
   }
   std::vector<int> host;
   auto put = [&](const std::vector<int>& v) { size_t o = host.size(); host.insert(host.end(), v.begin(), v.end()); return o; };
@@ -217,11 +263,11 @@ int op_ingest_frames(const uint8_t* src_hwc, int n, int h, int w, int flavour, u
     const int tx = out / 4, ty = tx <= 384 ? (384 / tx > 0 ? 384 / tx : 1) : 1;
     ingest_cv2_kernel<<<dim3((out + ty - 1) / ty, n), dim3(tx, ty), 0, st>>>(src_hwc, out_chw, t);
   } else {
-    const size_t smem = (size_t)t.ksy * t.new_w * 3;
+    const size_t smem = (size_t)t.tile_rows * t.new_w * 3;
     AHA_REQUIRE(smem <= 200 * 1024, "ingest_frames: the down-scale factor needs more than 200 KB of shared memory per row");
     if (smem > 48 * 1024)
       AHA_CUDA(cudaFuncSetAttribute(ingest_pil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    ingest_pil_kernel<<<dim3(out, n), 384, smem, st>>>(src_hwc, out_chw, t);
+    ingest_pil_kernel<<<dim3((out + t.th - 1) / t.th, n), 384, smem, st>>>(src_hwc, out_chw, t);
   }
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();

@@ -1,7 +1,7 @@
 """Times the frame-ingest kernels (N4) on one GPU: CUDA events on the launching stream, warm-up, inputs larger than L2
 (64 frames of 1920 x 1080 x 3 = 398 MB).  Prints one JSON line per (flavour, geometry).
 Algorithmic bytes per frame: PIL bicubic (down-scale): every source byte is under some tap -> h*w*3 read + 3*384*384
-written; cv2 bilinear: 4 source pixels per output pixel -> new_w*new_h*4*3 read + 3*384*384 written."""
+written; cv2 bilinear: 4 source pixels per output pixel -> min(h*w*3, new_w*new_h*4*3) read + 3*384*384 written."""
 import json
 import os
 import sys
@@ -33,7 +33,7 @@ def main():
                 A.ingest_frames(src, flavour)
             e1.record(); torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
-            read = h * w * 3 if flavour == "pil" else new_w * new_h * 4 * 3
+            read = h * w * 3 if flavour == "pil" else min(h * w * 3, new_w * new_h * 4 * 3)
             alg = (read + 3 * 384 * 384) * n
             print(json.dumps({"kernel": f"ingest_{flavour}_kernel", "geometry": [w, h], "frames_per_launch": n,
                               "ms_per_launch": round(ms, 4), "frames_per_s": round(n / ms * 1e3, 1),
