@@ -57,11 +57,12 @@ double bicubic(double x) {
   if (x < 2.0) return (((x - 5) * x + 8) * x - 4) * a;
   return 0.0;
 }
-int pil_axis(int src, int dst, std::vector<int>& lo, std::vector<int>& cnt, std::vector<int>& k) {
+int pil_axis(int src, int dst, int pad_to, std::vector<int>& lo, std::vector<int>& cnt, std::vector<int>& k) {
   double scale = (double)src / (double)dst, filterscale = scale;
   if (filterscale < 1.0) filterscale = 1.0;
   const double support = 2.0 * filterscale;
-  const int ksize = (int)ceil(support) * 2 + 1;
+  const int taps = (int)ceil(support) * 2 + 1;
+  const int ksize = (taps + pad_to - 1) / pad_to * pad_to;     // row length of the table, zero-filled past the taps
   lo.resize(dst); cnt.resize(dst); k.assign((size_t)dst * ksize, 0);
   const double ss = 1.0 / filterscale;
   std::vector<double> w(ksize);
@@ -126,76 +127,116 @@ __global__ void __launch_bounds__(384) ingest_cv2_kernel(const uint8_t* __restri
 }
 
 // ---- flavour 1.  One CTA = `th` consecutive canvas rows of one frame.  Horizontal pass of every source row under the
-// tile's vertical taps into an 8-bit shared-memory image (Pillow rounds to 8 bits between the passes): a thread owns one
-// (x, channel) column and walks the rows eight at a time with the accumulators in registers, so a coefficient is loaded
-// once per eight multiplies.  Then the vertical pass, written plane by plane with consecutive threads along x.
+// tile's vertical taps into an 8-bit shared-memory image (Pillow rounds to 8 bits between the passes), then the
+// vertical pass.  The kernel is bound by load instructions (L1 wavefronts), not by HBM, so both passes read 32-bit words:
+// a horizontal work item = one output pixel (three channels) x four source rows; it streams the interleaved source
+// bytes under its taps as aligned words (funnel-shifted to the pixel boundary), four pixels = three words at a time,
+// with the four coefficients of the group in one 16-byte load.  The vertical pass owns four adjacent bytes of the
+// horizontal image per thread.
+__device__ __forceinline__ uint32_t ingest_ldw(const uint32_t* p, uintptr_t end_up) {
+  return reinterpret_cast<uintptr_t>(p) < end_up ? __ldg(p) : 0u;     // words past the source only sit under zero taps
+}
+
 __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
                                                          IngestTables t) {
-  extern __shared__ uint8_t hor[];           // [rows under the tile][new_w * 3]
+  extern __shared__ __align__(16) uint8_t hor[];     // [rows under the tile][hp], hp = new_w * 3 rounded up to 4
+  constexpr int R = 4;
   const int Y0 = blockIdx.x * t.th, n = blockIdx.y;
   const size_t plane = (size_t)t.out * t.out;
-  const int row_bytes = t.new_w * 3;
+  const int row_bytes = t.new_w * 3, hp = (row_bytes + 3) & ~3;
   int d0 = Y0 - t.top, d1 = Y0 + t.th - t.top;          // destination rows [d0, d1) of the resized image
   d0 = d0 < 0 ? 0 : d0; d1 = d1 > t.new_h ? t.new_h : d1;
   int ybase = 0;
   if (d0 < d1) {
     ybase = __ldg(t.y_lo + d0);
     const int nrows = __ldg(t.y_lo + d1 - 1) + __ldg(t.y_cnt + d1 - 1) - ybase;
-    const uint8_t* img = src + (size_t)n * t.h * t.w * 3;
-    const size_t pitch = (size_t)t.w * 3;
-    for (int j = threadIdx.x; j < row_bytes; j += blockDim.x) {
-      const int x = j / 3, c = j - 3 * x;
-      const int lo = __ldg(t.x_lo + x), cnt = __ldg(t.x_cnt + x);
-      const int* k = t.x_k + (size_t)x * t.ksx;
-      const uint8_t* p0 = img + ((size_t)ybase * t.w + lo) * 3 + c;
-      for (int r0 = 0; r0 < nrows; r0 += 8) {
-        int acc[8];
+    const size_t frame_bytes = (size_t)t.h * t.w * 3;
+    const uint8_t* img = src + (size_t)n * frame_bytes;
+    const uintptr_t end_up = (reinterpret_cast<uintptr_t>(src + (size_t)gridDim.y * frame_bytes) + 3) & ~(uintptr_t)3;
+    const int items = t.new_w * ((nrows + R - 1) / R);
+    for (int item = threadIdx.x; item < items; item += blockDim.x) {
+      const int rg = item / t.new_w, x = item - rg * t.new_w, r0 = rg * R;
+      const int lo = __ldg(t.x_lo + x), ng = (__ldg(t.x_cnt + x) + 3) >> 2;
+      const int4* k4 = reinterpret_cast<const int4*>(t.x_k + (size_t)x * t.ksx);
+      const uint32_t* wp[R];
+      uint32_t carry[R];
+      int sh[R], acc[R][3];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) acc[u] = 1 << (kPilBits - 1);
-        const uint8_t* p = p0 + (size_t)r0 * pitch;
-        if (r0 + 8 <= nrows) {
-          for (int i = 0; i < cnt; ++i) {
-            const int kv = __ldg(k + i);
+      for (int u = 0; u < R; ++u) {
+        const int row = r0 + u < nrows ? r0 + u : nrows - 1;         // rows past the tile: clamped, sums dropped
+        const uintptr_t a = reinterpret_cast<uintptr_t>(img + ((size_t)(ybase + row) * t.w + lo) * 3);
+        wp[u] = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        sh[u] = (int)(a & 3) * 8;
+        carry[u] = ingest_ldw(wp[u], end_up);
+        acc[u][0] = acc[u][1] = acc[u][2] = 1 << (kPilBits - 1);
+      }
+      for (int g = 0; g < ng; ++g) {
+        const int4 kk = __ldg(k4 + g);
 #pragma unroll
-            for (int u = 0; u < 8; ++u) acc[u] += (int)__ldg(p + u * pitch + 3 * i) * kv;
-          }
-        } else {
-          for (int i = 0; i < cnt; ++i) {
-            const int kv = __ldg(k + i);
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-              if (r0 + u < nrows) acc[u] += (int)__ldg(p + u * pitch + 3 * i) * kv;
-          }
+        for (int u = 0; u < R; ++u) {
+          const uint32_t l1 = ingest_ldw(wp[u] + 1, end_up), l2 = ingest_ldw(wp[u] + 2, end_up),
+                         l3 = ingest_ldw(wp[u] + 3, end_up);
+          wp[u] += 3;
+          const uint32_t s0 = __funnelshift_r(carry[u], l1, sh[u]), s1 = __funnelshift_r(l1, l2, sh[u]),
+                         s2 = __funnelshift_r(l2, l3, sh[u]);       // twelve bytes = four interleaved pixels
+          carry[u] = l3;
+          acc[u][0] += (int)(s0 & 0xff) * kk.x + (int)(s0 >> 24) * kk.y + (int)((s1 >> 16) & 0xff) * kk.z +
+                       (int)((s2 >> 8) & 0xff) * kk.w;
+          acc[u][1] += (int)((s0 >> 8) & 0xff) * kk.x + (int)(s1 & 0xff) * kk.y + (int)(s1 >> 24) * kk.z +
+                       (int)((s2 >> 16) & 0xff) * kk.w;
+          acc[u][2] += (int)((s0 >> 16) & 0xff) * kk.x + (int)((s1 >> 8) & 0xff) * kk.y + (int)(s2 & 0xff) * kk.z +
+                       (int)(s2 >> 24) * kk.w;
         }
+      }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          if (r0 + u < nrows) {
-            const int v = acc[u] >> kPilBits;
-            hor[(r0 + u) * row_bytes + j] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+      for (int u = 0; u < R; ++u) {
+        if (r0 + u < nrows) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const int v = acc[u][c] >> kPilBits;
+            hor[(r0 + u) * hp + x * 3 + c] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
           }
         }
       }
     }
   }
   __syncthreads();
+  const uint32_t* hor32 = reinterpret_cast<const uint32_t*>(hor);
+  const int hp4 = hp >> 2, margin = t.out - t.new_w;
   for (int Y = Y0; Y < Y0 + t.th && Y < t.out; ++Y) {
     const int dy = Y - t.top;
-    const bool live = dy >= 0 && dy < t.new_h;
-    int roff = 0, ycnt = 0;
-    if (live) { roff = __ldg(t.y_lo + dy) - ybase; ycnt = __ldg(t.y_cnt + dy); }
-    const int* k = t.y_k + (size_t)(live ? dy : 0) * t.ksy;
     uint8_t* orow = out + (size_t)n * 3 * plane + (size_t)Y * t.out;
-    for (int j = threadIdx.x; j < 3 * t.out; j += blockDim.x) {
-      const int c = j / t.out, X = j - c * t.out, x = X - t.left;
-      int v = 0;
-      if (live && x >= 0 && x < t.new_w) {
-        const uint8_t* hp = hor + roff * row_bytes + x * 3 + c;
-        int acc = 1 << (kPilBits - 1);
-        for (int r = 0; r < ycnt; ++r) acc += (int)hp[r * row_bytes] * __ldg(k + r);
-        acc >>= kPilBits;
-        v = acc < 0 ? 0 : (acc > 255 ? 255 : acc);
+    if (dy < 0 || dy >= t.new_h) {                        // border row: zero words
+      for (int j = threadIdx.x; j < 3 * (t.out >> 2); j += blockDim.x) {
+        const int c = j / (t.out >> 2), q = j - c * (t.out >> 2);
+        reinterpret_cast<uint32_t*>(orow + c * plane)[q] = 0u;
       }
-      orow[c * plane + X] = (uint8_t)v;
+      continue;
+    }
+    for (int j = threadIdx.x; j < 3 * margin; j += blockDim.x) {       // left / right border
+      const int c = j / margin, m = j - c * margin;
+      orow[c * plane + (m < t.left ? m : t.new_w + m)] = 0;
+    }
+    const int roff = __ldg(t.y_lo + dy) - ybase, ycnt = __ldg(t.y_cnt + dy);
+    const int* k = t.y_k + (size_t)dy * t.ksy;
+    for (int q = threadIdx.x; q < hp4; q += blockDim.x) {
+      int a0 = 1 << (kPilBits - 1), a1 = a0, a2 = a0, a3 = a0;
+      const uint32_t* hq = hor32 + roff * hp4 + q;
+      for (int r = 0; r < ycnt; ++r) {
+        const uint32_t v = hq[r * hp4];
+        const int kv = __ldg(k + r);
+        a0 += (int)(v & 0xff) * kv; a1 += (int)((v >> 8) & 0xff) * kv;
+        a2 += (int)((v >> 16) & 0xff) * kv; a3 += (int)(v >> 24) * kv;
+      }
+      const int av[4] = {a0 >> kPilBits, a1 >> kPilBits, a2 >> kPilBits, a3 >> kPilBits};
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int j = 4 * q + b;
+        if (j < row_bytes) {
+          const int x = j / 3, c = j - 3 * x;
+          orow[c * plane + t.left + x] = (uint8_t)(av[b] < 0 ? 0 : (av[b] > 255 ? 255 : av[b]));
+        }
+      }
     }
   }
 }
@@ -219,8 +260,8 @@ int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
     cv2_axis(h, t.new_h, false, yl, yc, yk);
     t.ksx = t.ksy = 2;
   } else {
-    t.ksx = pil_axis(w, t.new_w, xl, xc, xk);
-    t.ksy = pil_axis(h, t.new_h, yl, yc, yk);
+    t.ksx = pil_axis(w, t.new_w, 4, xl, xc, xk);       // rows of four-tap groups, 16-byte aligned
+    t.ksy = pil_axis(h, t.new_h, 1, yl, yc, yk);
     // rows per CTA: the largest tile whose horizontal-pass image stays under 100 KB (two CTAs per SM)
     for (int th = 16; th >= 1; th /= 2) {
       int worst = 0;
@@ -230,11 +271,16 @@ int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
         if (d0 < d1) worst = std::max(worst, yl[d1 - 1] + yc[d1 - 1] - yl[d0]);
       }
       t.th = th; t.tile_rows = worst;
-      if ((size_t)worst * t.new_w * 3 <= 100 * 1024) break;
+      if ((size_t)worst * ((t.new_w * 3 + 3) & ~3) <= 100 * 1024) break;
     }
   }
   std::vector<int> host;
-  auto put = [&](const std::vector<int>& v) { size_t o = host.size(); host.insert(host.end(), v.begin(), v.end()); return o; };
+  auto put = [&](const std::vector<int>& v) {   // every table starts on a 16-byte boundary
+    size_t o = host.size();
+    host.insert(host.end(), v.begin(), v.end());
+    host.resize((host.size() + 3) & ~(size_t)3, 0);
+    return o;
+  };
   const size_t o_xl = put(xl), o_xc = put(xc), o_xk = put(xk), o_yl = put(yl), o_yc = put(yc), o_yk = put(yk);
   AHA_CUDA(cudaMalloc(&t.block, host.size() * sizeof(int)));
   AHA_CUDA(cudaMemcpyAsync(t.block, host.data(), host.size() * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -263,7 +309,7 @@ int op_ingest_frames(const uint8_t* src_hwc, int n, int h, int w, int flavour, u
     const int tx = out / 4, ty = tx <= 384 ? (384 / tx > 0 ? 384 / tx : 1) : 1;
     ingest_cv2_kernel<<<dim3((out + ty - 1) / ty, n), dim3(tx, ty), 0, st>>>(src_hwc, out_chw, t);
   } else {
-    const size_t smem = (size_t)t.tile_rows * t.new_w * 3;
+    const size_t smem = (size_t)t.tile_rows * ((t.new_w * 3 + 3) & ~3);
     AHA_REQUIRE(smem <= 200 * 1024, "ingest_frames: the down-scale factor needs more than 200 KB of shared memory per row");
     if (smem > 48 * 1024)
       AHA_CUDA(cudaFuncSetAttribute(ingest_pil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
