@@ -93,9 +93,9 @@ def load_video_for_testing(decoded_bgr: torch.Tensor, input_fps: float, output_f
     return frames, output_fps, duration
 
 
-def load_one_frame(frame_rgb: torch.Tensor, device="cuda") -> torch.Tensor:
+def load_one_frame(frame_rgb: torch.Tensor, device="cuda", out: int = OUTPUT_RESOLUTION) -> torch.Tensor:
     """LiveInferForDemo.load_one_frame up to the image processor: one decoded RGB frame [h, w, 3] uint8 -> [1, 3, 384,
     384] uint8 on the device (feed it to `model.visual_embed`, which fuses the processor's rescale / normalise)."""
     if frame_rgb.dim() != 3:
         raise ValueError("frame must be [height, width, 3]")
-    return ingest_frames(frame_rgb.to(device).unsqueeze(0), "pil")
+    return ingest_frames(frame_rgb.to(device).unsqueeze(0), "pil", out)

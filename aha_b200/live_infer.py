@@ -137,7 +137,18 @@ class LiveInferForBenchmark:
                         self._ready_events[id(f)] = (f, ev)                            # first frame of a batch carries its event
         _lib.load().aha_set_sm_sharing(0)
 
-    def load_one_frame(self, frame: torch.Tensor):
+    def load_one_frame(self, frame: Optional[torch.Tensor] = None, frame_object=None):
+        """`frame`: a canvas [3, 384, 384] uint8 that is already resized and padded.  `frame_object` (the reference's
+        keyword, test/live_infer_for_video.py:98-119): a decoded RGB picture of any size - PIL image, HWC numpy array or
+        HWC uint8 tensor - resized (PIL bicubic, bit-identical), padded and transposed on the device (aha_b200/ingest.py)."""
+        if (frame is None) == (frame_object is None):
+            raise ValueError("give exactly one of frame / frame_object")
+        if frame_object is not None:
+            from .ingest import load_one_frame as _ingest_one
+            if not isinstance(frame_object, torch.Tensor):
+                import numpy as np
+                frame_object = torch.from_numpy(np.ascontiguousarray(np.asarray(frame_object)))
+            frame = _ingest_one(frame_object, device=self.model.device, out=self.frame_resolution)[0]
         emb = self.model.visual_embed(frame.reshape(1, *frame.shape[-3:]))
         self.frame_embeds_queue.append((self.video_time if not self.frame_embeds_queue else
                                         self.frame_embeds_queue[-1][0] + self.frame_interval, emb))

@@ -80,6 +80,27 @@ def test_ingest_feeds_visual_embed(cuda):
     assert canvas.dtype == torch.uint8 and tuple(canvas.shape) == (1, 3, 384, 384) and canvas.is_contiguous()
 
 
+def test_demo_driver_takes_raw_pictures(cuda):
+    """LiveInferForDemo.load_one_frame(frame_object=...) (test/live_infer_for_video.py:98-119): a raw RGB picture gives
+    the same frame embeddings as the oracle's canvas handed in as `frame`."""
+    import dataclasses
+    base = A.config_preset("micro72")
+    cfg = dataclasses.replace(base, vision=dataclasses.replace(base.vision, image_size=112), frame_resolution=112)
+    w = A.random_init_state_dict(cfg, seed=1, device=cuda)
+    model = A.VideoHeadLiveLlavaQwenForCausalLM(cfg, w, device=cuda, max_tokens=64, max_frames=8, logits_mode="none")
+    start = torch.arange(5, dtype=torch.long).reshape(1, -1)
+    a = A.LiveInferForDemo(model, start, window_length=64, num_sink_tokens=4, frame_fps=1.0)
+    b = A.LiveInferForDemo(model, start, window_length=64, num_sink_tokens=4, frame_fps=1.0)
+    for i, (wd, ht) in enumerate([(320, 180), (90, 200), (112, 112)]):
+        pic = source_frame(wd, ht, 300 + i)
+        a.load_one_frame(frame_object=pic)                                    # numpy HWC, as np.array(PIL image)
+        b.load_one_frame(frame=torch.from_numpy(io.ingest_frame(pic, "pil", out=112)).to(cuda))
+    for (ta, ea), (tb, eb) in zip(a.frame_embeds_queue, b.frame_embeds_queue):
+        assert ta == tb and torch.equal(ea, eb)
+    with pytest.raises(ValueError):
+        a.load_one_frame()
+
+
 def test_errors(cuda):
     with pytest.raises(ValueError):
         A.ingest_frames(torch.zeros(1, 8, 8, 3, dtype=torch.uint8, device=cuda), "lanczos")
