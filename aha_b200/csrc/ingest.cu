@@ -299,6 +299,10 @@ int op_ingest_frames(const uint8_t* src_hwc, int n, int h, int w, int flavour, u
   AHA_REQUIRE(n >= 0 && h >= 1 && w >= 1 && h <= 16384 && w <= 16384, "ingest_frames: bad frame geometry");
   AHA_REQUIRE(out >= 4 && out % 4 == 0 && out <= 1536, "ingest_frames: the canvas side must be a multiple of 4, at most 1536");
   AHA_REQUIRE((reinterpret_cast<uintptr_t>(out_chw) & 3) == 0, "ingest_frames: the canvas must be 4-byte aligned");
+  // Pillow >= 11 resamples pictures more than 100 times taller than wide vertical pass first (Image.resize), the
+  // reference's pinned 10.4.0 predates that; the result depends on the installed version, so the case is refused
+  AHA_REQUIRE(!(flavour == 1 && (long long)h > 100LL * w && out < h),
+              "ingest_frames: PIL flavour: height > 100 x width is resampled in a Pillow-version-dependent pass order; not supported");
   if (n == 0) return AHA_OK;
   AHA_REQUIRE(n <= 65535, "ingest_frames: at most 65535 frames per call");
   std::lock_guard<std::mutex> lock(g_tab_mutex);

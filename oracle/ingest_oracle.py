@@ -18,6 +18,9 @@ restated below:
   * Pillow Resample.c, 8 bits per channel: bicubic (a = -0.5) with the support stretched by the down-scale factor,
     coefficients normalised in double and rounded to 22-bit fixed point, horizontal pass into an 8-bit image, then the
     vertical pass, each `clip8((sum + 2^21) >> 22)`.
+Versions: the reference pins opencv-python 4.10.0.84 and pillow 10.4.0 (requirements.txt:33,36); 4.13.0 / 12.2.0 are what
+this image has.  The one known difference on this path: Pillow 12.2 resamples pictures more than 100 times taller than
+wide vertical pass first (PIL/Image.py, resize); that geometry is refused (ValueError) instead of guessed.
 PINNED: both restatements are executed against cv2 / PIL themselves (tests/golden/make_golden_ingest.py, run in the
 build container; the goldens in tests/golden/ingest.npz are the libraries' outputs, not this file's)."""
 from __future__ import annotations
@@ -150,6 +153,10 @@ def _pil_pass(img: np.ndarray, dst: int, axis: int) -> np.ndarray:
 def pil_resize_bicubic(img: np.ndarray, new_w: int, new_h: int) -> np.ndarray:
     """img [h, w, c] uint8 -> [new_h, new_w, c], bit-identical to PIL.Image.resize((new_w, new_h)) (BICUBIC)."""
     h, w, _ = img.shape
+    if h > w * 100 and new_h < h:
+        # Pillow 12.2 Image.resize runs the vertical pass first for such pictures; the reference's pinned 10.4.0
+        # (requirements.txt:36) predates that special case.  Version-dependent: refused here and by the kernel.
+        raise ValueError("height > 100 x width: Pillow-version-dependent pass order")
     out = img
     if new_w != w:
         out = _pil_pass(out, new_w, 1)

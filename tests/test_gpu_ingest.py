@@ -101,6 +101,47 @@ def test_demo_driver_takes_raw_pictures(cuda):
         a.load_one_frame()
 
 
+def _library_canvas(pic, flavour):
+    """cv2 / PIL themselves with the reference's call sequence (test/inference.py:540-563, live_infer_for_video.py:107-119)."""
+    h, w = pic.shape[:2]
+    nw, nh, left, top = io.fit_geometry(w, h)
+    border = dict(top=top, bottom=(384 - nh + 1) // 2, left=left, right=(384 - nw + 1) // 2)
+    if flavour == "cv2":
+        cv2 = pytest.importorskip("cv2")
+        c = cv2.copyMakeBorder(cv2.resize(pic, (nw, nh)), borderType=cv2.BORDER_CONSTANT, value=(0, 0, 0), **border)
+        return np.transpose(cv2.cvtColor(c, cv2.COLOR_BGR2RGB), (2, 0, 1))
+    Image = pytest.importorskip("PIL.Image")
+    ImageOps = pytest.importorskip("PIL.ImageOps")
+    r = Image.fromarray(pic).resize((nw, nh))
+    c = ImageOps.expand(r, border=(border["left"], border["top"], border["right"], border["bottom"]), fill=(0, 0, 0))
+    return np.transpose(np.array(c), (2, 0, 1))
+
+
+@pytest.mark.parametrize("flavour", ["cv2", "pil"])
+def test_random_geometries_against_the_libraries(cuda, flavour):
+    """Seeded random and extreme geometries, compared with cv2 / PIL run on the box (skipped where they are absent)
+    and with the oracle."""
+    rng = np.random.default_rng(11)
+    geos = [(1000, 3), (3, 290), (2, 2), (1, 1), (383, 384), (384, 383), (769, 768), (768, 769), (767, 767), (2500, 1407),
+            (1536, 864), (192, 192), (191, 192)] + [(int(rng.integers(2, 1400)), int(rng.integers(2, 1400))) for _ in range(12)]
+    for w, h in geos:
+        pic = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        got = A.ingest_frames(torch.from_numpy(pic).to(cuda)[None], flavour)[0].cpu().numpy()
+        assert np.array_equal(got, _library_canvas(pic, flavour)), (flavour, w, h)
+        assert np.array_equal(got, io.ingest_frame(pic, flavour)), (flavour, w, h)
+
+
+def test_refused_geometries(cuda):
+    # cv2 raises on an empty target (int(2 / 1000 * 384) == 0); Pillow's pass order for h > 100 w depends on its version
+    with pytest.raises(ValueError, match="empty image"):
+        A.ingest_frames(torch.zeros(1, 2, 1000, 3, dtype=torch.uint8, device=cuda), "cv2")
+    with pytest.raises(ValueError, match="version-dependent"):
+        A.ingest_frames(torch.zeros(1, 1000, 3, 3, dtype=torch.uint8, device=cuda), "pil")
+    with pytest.raises(ValueError):
+        io.ingest_frame(np.zeros((1000, 3, 3), np.uint8), "pil")
+    assert tuple(A.ingest_frames(torch.zeros(1, 1000, 3, 3, dtype=torch.uint8, device=cuda), "cv2").shape) == (1, 3, 384, 384)
+
+
 def test_errors(cuda):
     with pytest.raises(ValueError):
         A.ingest_frames(torch.zeros(1, 8, 8, 3, dtype=torch.uint8, device=cuda), "lanczos")
