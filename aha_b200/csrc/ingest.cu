@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restri
       const int lo = __ldg(t.x_lo + x), ng = (__ldg(t.x_cnt + x) + 3) >> 2;
       const int4* k4 = reinterpret_cast<const int4*>(t.x_k + (size_t)x * t.ksx);
       const uint32_t* wp[R];
-      uint32_t carry[R];
-      int sh[R], acc[R][3];
+      uint32_t carry[R], lo8[R][3], mid8[R][3];
+      int sh[R], hi8[R][3];
 #pragma unroll
       for (int u = 0; u < R; ++u) {
         const int row = r0 + u < nrows ? r0 + u : nrows - 1;         // rows past the tile: clamped, sums dropped
@@ -168,10 +168,11 @@ __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restri
         wp[u] = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
         sh[u] = (int)(a & 3) * 8;
         carry[u] = ingest_ldw(wp[u], end_up);
-        acc[u][0] = acc[u][1] = acc[u][2] = 1 << (kPilBits - 1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { lo8[u][c] = mid8[u][c] = 0u; hi8[u][c] = 0; }
       }
       for (int g = 0; g < ng; ++g) {
-        const int4 kk = __ldg(k4 + g);
+        const int4 kk = __ldg(k4 + g);       // the four taps of the group as byte limbs: low, middle, high (signed)
 #pragma unroll
         for (int u = 0; u < R; ++u) {
           const uint32_t l1 = ingest_ldw(wp[u] + 1, end_up), l2 = ingest_ldw(wp[u] + 2, end_up),
@@ -180,12 +181,16 @@ __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restri
           const uint32_t s0 = __funnelshift_r(carry[u], l1, sh[u]), s1 = __funnelshift_r(l1, l2, sh[u]),
                          s2 = __funnelshift_r(l2, l3, sh[u]);       // twelve bytes = four interleaved pixels
           carry[u] = l3;
-          acc[u][0] += (int)(s0 & 0xff) * kk.x + (int)(s0 >> 24) * kk.y + (int)((s1 >> 16) & 0xff) * kk.z +
-                       (int)((s2 >> 8) & 0xff) * kk.w;
-          acc[u][1] += (int)((s0 >> 8) & 0xff) * kk.x + (int)(s1 & 0xff) * kk.y + (int)(s1 >> 24) * kk.z +
-                       (int)((s2 >> 16) & 0xff) * kk.w;
-          acc[u][2] += (int)((s0 >> 16) & 0xff) * kk.x + (int)((s1 >> 8) & 0xff) * kk.y + (int)(s2 & 0xff) * kk.z +
-                       (int)(s2 >> 24) * kk.w;
+          // the four bytes of one channel: stream bytes c, c + 3, c + 6, c + 9
+          const uint32_t px[3] = {__byte_perm(__byte_perm(s0, s1, 0x0630), s2, 0x5210),
+                                  __byte_perm(__byte_perm(s0, s1, 0x0741), s2, 0x6210),
+                                  __byte_perm(__byte_perm(s0, s1, 0x0052), s2, 0x7410)};
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            lo8[u][c] = __dp4a(px[c], (uint32_t)kk.x, lo8[u][c]);
+            mid8[u][c] = __dp4a(px[c], (uint32_t)kk.y, mid8[u][c]);
+            asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(hi8[u][c]) : "r"(px[c]), "r"(kk.z), "r"(hi8[u][c]));
+          }
         }
       }
 #pragma unroll
@@ -193,7 +198,8 @@ __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restri
         if (r0 + u < nrows) {
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
-            const int v = acc[u][c] >> kPilBits;
+            // sum of byte * (low + 256 middle + 65536 high); exact modulo 2^32 and the true sum fits
+            const int v = (int)(lo8[u][c] + (mid8[u][c] << 8) + ((uint32_t)hi8[u][c] << 16) + (1u << (kPilBits - 1))) >> kPilBits;
             hor[(r0 + u) * hp + x * 3 + c] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
           }
         }
@@ -261,6 +267,19 @@ int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
     t.ksx = t.ksy = 2;
   } else {
     t.ksx = pil_axis(w, t.new_w, 4, xl, xc, xk);       // rows of four-tap groups, 16-byte aligned
+    // the horizontal pass multiplies with dp4a: every group of four taps is stored as three words of byte limbs,
+    // k = low + 256 * middle + 65536 * high with low, middle in [0, 255] and high a signed byte
+    for (size_t g = 0; g + 3 < xk.size(); g += 4) {
+      uint32_t lo8 = 0, mid8 = 0, hi8 = 0;
+      for (int i = 0; i < 4; ++i) {
+        const int k = xk[g + i], hi = k >> 16;
+        AHA_REQUIRE(hi >= -128 && hi <= 127, "ingest_frames: coefficient out of the 24-bit range");
+        lo8 |= (uint32_t)(k & 255) << (8 * i);
+        mid8 |= (uint32_t)((k >> 8) & 255) << (8 * i);
+        hi8 |= (uint32_t)(hi & 255) << (8 * i);
+      }
+      xk[g] = (int)lo8; xk[g + 1] = (int)mid8; xk[g + 2] = (int)hi8; xk[g + 3] = 0;
+    }
     t.ksy = pil_axis(h, t.new_h, 1, yl, yc, yk);
     // rows per CTA: the largest tile whose horizontal-pass image stays under 100 KB (two CTAs per SM)
     for (int th = 16; th >= 1; th /= 2) {
