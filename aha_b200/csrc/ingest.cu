@@ -25,7 +25,11 @@ struct IngestTables {            // device arrays of one (h, w, flavour, out) ge
   int* y_lo = nullptr;  int* y_cnt = nullptr;  int* y_k = nullptr;   // cv2: y_lo = row0, y_cnt = row1
   void* block = nullptr;
 };
-IngestTables g_tab;
+// tables of the last few geometries (a demo alternates between a video geometry and single pictures); the oldest entry
+// is freed only after a device-wide synchronise, whatever streams its launches ran on
+constexpr size_t kTableCacheEntries = 8;
+std::vector<IngestTables> g_tabs;
+IngestTables g_tab;               // the entry of the current call
 std::mutex g_tab_mutex;
 
 // ---- OpenCV 8-bit INTER_LINEAR: index + two 11-bit coefficients per destination coordinate
@@ -250,8 +254,15 @@ __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restri
 int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
   int device = 0;
   AHA_CUDA(cudaGetDevice(&device));
-  if (g_tab.h == h && g_tab.w == w && g_tab.flavour == flavour && g_tab.out == out && g_tab.device == device) return AHA_OK;
-  if (g_tab.block) { AHA_CUDA(cudaStreamSynchronize(st)); cudaFree(g_tab.block); g_tab = IngestTables{}; }
+  for (const IngestTables& e : g_tabs)
+    if (e.h == h && e.w == w && e.flavour == flavour && e.out == out && e.device == device) { g_tab = e; return AHA_OK; }
+  if (g_tabs.size() >= kTableCacheEntries) {
+    AHA_CUDA(cudaSetDevice(g_tabs.front().device));      // the oldest entry may belong to another device of the process
+    AHA_CUDA(cudaDeviceSynchronize());
+    cudaFree(g_tabs.front().block);
+    AHA_CUDA(cudaSetDevice(device));
+    g_tabs.erase(g_tabs.begin());
+  }
   IngestTables t;
   t.h = h; t.w = w; t.flavour = flavour; t.out = out; t.device = device;
   // test/inference.py:540-545: the longer side becomes `out`, the other int((short / long) * out), in float64
@@ -308,6 +319,7 @@ int build_tables(int h, int w, int flavour, int out, cudaStream_t st) {
   t.x_lo = base + o_xl; t.x_cnt = base + o_xc; t.x_k = base + o_xk;
   t.y_lo = base + o_yl; t.y_cnt = base + o_yc; t.y_k = base + o_yk;
   g_tab = t;
+  g_tabs.push_back(t);
   return AHA_OK;
 }
 
