@@ -88,12 +88,20 @@ int pil_axis(int src, int dst, int pad_to, std::vector<int>& lo, std::vector<int
   return ksize;
 }
 
-// ---- flavour 0.  One thread = four consecutive canvas pixels of one row, all three colour planes.
+__device__ __forceinline__ uint32_t ingest_ldw(const uint32_t* p, uintptr_t end_up) {
+  return reinterpret_cast<uintptr_t>(p) < end_up ? __ldg(p) : 0u;     // words past the source only sit under zero taps
+}
+
+// ---- flavour 0.  One thread = four consecutive canvas pixels of one row, all three colour planes.  The two taps of a row
+// are neighbouring pixels = six consecutive bytes: read as aligned words and funnel-shifted (at the right border the
+// second tap carries a zero coefficient, so what lies under it does not matter).
 __global__ void __launch_bounds__(384) ingest_cv2_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
                                                          IngestTables t) {
   const int X0 = threadIdx.x * 4, Y = blockIdx.x * blockDim.y + threadIdx.y, n = blockIdx.y;
   if (X0 >= t.out || Y >= t.out) return;
-  const uint8_t* img = src + (size_t)n * t.h * t.w * 3;
+  const size_t frame_bytes = (size_t)t.h * t.w * 3;
+  const uint8_t* img = src + (size_t)n * frame_bytes;
+  const uintptr_t end_up = (reinterpret_cast<uintptr_t>(src + (size_t)gridDim.y * frame_bytes) + 3) & ~(uintptr_t)3;
   const int dy = Y - t.top;
   uint32_t px[3] = {0u, 0u, 0u};             // four packed bytes per output plane
   if (dy >= 0 && dy < t.new_h) {
@@ -106,13 +114,25 @@ __global__ void __launch_bounds__(384) ingest_cv2_kernel(const uint8_t* __restri
     for (int i = 0; i < 4; ++i) {
       const int dx = X0 + i - t.left;
       if (dx < 0 || dx >= t.new_w) continue;
-      int c0, c1, a0, a1;
-      if (t.area_fast) { c0 = 2 * dx; c1 = 2 * dx + 1; a0 = a1 = 0; }
-      else { c0 = __ldg(t.x_lo + dx); c1 = __ldg(t.x_cnt + dx); a0 = __ldg(t.x_k + 2 * dx); a1 = __ldg(t.x_k + 2 * dx + 1); }
+      int c0, a0, a1;                        // the second tap is pixel c0 + 1 (or carries a zero coefficient)
+      if (t.area_fast) { c0 = 2 * dx; a0 = a1 = 0; }
+      else { c0 = __ldg(t.x_lo + dx); a0 = __ldg(t.x_k + 2 * dx); a1 = __ldg(t.x_k + 2 * dx + 1); }
+      uint32_t t0[2], t1[2];                 // bytes 0..5 of the pixel pair in row0 / row1
+      {
+        const uintptr_t a0p = reinterpret_cast<uintptr_t>(row0 + c0 * 3), a1p = reinterpret_cast<uintptr_t>(row1 + c0 * 3);
+        const uint32_t* w0 = reinterpret_cast<const uint32_t*>(a0p & ~(uintptr_t)3);
+        const uint32_t* w1 = reinterpret_cast<const uint32_t*>(a1p & ~(uintptr_t)3);
+        const int sh0 = (int)(a0p & 3) * 8, sh1 = (int)(a1p & 3) * 8;
+        const uint32_t x0 = ingest_ldw(w0, end_up), x1 = ingest_ldw(w0 + 1, end_up), x2 = ingest_ldw(w0 + 2, end_up);
+        const uint32_t y0 = ingest_ldw(w1, end_up), y1 = ingest_ldw(w1 + 1, end_up), y2 = ingest_ldw(w1 + 2, end_up);
+        t0[0] = __funnelshift_r(x0, x1, sh0); t0[1] = __funnelshift_r(x1, x2, sh0);
+        t1[0] = __funnelshift_r(y0, y1, sh1); t1[1] = __funnelshift_r(y1, y2, sh1);
+      }
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const int s00 = __ldg(row0 + c0 * 3 + c), s01 = __ldg(row0 + c1 * 3 + c);
-        const int s10 = __ldg(row1 + c0 * 3 + c), s11 = __ldg(row1 + c1 * 3 + c);
+        const int s00 = (int)((t0[0] >> (8 * c)) & 0xff), s10 = (int)((t1[0] >> (8 * c)) & 0xff);
+        const int s01 = c == 0 ? (int)(t0[0] >> 24) : (int)((t0[1] >> (8 * (c - 1))) & 0xff);
+        const int s11 = c == 0 ? (int)(t1[0] >> 24) : (int)((t1[1] >> (8 * (c - 1))) & 0xff);
         int v;
         if (t.area_fast) v = (s00 + s01 + s10 + s11 + 2) >> 2;
         else {
@@ -137,10 +157,6 @@ __global__ void __launch_bounds__(384) ingest_cv2_kernel(const uint8_t* __restri
 // bytes under its taps as aligned words (funnel-shifted to the pixel boundary), four pixels = three words at a time,
 // with the four coefficients of the group in one 16-byte load.  The vertical pass owns four adjacent bytes of the
 // horizontal image per thread.
-__device__ __forceinline__ uint32_t ingest_ldw(const uint32_t* p, uintptr_t end_up) {
-  return reinterpret_cast<uintptr_t>(p) < end_up ? __ldg(p) : 0u;     // words past the source only sit under zero taps
-}
-
 __global__ void __launch_bounds__(384) ingest_pil_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out,
                                                          IngestTables t) {
   extern __shared__ __align__(16) uint8_t hor[];     // [rows under the tile][hp], hp = new_w * 3 rounded up to 4
