@@ -80,12 +80,17 @@ def load_video_for_testing(decoded_bgr: torch.Tensor, input_fps: float, output_f
                                                max_num_frames, frames_readable=T)
     if not kept:
         return None, None, None, None
-    idx = torch.as_tensor(kept, dtype=torch.long, device=decoded_bgr.device)
     outs = []
     for s in range(0, len(kept), batch):
-        part = decoded_bgr.index_select(0, idx[s:s + batch])
-        if not part.is_cuda:
-            part = part.pin_memory().to(device, non_blocking=True)
+        chunk = kept[s:s + batch]
+        if decoded_bgr.is_cuda:
+            part = decoded_bgr.index_select(0, torch.as_tensor(chunk, dtype=torch.long, device=decoded_bgr.device))
+        else:
+            # frame by frame straight into the device batch (asynchronous when the clip sits in pinned memory): no
+            # gathered or re-pinned copy of the clip on the host
+            part = torch.empty((len(chunk),) + tuple(decoded_bgr.shape[1:]), dtype=torch.uint8, device=device)
+            for j, i in enumerate(chunk):
+                part[j].copy_(decoded_bgr[i], non_blocking=True)
         outs.append(ingest_frames(part, "cv2"))
     frames = outs[0] if len(outs) == 1 else torch.cat(outs)
     if return_true_frames:
