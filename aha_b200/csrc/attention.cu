@@ -110,8 +110,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const int kt0 = split * per;
   const int nkt = max(0, min(nkt_all, kt0 + per) - kt0);   // key tiles of this CTA: kt0 .. kt0 + nkt - 1
   const int stage_bytes = DB * kAtomBytes;
+  // K / V tensor maps: per segment (device memory) when the streams of a batched launch own separate cache slabs
+  const void* tmk = seg.k_tmap ? seg.k_tmap : static_cast<const void*>(&tmap_k);
+  const void* tmv = seg.v_tmap ? seg.v_tmap : static_cast<const void*>(&tmap_v);
 
-  if (warp == 0 && lane == 0) { prefetch_tensormap(&tmap_q); prefetch_tensormap(&tmap_k); prefetch_tensormap(&tmap_v); }
+  if (warp == 0 && lane == 0) { prefetch_tensormap(&tmap_q); prefetch_tensormap(tmk); prefetch_tensormap(tmv); }
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
     for (int s = 0; s < kStagesKV; ++s) {
@@ -139,8 +142,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     for (int it = 0; it < nkt; ++it) {
       const int key0 = (kt0 + it) * kTile;
       for (int b = 0; b < DB; ++b) {
-        tma_prefetch_2d(&tmap_k, k_col + b * 64, k_row + key0);
-        tma_prefetch_2d(&tmap_v, v_col + b * 64, v_row + key0);
+        tma_prefetch_2d(tmk, k_col + b * 64, k_row + key0);
+        tma_prefetch_2d(tmv, v_col + b * 64, v_row + key0);
       }
     }
   }
@@ -182,7 +185,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           mbar_arrive_expect_tx(&k_full[s], stage_bytes);
           const int key0 = (kt0 + it) * kTile;
           for (int b = 0; b < DB; ++b)
-            tma_load_2d(sK + s * stage_bytes + b * kAtomBytes, &tmap_k, &k_full[s], k_col + b * 64, k_row + key0);
+            tma_load_2d(sK + s * stage_bytes + b * kAtomBytes, tmk, &k_full[s], k_col + b * 64, k_row + key0);
         }
         if (!p.pf_early)
           l2_prefetch_slice(p.pf, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
@@ -199,7 +202,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           mbar_arrive_expect_tx(&v_full[s], stage_bytes);
           const int key0 = (kt0 + it) * kTile;
           for (int b = 0; b < DB; ++b)
-            tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, &tmap_v, &v_full[s], v_col + b * 64, v_row + key0);
+            tma_load_2d(sV + s * stage_bytes + b * kAtomBytes, tmv, &v_full[s], v_col + b * 64, v_row + key0);
         }
       }
     } else if (warp == 1) {
@@ -467,15 +470,31 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       dbg_stamp(ts, 8);
       __threadfence();
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      int* cnt = p.ws_counters + group_lin;
-      if (threadIdx.x == 128) {
-        atomicAdd(cnt, 1);
-        uint32_t spins = 0;
-        while (*reinterpret_cast<volatile int*>(cnt) < splits) {
-          if (++spins > (1u << 24)) { printf("aha_b200: attention split arrival wait timed out (group %d)\n", group_lin); __trap(); }
+      bool merge_all = false;
+      if (p.merge_last) {
+        // grids that are not co-resident: nobody waits - the last split to arrive merges every chunk of the group
+        int* cnt = p.ws_pcounters + group_lin;
+        if (threadIdx.x == 128) {
+          const int old = atomicAdd(cnt, 1);
+          const int last = (old == splits - 1) ? 1 : 0;
+          if (last) *cnt = 0;                       // self-resetting
+          xch[0] = __int_as_float(last);
         }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        merge_all = __float_as_int(xch[0]) != 0;
+      } else {
+        int* cnt = p.ws_counters + group_lin;
+        if (threadIdx.x == 128) {
+          atomicAdd(cnt, 1);
+          uint32_t spins = 0;
+          while (*reinterpret_cast<volatile int*>(cnt) < splits) {
+            if (++spins > (1u << 24)) { printf("aha_b200: attention split arrival wait timed out (group %d)\n", group_lin); __trap(); }
+          }
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (!p.merge_last || merge_all) {
+      const int c_first = merge_all ? 0 : split, c_step = merge_all ? 1 : splits;
       __threadfence();
       dbg_stamp(ts, 9);
       const float* grp = p.ws_partial + (size_t)group_lin * splits * cta_floats;
@@ -483,10 +502,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // pieces of this CTA's first chunk are requested together with the statistics: one L2 round trip, not two
       // (a 16-column chunk is shared by the two threads of a row: 8 columns each)
       float v[8][8];
-      if (split < (p.d_pad >> 4)) {
+      if (c_first < (p.d_pad >> 4)) {
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
-          const float* peer = grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)(split * 16 + half * 8) * kTile + row;
+          const float* peer = grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)(c_first * 16 + half * 8) * kTile + row;
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[s][j] = __ldcg(peer + (size_t)j * kTile);
         }
@@ -511,9 +530,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const float inv = L > 0.f ? 1.f / L : 0.f;
       bf16* orow = p.out + (size_t)(seg.out_row0 + tok) * p.out_ld + (size_t)(blk * p.group + (m % p.group)) * p.d;
 #pragma unroll 1
-      for (int c = split; c < (p.d_pad >> 4); c += splits) {
+      for (int c = c_first; c < (p.d_pad >> 4); c += c_step) {
         const int cc = c * 16 + half * 8;
-        if (c != split) {
+        if (c != c_first) {
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
             const float* peer = grp + (size_t)(s < splits ? s : 0) * cta_floats + (size_t)cc * kTile + row;
@@ -543,6 +562,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
       }
       dbg_stamp(ts, 10);
+      }
     }
   }
 
@@ -579,10 +599,14 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   rc = get_tmap(p.k, (int)p.k_rows_total, p.k_ld, p.k_ld, kTile, &tk); if (rc) return rc;
   rc = get_tmap(p.v, (int)p.v_rows_total, p.v_ld, p.v_ld, kTile, &tv); if (rc) return rc;
   const int smem = AttnSmem::total(DB);
-  static int attr_smem = 0;
-  if (attr_smem < smem) {
+  static int attr_smem[16] = {0};          // function attributes and the SM count are per device
+  static int sm_counts[16] = {0};
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  AHA_REQUIRE(dev >= 0 && dev < 16, "attention: device index out of range");
+  if (attr_smem[dev] < smem) {
     AHA_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_smem = smem;
+    attr_smem[dev] = smem;
   }
   // key-axis split: a frame chunk has only a handful of (query tile, kv head) pairs, far fewer than SMs
   const int q_tiles = (p.nq_rows + kTile - 1) / kTile;
@@ -590,8 +614,8 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   int max_tiles = 0;
   for (int i = 0; i < p.n_segs; ++i) max_tiles = max_tiles > (p.segs[i].klen + kTile - 1) / kTile ? max_tiles : (p.segs[i].klen + kTile - 1) / kTile;
   // the splits of a group wait for each other, so the whole grid must be resident at once: one CTA per SM
-  static int sm_count = 0;
-  if (!sm_count) { int dev = 0; AHA_CUDA(cudaGetDevice(&dev)); AHA_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev)); }
+  if (!sm_counts[dev]) AHA_CUDA(cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev));
+  const int sm_count = sm_counts[dev];
   int splits = 1;
   if (ctas < sm_count && max_tiles > 1 && !p.no_split) {
     splits = sm_count / ctas;
@@ -601,14 +625,31 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
     const int per = (max_tiles + splits - 1) / splits;
     splits = (max_tiles + per - 1) / per;       // no empty splits for the longest segment
   }
+  // Long key axes with too few (query tile, head) pairs to fill the device evenly (8 streams x 4 kv heads x 3 query tiles
+  // = 96 CTAs of 64 key tiles each at a window of 8192): split further than co-residency allows and let the last split to
+  // arrive merge (nobody waits).  Cost model: waves x key tiles per CTA, one tile's worth of time for parking + merging.
+  p.merge_last = 0;
+  if (!p.no_split && max_tiles >= 16 && ctas <= GemmWorkspace::kPCounters / 2) {
+    long best = (long)((ctas * splits + sm_count - 1) / sm_count) * ((max_tiles + splits - 1) / splits) + (splits > 1 ? 1 : 0);
+    int best_s = splits;
+    for (int s = 2; s <= 8 && s <= max_tiles; ++s) {
+      const int per = (max_tiles + s - 1) / s;
+      if ((max_tiles + per - 1) / per != s) continue;
+      const long cost = (long)((ctas * s + sm_count - 1) / sm_count) * per + 1;
+      if (cost < best) { best = cost; best_s = s; }
+    }
+    if (const char* e = getenv("AHA_ATTN_SPLITS_LONG")) { const int v = atoi(e); if (v >= 1 && v <= 8) best_s = v; }
+    if (best_s != splits && ctas * best_s > sm_count) { splits = best_s; p.merge_last = 1; }
+  }
   if (splits > 1) {
     const size_t need = (size_t)ctas * splits * ((size_t)kTile * p.d_pad + 2 * kTile) * sizeof(float);
-    if (need > GemmWorkspace::kPartialBytes || ctas > GemmWorkspace::kCounters) splits = 1;
+    if (need > GemmWorkspace::kPartialBytes || (!p.merge_last && ctas > GemmWorkspace::kCounters)) { splits = 1; p.merge_last = 0; }
   }
   if (splits > 1) {
     GemmSplitScratch sc;
-    rc = aha_split_scratch(st, &sc); if (rc) return rc;     // advances the stream's counter bank: only for a real split launch
-    p.ws_partial = sc.partial; p.ws_counters = sc.bank; p.ws_zero = sc.zero; p.ws_zero_n = sc.zero_n;
+    rc = aha_split_scratch(st, &sc, !p.merge_last); if (rc) return rc;     // (advances the stream's counter bank: only for a real waiting-split launch)
+    p.ws_partial = sc.partial; p.ws_counters = sc.bank; p.ws_zero = sc.zero; p.ws_zero_n = p.merge_last ? 0 : sc.zero_n;
+    p.ws_pcounters = sc.pcounters;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(q_tiles, p.n_blocks, p.n_segs * splits);

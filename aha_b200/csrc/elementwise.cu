@@ -252,7 +252,8 @@ __global__ void embed_assemble_kernel(const bf16* __restrict__ table, const int6
   const bf16* src;
   if (row < n_ids) {
     long long id = ids[row];
-    if (id < 0 || id >= vocab) id = 0;  // torch would raise; ids are validated on the host side of the wrapper
+    if (id < 0 || id >= vocab) id = 0;  // memory safety only: torch would raise, and so do the Python wrappers (model.py:
+                                        // assemble_chunk and get_input_embeddings check the range before this launch)
     src = table + (size_t)id * hidden;
   } else {
     src = frame_embeds + (size_t)(row - n_ids) * hidden;
@@ -500,7 +501,7 @@ int op_pool(const bf16* x, bf16* out, int frames, int side, int channels, int st
 
 int op_rope_table(const RopeTableArgs& a, int n_streams, int q, int d, const float* inv_freq_dev, bf16* cos_out,
                   bf16* sin_out, cudaStream_t st) {
-  AHA_REQUIRE(n_streams > 0 && n_streams <= 16 && q > 0 && d % 2 == 0, "rope_table: bad shape");
+  AHA_REQUIRE(n_streams > 0 && n_streams <= 32 && q > 0 && d % 2 == 0, "rope_table: bad shape");
   dim3 grid((q * (d / 2) + 127) / 128, n_streams);
   return launch_pdl(rope_table_kernel, grid, dim3(128), 0, st, a, q, d, inv_freq_dev, cos_out, sin_out);
 }

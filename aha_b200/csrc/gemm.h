@@ -30,6 +30,7 @@ struct GemmParams {
   int* ws_counters;     // split-K arrival counter per tile, in this launch's counter bank (zero on entry)
   int* ws_zero;         // the OTHER counter bank, ws_zero_n ints: this launch zeroes it for the next split launch
   int ws_zero_n;
+  int* ws_pcounters;    // persistent skinny kernel: self-resetting counter per (tile, column group), zero between launches
   unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
   unsigned long long* dbg_all;  // bring-up: (accumulator complete, exit) of every CTA on the global ns timer, or null
   L2Prefetch pf;        // weights of LATER kernels to request into L2 once this CTA's own loads are in flight
@@ -73,6 +74,7 @@ struct GemmCall {
 struct GemmSplitScratch {
   float* partial = nullptr;
   int* counters = nullptr;       // all banks (allocation base)
+  int* pcounters = nullptr;      // self-resetting counters of the last-arriver merges (persistent skinny GEMM, long-key attention)
   int* bank = nullptr;           // this launch's bank
   int* zero = nullptr;           // the bank to zero
   int zero_n = 0;
@@ -82,6 +84,7 @@ struct GemmWorkspace {
   int sm_count = 148;
   static constexpr size_t kPartialBytes = 64u << 20;
   static constexpr int kCounters = 1024;
+  static constexpr int kPCounters = 8192;   // [0, 4096): persistent skinny GEMM, [4096, 8192): attention last-arriver merge
   std::map<cudaStream_t, GemmSplitScratch> scratch;
   std::mutex mu;
 };
@@ -90,7 +93,8 @@ int gemm_workspace_create(GemmWorkspace* w, int device);
 bool aha_sm_shared();   // aha_set_sm_sharing(1) is in effect
 // Per-stream split scratch of the default workspace for ONE split launch (every call advances the stream's bank
 // sequence: call it only when the split kernel is really launched).  out->bank points at the attention half.
-int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out);
+// advance = false: only the partial workspace and the self-resetting counters (attention half) are wanted; no bank switch.
+int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out, bool advance = true);
 void gemm_workspace_destroy(GemmWorkspace* w);
 // Enqueues the GEMM on `stream`. Returns AHA_OK or a negative error code.
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream);
@@ -99,6 +103,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream);
 int get_tmap(const void* ptr, int rows, int K, int ld, int box_rows, CUtensorMap* out);
 // Launch counters (bench.py's gpu_launches claim).
 extern unsigned long long g_aha_launch_count;
+
+// Largest token count the skinny (weights = MMA A operand) orientation takes: 4 column tiles of the persistent kernel.
+constexpr int kGemmSkinnyMaxTokens = 832;
 
 // Optional per-launch CUDA-event timing (aha_profile_gemm / aha_profile_gemm_read): returns null when disabled.
 struct ProfSlot;

@@ -237,17 +237,17 @@ __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* 
 // feature; their squares are summed over the tile's 128 features (shuffles, then the four warps through shared memory)
 // and the tile's partial goes to sumsq_out[feature tile][token].  Called by all four epilogue warps together.
 __device__ __forceinline__ void emit_sumsq16(const GemmParams& p, float (*sq_red)[16], const float (&acc)[16], bool fvalid,
-                                             int ew, int lane, int tok0) {
+                                             int ew, int lane, int tok0, int tile, int bar_id = 1) {
   const int ntok = min(16, p.Nb - tok0);
 #pragma unroll
   for (int t = 0; t < 16; ++t) {
     const float s = warp_sum(fvalid ? acc[t] * acc[t] : 0.f);
     if (lane == 0) sq_red[ew][t] = s;
   }
-  asm volatile("bar.sync 1, 128;" ::: "memory");
+  asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
   if (ew == 0 && lane < ntok)
-    p.sumsq_out[(size_t)blockIdx.x * p.sumsq_ld + tok0 + lane] = sq_red[0][lane] + sq_red[1][lane] + sq_red[2][lane] + sq_red[3][lane];
-  asm volatile("bar.sync 1, 128;" ::: "memory");
+    p.sumsq_out[(size_t)tile * p.sumsq_ld + tok0 + lane] = sq_red[0][lane] + sq_red[1][lane] + sq_red[2][lane] + sq_red[3][lane];
+  asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
 }
 
 // Split-K merge of one 16-column chunk: the partials of all S splits are requested before the first use (one L2 round
@@ -659,7 +659,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           }
           if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
           else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
-          if (p.sumsq_out) emit_sumsq16(p, sq_red, acc, fvalid, ew, lane, b0 + jc);
+          if (p.sumsq_out) emit_sumsq16(p, sq_red, acc, fvalid, ew, lane, b0 + jc, blockIdx.x);
           dbg_stamp(ts, 9 + (jc >> 4) * 2);
         }
       } else if (p.out_f32) {
@@ -747,7 +747,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         if (kSwap) epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc, (pre_res && jc == split * 16) ? res : nullptr);
         else epi_tall16<kAct>(p, a0 + i, b0 + jc, acc);
-        if (kSwap && p.sumsq_out) emit_sumsq16(p, sq_red, acc, fvalid, ew, lane, b0 + jc);
+        if (kSwap && p.sumsq_out) emit_sumsq16(p, sq_red, acc, fvalid, ew, lane, b0 + jc, blockIdx.x);
       }
     }
     tc_fence_before();
@@ -893,6 +893,263 @@ gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Persistent skinny ("swap") GEMM for batched decoder steps: 256 < tokens <= 832 (e.g. 8 streams x 49 frame tokens = 392).
+// A = weights (128 feature rows per tile), B = tokens in column tiles of 208 (392 tokens = 2 tiles, 94 % of the MMA N
+// dimension used; the tall orientation would pad 392 token rows to 512).  One CTA per SM walks over work items
+// (feature tile, k split, token tile) - the token tiles of a feature tile are neighbours in the item order, so the CTAs
+// that share a weight tile pull it at the same time and HBM sees it once.  Two 208-column accumulators in TMEM: the
+// eight epilogue warps (two groups of four: columns [0,112) and [112,208)) drain item t under the main loop of item t+1.
+// Split-K items park their fp32 partial in the L2 workspace and bump the counter of their (tile, column group); the
+// LAST arriver reduces all splits in split order (deterministic) and runs the epilogue - nobody waits, so the items of a
+// tile need not be co-resident.  The counters reset themselves.  Same epilogues as the one-shot skinny kernel: bias,
+// SiLU*mul on interleaved gate|up rows, residual, folded RMSNorm on both sides (GemmCall).
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kPsBN = 208;
+struct PSCfg {
+  static constexpr int kStages = 5;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBBytes = kPsBN * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kEpiWarps = 8;
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
+  static constexpr int kEpiWarpBytes = 1280;
+  static constexpr int kMaxTokens = 832;                  // 4 column tiles
+  static constexpr int kAccStride = 256;                  // TMEM columns between the two accumulators
+  static constexpr int kGroupCols = 112;                  // columns of epilogue group 0 (group 1: the other 96)
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiWarpBytes + kMaxTokens * 4 + 256 + 1024;
+};
+
+__device__ __forceinline__ void reduce_splits_dyn(const float* pp, size_t stride, int splits, float (&acc)[16]) {
+  switch (splits) {
+    case 2: reduce_splits16<2>(pp, stride, acc); break;
+    case 3: reduce_splits16<3>(pp, stride, acc); break;
+    case 4: reduce_splits16<4>(pp, stride, acc); break;
+    case 5: reduce_splits16<5>(pp, stride, acc); break;
+    case 6: reduce_splits16<6>(pp, stride, acc); break;
+    default:
+#pragma unroll 1
+      for (int sp = 0; sp < splits; sp += 4) {     // four splits in flight at a time
+        if (sp + 4 <= splits) reduce_splits16<4>(pp + (size_t)sp * stride, stride, acc);
+        else for (int q = sp; q < splits; ++q) reduce_splits16<1>(pp + (size_t)q * stride, stride, acc);
+      }
+  }
+}
+
+template <int kAct>
+__global__ void __launch_bounds__(PSCfg::kThreads, 1)
+gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                            const GemmParams p, const int tiles_a, const int tiles_b) {
+  using C = PSCfg;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ float sq_red[2][4][16];
+  __shared__ int last_flag[2];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + C::kStages * C::kABytes;
+  uint8_t* smem_epi = smem + C::kStages * C::kStageBytes;
+  float* rstd_all = reinterpret_cast<float*>(smem_epi + C::kEpiWarps * C::kEpiWarpBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(rstd_all + C::kMaxTokens);
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tmem_full = empty_bar + C::kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;             // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  const int n_items = tiles_a * tiles_b * p.splits;
+  // item -> (feature tile, split, token tile); token tile fastest: the readers of one weight tile are neighbours
+  auto decode = [&](int it, int& a0, int& b0, int& kb0, int& kb1, int& tile_lin, int& split) {
+    const int tb = it % tiles_b, r = it / tiles_b;
+    split = r % p.splits;
+    const int f = r / p.splits;
+    a0 = f * kBlockM; b0 = tb * kPsBN;
+    kb0 = split * p.kb_per_split; kb1 = min(kb_total, kb0 + p.kb_per_split);
+    tile_lin = f * tiles_b + tb;
+  };
+  const uint64_t pol_a = l2_policy_evict_first(), pol_b = l2_policy_evict_last();
+  int pre = 0;
+  if ((int)blockIdx.x < n_items) {
+    int a0, b0, kb0, kb1, tl_, sp_;
+    decode(blockIdx.x, a0, b0, kb0, kb1, tl_, sp_);
+    pre = min(C::kStages, kb1 - kb0);
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], C::kEpiWarps); }
+    fence_barrier_init();
+    // the weight tiles of the first ring do not depend on any earlier kernel: requested before griddepcontrol.wait (PDL)
+    if (pre > 0) {
+      int a0, b0, kb0, kb1, tl_, sp_;
+      decode(blockIdx.x, a0, b0, kb0, kb1, tl_, sp_);
+      for (int kb = 0; kb < pre; ++kb) {
+        mbar_arrive_expect_tx(&full_bar[kb], C::kStageBytes);
+        tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], (kb0 + kb) * kBlockK, a0, pol_a);
+      }
+    }
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ===== TMA producer: one continuous stream of k-blocks over all items of this CTA =====
+    if (lane == 0) {
+      pdl_wait();
+      uint32_t cnt = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        int a0, b0, kb0, kb1, tl_, sp_;
+        decode(it, a0, b0, kb0, kb1, tl_, sp_);
+        for (int kb = kb0; kb < kb1; ++kb, ++cnt) {
+          const int s = cnt % C::kStages;
+          if (cnt < (uint32_t)pre) {           // first ring: the weight tile is already on its way
+            tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, b0, pol_b);
+          } else {
+            mbar_wait(&empty_bar[s], ((cnt / C::kStages) & 1) ^ 1);
+            mbar_arrive_expect_tx(&full_bar[s], C::kStageBytes);
+            tma_load_2d_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kb * kBlockK, a0, pol_a);
+            tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, b0, pol_b);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, kPsBN);
+      uint32_t cnt = 0, tl = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++tl) {
+        int a0, b0, kb0, kb1, tl_, sp_;
+        decode(it, a0, b0, kb0, kb1, tl_, sp_);
+        const uint32_t buf = tl & 1;
+        mbar_wait(&tmem_empty[buf], ((tl >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * C::kAccStride;
+        for (int kb = kb0; kb < kb1; ++kb, ++cnt) {
+          const int s = cnt % C::kStages;
+          mbar_wait(&full_bar[s], (cnt / C::kStages) & 1);
+          tc_fence_after();
+          const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + s * C::kABytes));
+          const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + s * C::kBBytes));
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma_f16_ss(tacc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+          umma_commit(&empty_bar[s]);
+        }
+        umma_commit(&tmem_full[buf]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3).., group (w - 4) / 4 owns columns [0,112) or [112,208) =====
+    const int ew = warp & 3, grp = (warp - 4) >> 2;
+    const int i = ew * 32 + lane;
+    const int col_begin = grp ? C::kGroupCols : 0, col_end = grp ? kPsBN : C::kGroupCols;
+    const int bar_id = 1 + grp;
+    uint8_t* stage_warp = smem_epi + (warp - 4) * C::kEpiWarpBytes;
+    pdl_wait();   // residuals, norm partials and the output buffer belong to earlier kernels until here
+    if (p.rs_partials) {
+      for (int t = threadIdx.x - 128; t < C::kMaxTokens; t += 32 * C::kEpiWarps) {
+        float sum = 0.f;
+        if (t < p.Nb)
+          for (int r = 0; r < p.rs_n; ++r) sum += __ldcg(p.rs_partials + (size_t)r * p.rs_ld + t);
+        rstd_all[t] = (t < p.Nb) ? rsqrtf(sum * p.rs_inv_cols + p.rs_eps) : 0.f;
+      }
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+    }
+    uint32_t tl = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++tl) {
+      int a0, b0, kb0, kb1, tile_lin, split;
+      decode(it, a0, b0, kb0, kb1, tile_lin, split);
+      const uint32_t buf = tl & 1;
+      mbar_wait(&tmem_full[buf], (tl >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * C::kAccStride + ((uint32_t)(ew * 32) << 16);
+      const int feat = a0 + i;
+      const bool fvalid = feat < p.Ma;
+      const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
+      const bool staged = swap_staged_ok(p, a0) && !p.sumsq_out;
+      const int ncols = min(kPsBN, p.Nb - b0);
+      const int my_end = min(col_end, ncols);
+      if (p.splits == 1) {
+#pragma unroll 1
+        for (int jc = col_begin; jc < my_end; jc += 16) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(taddr + jc, r);
+          tmem_ld_wait();
+          float acc[16];
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
+          if (p.rs_partials) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
+          }
+          if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
+          else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+          if (p.sumsq_out) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+      } else {
+        constexpr size_t kSplitStride = (size_t)kPsBN * kBlockM;
+        float* part = p.ws_partial + ((size_t)tile_lin * p.splits + split) * kSplitStride + i;
+#pragma unroll 1
+        for (int jc = col_begin; jc < my_end; jc += 16) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(taddr + jc, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int t = 0; t < 16; ++t) __stcg(part + (jc + t) * kBlockM, __uint_as_float(r[t]));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[buf]);     // the accumulator is free: the rest works on the parked copy
+        __threadfence();
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        if (ew == 0 && lane == 0) {
+          int* cnt = p.ws_pcounters + tile_lin * 2 + grp;
+          const int old = atomicAdd(cnt, 1);
+          const int last = (old == p.splits - 1) ? 1 : 0;
+          if (last) *cnt = 0;                              // self-resetting: nobody else touches it in this launch
+          last_flag[grp] = last;
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        if (last_flag[grp]) {
+          __threadfence();
+          const float* base = p.ws_partial + (size_t)tile_lin * p.splits * kSplitStride + i;
+#pragma unroll 1
+          for (int jc = col_begin; jc < my_end; jc += 16) {
+            float acc[16];
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+            reduce_splits_dyn(base + jc * kBlockM, kSplitStride, p.splits, acc);
+            if (p.rs_partials) {
+#pragma unroll
+              for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
+            }
+            if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
+            else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+            if (p.sumsq_out) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // =====================================================================================
@@ -986,11 +1243,13 @@ namespace {
 template <int BN, bool kSwap, int kAct, bool kDeep>
 int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t stream) {
   using C = Cfg<BN, kDeep>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[16] = {false};     // function attributes are per device
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 16 && !attr_done[dev]) {
     AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct, kDeep>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     AHA_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kAct, kDeep>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    attr_done = true;
+    attr_done[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
@@ -1051,13 +1310,15 @@ template <int BN, int kAct>
 int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_m, int tiles_n, int sm_count,
                       cudaStream_t stream) {
   using C = PCfg<BN>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[16] = {false};     // function attributes are per device
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 16 && !attr_done[dev]) {
     AHA_CUDA(cudaFuncSetAttribute(gemm_tall_persistent_kernel<BN, kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     // same (maximal) shared-memory carve-out as every other kernel of the library: CTAs of two kernels only share an SM
     // when their carve-outs agree
     AHA_CUDA(cudaFuncSetAttribute(gemm_tall_persistent_kernel<BN, kAct>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    attr_done = true;
+    attr_done[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(std::min(tiles_m * tiles_n, sm_count)); cfg.blockDim = dim3(C::kThreads);
@@ -1080,6 +1341,33 @@ int dispatch_persistent(int act, const CUtensorMap& ta, const CUtensorMap& tb, c
     case GEMM_ACT_SILU_MUL: return launch_persistent<BN, GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
     default: return launch_persistent<BN, GEMM_ACT_NONE>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
   }
+}
+}  // namespace
+
+namespace {
+template <int kAct>
+int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_a, int tiles_b,
+                           int sm_count, cudaStream_t stream) {
+  using C = PSCfg;
+  static bool attr_done[16] = {false};
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 16 && !attr_done[dev]) {
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_done[dev] = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(std::min(tiles_a * tiles_b * p.splits, sm_count)); cfg.blockDim = dim3(C::kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_swap_persistent_kernel<kAct>, ta, tb, p, tiles_a, tiles_b));
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
 }
 }  // namespace
 
@@ -1134,17 +1422,21 @@ void gemm_workspace_destroy(GemmWorkspace* w) {
   w->scratch.clear();
 }
 
-static int split_scratch(GemmWorkspace* w, cudaStream_t st, GemmSplitScratch* out) {
+// advance = false: a launch that uses only the partial workspace and the self-resetting counters (no bank switch)
+static int split_scratch(GemmWorkspace* w, cudaStream_t st, GemmSplitScratch* out, bool advance = true) {
   std::lock_guard<std::mutex> lk(w->mu);
   auto it = w->scratch.find(st);
   if (it == w->scratch.end()) {
     GemmSplitScratch s;
     AHA_CUDA(cudaMalloc(&s.partial, GemmWorkspace::kPartialBytes));
-    AHA_CUDA(cudaMalloc(&s.counters, 4 * GemmWorkspace::kCounters * sizeof(int)));
-    AHA_CUDA(cudaMemsetAsync(s.counters, 0, 4 * GemmWorkspace::kCounters * sizeof(int), st));
+    const size_t n_cnt = 4 * GemmWorkspace::kCounters + GemmWorkspace::kPCounters;
+    AHA_CUDA(cudaMalloc(&s.counters, n_cnt * sizeof(int)));
+    AHA_CUDA(cudaMemsetAsync(s.counters, 0, n_cnt * sizeof(int), st));
+    s.pcounters = s.counters + 4 * GemmWorkspace::kCounters;
     it = w->scratch.emplace(st, s).first;
   }
   GemmSplitScratch& s = it->second;
+  if (!advance) { *out = s; return AHA_OK; }
   const int bank = (int)(s.seq++ & 1);
   *out = s;
   out->bank = s.counters + bank * 2 * GemmWorkspace::kCounters;
@@ -1154,13 +1446,14 @@ static int split_scratch(GemmWorkspace* w, cudaStream_t st, GemmSplitScratch* ou
 }
 
 GemmWorkspace* aha_default_workspace(int* rc_out);
-int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out) {
+int aha_split_scratch(cudaStream_t st, GemmSplitScratch* out, bool advance) {
   int rc;
   GemmWorkspace* w = aha_default_workspace(&rc);
   if (!w) return rc;
-  rc = split_scratch(w, st, out);
+  rc = split_scratch(w, st, out, advance);
   if (rc) return rc;
-  out->bank += GemmWorkspace::kCounters;
+  if (advance) out->bank += GemmWorkspace::kCounters;
+  else out->pcounters += GemmWorkspace::kPCounters / 2;     // the attention half of the self-resetting counters
   return AHA_OK;
 }
 
@@ -1170,8 +1463,14 @@ bool aha_sm_shared() { return g_sm_shared != 0; }
 
 int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   AHA_REQUIRE(c.tokens > 0 && c.features > 0 && c.K > 0, "GEMM with an empty dimension");
-  int swap = c.force_swap >= 0 ? c.force_swap : (c.tokens <= 256 ? 1 : 0);
+  // skinny orientation (weights = MMA A operand): up to 256 tokens in the one-shot kernel, up to kGemmSkinnyMaxTokens in
+  // the persistent one (bf16 outputs only)
+  int swap = c.force_swap >= 0 ? c.force_swap : ((c.tokens <= 256 || (c.tokens <= kGemmSkinnyMaxTokens && !c.out_f32)) ? 1 : 0);
   if (c.act == GEMM_ACT_GELU_TANH || c.act == GEMM_ACT_GELU_ERF) swap = 0;   // GELU epilogues exist in the tall orientation only
+  if (swap && c.tokens > 256 && (c.out_f32 || c.tokens > kGemmSkinnyMaxTokens)) {
+    AHA_REQUIRE(c.force_swap < 0, "skinny orientation above 256 tokens: bf16 output and at most 832 tokens");
+    swap = 0;
+  }
   if (c.act == GEMM_ACT_SILU_MUL) {
     AHA_REQUIRE(!c.out_f32 && !c.residual, "SiLU*mul epilogue writes bf16 without residual");
   }
@@ -1180,7 +1479,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   p.out = c.out; p.ldo = c.ldo; p.out_f32 = c.out_f32; p.round_bf16 = c.round_bf16; p.act = c.act;
   p.bias = c.bias; p.residual = c.residual; p.ldr = c.ldr; p.res_mod = c.res_mod;
   if (c.rs_partials || c.sumsq_out) {
-    AHA_REQUIRE(swap && c.act != GEMM_ACT_GELU_TANH && c.act != GEMM_ACT_GELU_ERF, "folded RMSNorm needs the skinny orientation (tokens <= 256)");
+    AHA_REQUIRE(swap && c.act != GEMM_ACT_GELU_TANH && c.act != GEMM_ACT_GELU_ERF, "folded RMSNorm needs the skinny orientation (tokens <= 832, bf16 output, no GELU)");
     AHA_REQUIRE(!c.rs_partials || (c.rs_n > 0 && c.rs_ld >= c.tokens), "folded RMSNorm: bad partial-sum layout");
     AHA_REQUIRE(!c.sumsq_out || (c.sumsq_ld >= c.tokens && !c.out_f32 && c.act == GEMM_ACT_NONE), "folded RMSNorm: bad sum-of-squares output");
     p.rs_partials = c.rs_partials; p.rs_n = c.rs_n; p.rs_ld = c.rs_ld; p.rs_eps = c.rs_eps; p.rs_inv_cols = 1.0f / (float)c.K;
@@ -1191,6 +1490,52 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
   else      { p.Ma = c.tokens; p.Nb = c.features; a = c.x; lda = c.ldx; b = c.w; ldb = c.ldw; }
 
+  // Persistent skinny path: batched decoder steps (256 < tokens <= 832)
+  if (swap && c.tokens > 256) {
+    const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, tiles_b = (p.Nb + kPsBN - 1) / kPsBN;
+    const int tiles = tiles_a * tiles_b;
+    const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+    if (c.sumsq_tiles) *c.sumsq_tiles = tiles_a;
+    int splits = c.force_splits;
+    if (splits <= 0) {
+      // every SM should get the same number of k-blocks; a split item pays for parking / merging its partial tile
+      static const int max_env = getenv("AHA_PS_SPLITS") ? atoi(getenv("AHA_PS_SPLITS")) : 8;
+      long best_cost = -1;
+      for (int s = 1; s <= max_env && s <= kb_total; ++s) {
+        const int kb_per = (kb_total + s - 1) / s;
+        if ((kb_total + kb_per - 1) / kb_per != s || (s > 1 && kb_per < 8)) continue;
+        const long items = (long)tiles * s;
+        const long cost = ((items + w->sm_count - 1) / w->sm_count) * (kb_per + (s > 1 ? 8 : 2));
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
+      }
+    }
+    if (splits > kb_total) splits = kb_total;
+    int kb_per = (kb_total + splits - 1) / splits;
+    splits = (kb_total + kb_per - 1) / kb_per;
+    while (splits > 1 && ((size_t)tiles * splits * kPsBN * kBlockM * sizeof(float) > GemmWorkspace::kPartialBytes || tiles * 2 > 4096)) {
+      --splits;
+      kb_per = (kb_total + splits - 1) / splits;
+      splits = (kb_total + kb_per - 1) / kb_per;
+    }
+    p.splits = splits; p.kb_per_split = kb_per; p.dbg = 0;
+    if (splits > 1) {
+      GemmSplitScratch sc;
+      int src = split_scratch(w, stream, &sc, false); if (src) return src;
+      p.ws_partial = sc.partial; p.ws_pcounters = sc.pcounters;
+    }
+    CUtensorMap ta, tb;
+    int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
+    rc = get_tmap(b, p.Nb, p.K, ldb, kPsBN, &tb); if (rc) return rc;
+    ProfSlot* slot = prof_begin(5, stream);
+    rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_a, tiles_b, w->sm_count, stream)
+                                    : launch_swap_persistent<GEMM_ACT_NONE>(ta, tb, p, tiles_a, tiles_b, w->sm_count, stream);
+    if (slot) {
+      const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * 2;
+      prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,
+               2.0 * c.tokens * (double)c.features * c.K);
+    }
+    return rc;
+  }
   // Persistent tall path: bf16 output, enough 128 x BN tiles to give every SM several of them
   {
     static int persist = -1;

@@ -5,7 +5,9 @@
 #include "kvcache.h"
 #include "gemm.h"
 #include "ptx_sm100.cuh"
+#include <cuda.h>
 #include <algorithm>
+#include <vector>
 #include <cstdlib>
 
 namespace {
@@ -128,6 +130,57 @@ __global__ void __launch_bounds__(256, 3) rerotate_kernel(RerotLayers ls, const 
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       if (u < kHeadsPerThread && h0 + u < kvh) {
+        const uint32_t l[4] = {lo[u].x, lo[u].y, lo[u].z, lo[u].w}, hh[4] = {hi[u].x, hi[u].y, hi[u].z, hi[u].w};
+        uint32_t ol[4], oh[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) rerot_pair(l[e], hh[e], cl[e], ch[e], sl[e], sh[e], ol[e], oh[e]);
+        bf16* row = K + ((size_t)(h0 + u) * cap + slot) * d + c * 8;
+        st_v4(row, make_uint4(ol[0], ol[1], ol[2], ol[3]));
+        st_v4(row + half, make_uint4(oh[0], oh[1], oh[2], oh[3]));
+      }
+    }
+  }
+}
+
+// The same re-rotation for every stream of a batched prefill call in ONE launch: blockIdx.y = stream * n_layers + layer,
+// slab pointers come from each cache's device-resident layer table.
+struct RerotStream { bf16* const* layer_k; const bf16* rerot; int base, keep, S, R, cap; };
+struct RerotBatch { RerotStream s[kMaxStreams]; };
+
+__global__ void __launch_bounds__(256, 3) rerotate_batched_kernel(RerotBatch b, int n_layers, int kvh, int d) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const RerotStream& st = b.s[blockIdx.y / n_layers];
+  const int keep = st.keep;
+  const int tpk = d >> 4;  // threads per key
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= keep * tpk) return;
+  bf16* K = st.layer_k[blockIdx.y % n_layers];
+  const int half = d >> 1, cap = st.cap;
+  const int c = idx % tpk, r = idx / tpk;
+  int slot = st.base + r;
+  if (slot >= st.R) slot -= st.R;
+  slot += st.S;
+  const bf16* rc = st.rerot + (size_t)r * d + c * 8;
+  const bf16* rs = rc + (size_t)keep * d;
+  const uint4 clo = *reinterpret_cast<const uint4*>(rc), chi = *reinterpret_cast<const uint4*>(rc + half);
+  const uint4 slo = *reinterpret_cast<const uint4*>(rs), shi = *reinterpret_cast<const uint4*>(rs + half);
+  const uint32_t cl[4] = {clo.x, clo.y, clo.z, clo.w}, ch[4] = {chi.x, chi.y, chi.z, chi.w};
+  const uint32_t sl[4] = {slo.x, slo.y, slo.z, slo.w}, sh[4] = {shi.x, shi.y, shi.z, shi.w};
+#pragma unroll 1
+  for (int h0 = blockIdx.z * 4; h0 < min(kvh, (int)(blockIdx.z + 1) * 4); h0 += 4) {
+    uint4 lo[4], hi[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (h0 + u < kvh) {
+        const bf16* row = K + ((size_t)(h0 + u) * cap + slot) * d + c * 8;
+        lo[u] = *reinterpret_cast<const uint4*>(row);
+        hi[u] = *reinterpret_cast<const uint4*>(row + half);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (h0 + u < kvh) {
         const uint32_t l[4] = {lo[u].x, lo[u].y, lo[u].z, lo[u].w}, hh[4] = {hi[u].x, hi[u].y, hi[u].z, hi[u].w};
         uint32_t ol[4], oh[4];
 #pragma unroll
@@ -409,6 +462,11 @@ int cache_ensure_layer(aha_cache_s* c, int layer) {
     const size_t bytes = (size_t)c->kvh * c->cap * c->d * sizeof(bf16);
     AHA_CUDA(cudaMalloc(&ly.k, bytes));
     AHA_CUDA(cudaMalloc(&ly.v, bytes));
+    // attention loads whole 128-row tiles by TMA and masks only the scores: rows past the valid length meet P = 0 in the
+    // P.V product, so they must hold finite values (recycled device memory may hold NaN / Inf bit patterns)
+    AHA_CUDA(cudaMemset(ly.k, 0, bytes));
+    AHA_CUDA(cudaMemset(ly.v, 0, bytes));
+    c->dev_views_layers = 0;      // the device-resident views are rebuilt on the next batched call
   }
   if (layer + 1 > c->n_layers) c->n_layers = layer + 1;
   return AHA_OK;
@@ -421,7 +479,20 @@ int cache_layer0_bookkeeping(aha_cache_s* c, const UpdatePlan& p, const bf16* co
     c->have_rope = (cos != nullptr && sin != nullptr);
     if (c->have_rope) {
       if (c->cos_rows == 0 || c->cos_rows < c->W) {               // sink_cache.py:116-121
-        AHA_REQUIRE(c->cos_rows + q <= c->W + c->max_chunk, "cos/sin table overflow (chunk larger than max_chunk)");
+        if (c->cos_rows + q > c->cos_cap_rows) {
+          // a later chunk may be longer than the first one (the reference accepts any q): grow the tables, stream-ordered
+          const int rows = std::max(c->cos_rows + q, 2 * c->cos_cap_rows);
+          bf16 *nc = nullptr, *ns = nullptr;
+          AHA_CUDA(cudaMallocAsync(&nc, (size_t)rows * c->d * sizeof(bf16), st));
+          AHA_CUDA(cudaMallocAsync(&ns, (size_t)rows * c->d * sizeof(bf16), st));
+          if (c->cos_rows > 0) {
+            AHA_CUDA(cudaMemcpyAsync(nc, c->cos_table, (size_t)c->cos_rows * c->d * sizeof(bf16), cudaMemcpyDeviceToDevice, st));
+            AHA_CUDA(cudaMemcpyAsync(ns, c->sin_table, (size_t)c->cos_rows * c->d * sizeof(bf16), cudaMemcpyDeviceToDevice, st));
+          }
+          AHA_CUDA(cudaFreeAsync(c->cos_table, st));
+          AHA_CUDA(cudaFreeAsync(c->sin_table, st));
+          c->cos_table = nc; c->sin_table = ns; c->cos_cap_rows = rows;
+        }
         const size_t bytes = (size_t)q * c->d * sizeof(bf16);
         AHA_CUDA(cudaMemcpyAsync(c->cos_table + (size_t)c->cos_rows * c->d, cos, bytes, cudaMemcpyDeviceToDevice, st));
         AHA_CUDA(cudaMemcpyAsync(c->sin_table + (size_t)c->cos_rows * c->d, sin, bytes, cudaMemcpyDeviceToDevice, st));
@@ -515,6 +586,56 @@ int cache_rerotate(aha_cache_s* c, int layer0, int n, const UpdatePlan& p, cudaS
   return AHA_OK;
 }
 
+int cache_ensure_device_views(aha_cache_s* c, int n_layers) {
+  if (c->dev_views_layers >= n_layers && c->tmaps_dev) return AHA_OK;
+  AHA_REQUIRE((int)c->layers.size() >= n_layers, "device views requested for layers that are not allocated");
+  std::vector<CUtensorMap> maps(2 * (size_t)n_layers);
+  std::vector<bf16*> ks(n_layers);
+  for (int l = 0; l < n_layers; ++l) {
+    const CacheLayer& ly = c->layers[l];
+    AHA_REQUIRE(ly.k && ly.v, "device views: layer slab missing");
+    int rc = get_tmap(ly.k, c->kvh * c->cap, c->d, c->d, 128, &maps[2 * l]); if (rc) return rc;
+    rc = get_tmap(ly.v, c->kvh * c->cap, c->d, c->d, 128, &maps[2 * l + 1]); if (rc) return rc;
+    ks[l] = ly.k;
+  }
+  // (rare: once per cache) old tables may still be referenced by kernels in flight: free them only after a device sync
+  if (c->tmaps_dev || c->layer_k_dev) { AHA_CUDA(cudaDeviceSynchronize()); cudaFree(c->tmaps_dev); cudaFree(c->layer_k_dev); c->tmaps_dev = nullptr; c->layer_k_dev = nullptr; }
+  AHA_CUDA(cudaMalloc(&c->tmaps_dev, maps.size() * sizeof(CUtensorMap)));
+  AHA_CUDA(cudaMalloc(&c->layer_k_dev, ks.size() * sizeof(bf16*)));
+  AHA_CUDA(cudaMemcpy(c->tmaps_dev, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+  AHA_CUDA(cudaMemcpy(c->layer_k_dev, ks.data(), ks.size() * sizeof(bf16*), cudaMemcpyHostToDevice));
+  c->dev_views_layers = n_layers;
+  return AHA_OK;
+}
+
+int cache_rerotate_batched(aha_cache_s* const* caches, const UpdatePlan* plans, int n_streams, int n_layers, cudaStream_t st) {
+  RerotBatch b{};
+  int n = 0, max_keep = 0, kvh = 0, d = 0;
+  double bytes = 0;
+  for (int s = 0; s < n_streams; ++s) {
+    aha_cache_s* c = caches[s];
+    const UpdatePlan& p = plans[s];
+    if (p.keep <= 0 || !c->have_rope) continue;
+    auto it = c->rerot.find(p.q);
+    AHA_REQUIRE(it != c->rerot.end(), "re-rotation table missing for this chunk length (layer 0 must be updated first)");
+    AHA_REQUIRE(n == 0 || (c->kvh == kvh && c->d == d), "batched re-rotation: cache geometries differ");
+    int rc = cache_ensure_device_views(c, n_layers); if (rc) return rc;
+    kvh = c->kvh; d = c->d;
+    b.s[n++] = RerotStream{c->layer_k_dev, it->second, p.new_base, p.keep, c->S, c->R, c->cap};
+    max_keep = std::max(max_keep, p.keep);
+    bytes += 2.0 * n_layers * (double)p.keep * c->kvh * c->d * sizeof(bf16);
+  }
+  if (n == 0) return AHA_OK;
+  const long long items = (long long)max_keep * (d / 16);
+  dim3 grid((unsigned)((items + 255) / 256), n * n_layers, (kvh + 3) / 4);
+  ProfSlot* slot = prof_begin(2, st);
+  int rc = launch_pdl(rerotate_batched_kernel, grid, dim3(256), 0, st, b, n_layers, kvh, d);
+  if (slot) prof_end(slot, st, bytes, 0.0);
+  if (rc) return rc;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+
 int cache_store(aha_cache_s* c, int layer, const UpdatePlan& p, const bf16* k, const bf16* v, long long k_hs,
                 long long k_ts, long long v_hs, long long v_ts, cudaStream_t st) {
   const int n = p.store_end - p.store_begin;
@@ -541,7 +662,7 @@ void cache_commit(aha_cache_s* c, int layer, const UpdatePlan& p) {
 
 int op_rope_append(const bf16* qkv, const bf16* cos, const bf16* sin, bf16* qbuf, const RopeAppendArgs& a, int n_streams,
                    int q, int heads, int kvh, int d, int cap, cudaStream_t st) {
-  AHA_REQUIRE(n_streams > 0 && n_streams <= 16 && d % 16 == 0 && heads % kvh == 0, "rope_append: bad shape");
+  AHA_REQUIRE(n_streams > 0 && n_streams <= kMaxStreams && d % 16 == 0 && heads % kvh == 0, "rope_append: bad shape");
   const long long items = (long long)q * (heads + 2 * kvh) * (d / 16);
   dim3 grid(grid_for(items, 256), n_streams);
   return launch_pdl(rope_append_kernel, grid, dim3(256), 0, st, qkv, cos, sin, qbuf, a, q, heads, kvh, d, cap);
@@ -572,6 +693,7 @@ int aha_cache_create(int n_layers, int kv_heads, int head_dim, int policy, int w
     const size_t rows = (size_t)window + c->max_chunk;
     e = cudaMalloc(&c->cos_table, rows * head_dim * sizeof(bf16));
     if (e == cudaSuccess) e = cudaMalloc(&c->sin_table, rows * head_dim * sizeof(bf16));
+    c->cos_cap_rows = (int)rows;
   }
   if (e != cudaSuccess) { aha_cache_destroy(c); return aha_cuda_fail(e, "cudaMalloc(cache)", __FILE__, __LINE__); }
   for (int l = 0; l < n_layers; ++l) {
@@ -596,6 +718,7 @@ int aha_cache_destroy(aha_cache_t c) {
   for (auto& ly : c->layers) { cudaFree(ly.k); cudaFree(ly.v); }
   for (auto& kv : c->rerot) cudaFree(kv.second);
   cudaFree(c->ids); cudaFree(c->cos_table); cudaFree(c->sin_table); cudaFree(c->scratch);
+  cudaFree(c->tmaps_dev); cudaFree(c->layer_k_dev);
   delete c;
   return AHA_OK;
 }

@@ -57,6 +57,13 @@ struct aha_cache_s {
   // SinkCache.cos_sin_rerotation_cache (sink_cache.py:35-55): q -> [2][W-S-q][d] bf16
   std::map<int, bf16*> rerot;
   bf16* scratch = nullptr;        // compaction scratch [kv_heads][W][d] x 2, allocated on demand
+  // device-resident views of the layer slabs for launches that cover several streams at once (aha_prefill_chunk with
+  // n_streams > 1): tmaps_dev[2 * layer + {0: K, 1: V}] are the TMA descriptors the attention kernel picks per segment,
+  // layer_k_dev[layer] the K slab pointers the batched re-rotation walks.  Built by cache_ensure_device_views().
+  void* tmaps_dev = nullptr;      // CUtensorMap [2 * dev_views_layers]
+  bf16** layer_k_dev = nullptr;
+  int dev_views_layers = 0;
+  int cos_cap_rows = 0;           // rows allocated in cos_table / sin_table
 };
 
 // Integer semantics of one update (shared by the HF-compatible aha_cache_update and by aha_prefill_chunk).
@@ -67,6 +74,9 @@ int cache_ensure_layer(aha_cache_s* c, int layer);
 int cache_layer0_bookkeeping(aha_cache_s* c, const UpdatePlan& p, const bf16* cos, const bf16* sin, cudaStream_t st);
 // moves the kept tokens of an oversize linear layout into the ring (rare path)
 int cache_compact(aha_cache_s* c, int layer, const UpdatePlan& p, cudaStream_t st);
+int cache_ensure_device_views(aha_cache_s* c, int n_layers);
+// re-rotates the kept keys of all `n_layers` layers of every stream in one launch (streams whose plan keeps nothing are skipped)
+int cache_rerotate_batched(aha_cache_s* const* caches, const UpdatePlan* plans, int n_streams, int n_layers, cudaStream_t st);
 // re-rotates the kept keys of layers [layer0, layer0+n) in one launch (plan.keep > 0)
 int cache_rerotate(aha_cache_s* c, int layer0, int n, const UpdatePlan& p, cudaStream_t st);
 // stores already-rotated k / v of the chunk (strided source) into the planned slots
@@ -74,13 +84,14 @@ int cache_store(aha_cache_s* c, int layer, const UpdatePlan& p, const bf16* k, c
                 long long k_ts, long long v_hs, long long v_ts, cudaStream_t st);
 void cache_commit(aha_cache_s* c, int layer, const UpdatePlan& p);
 
-// Fused RoPE + append used by aha_prefill_chunk (kvcache.cu): for up to 16 streams, reads the packed projection output
+// Fused RoPE + append used by aha_prefill_chunk (kvcache.cu): for up to kMaxStreams streams, reads the packed projection output
 // qkv [n_streams*q, (heads + 2*kv_heads)*d], rotates q and k at the chunk positions (cos/sin [n_streams][q][d]),
 // writes q to qbuf [n_streams][kv_heads][q*group][d] and k / v into every stream's cache slots.
 struct RopeAppendStream {
   bf16* k; bf16* v;                // this layer's slabs
   int store_begin, store_end, store_phys0, wrap_end, R;
 };
-struct RopeAppendArgs { RopeAppendStream s[16]; };
+constexpr int kMaxStreams = 32;   // streams per aha_prefill_chunk call (AttnProblem::segs, kernel parameter blocks)
+struct RopeAppendArgs { RopeAppendStream s[kMaxStreams]; };
 int op_rope_append(const bf16* qkv, const bf16* cos, const bf16* sin, bf16* qbuf, const RopeAppendArgs& a, int n_streams,
                    int q, int heads, int kvh, int d, int cap, cudaStream_t st);

@@ -348,34 +348,41 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
   const aha_model_desc& d = m->d;
   const int H = d.hidden, nh = d.heads, kvh = d.kv_heads, hd = d.head_dim, G = nh / kvh;
   const int M = ns * q, qd = nh * hd;
-  AHA_REQUIRE(ns > 0 && ns <= 16, "prefill: between 1 and 16 streams per call");
+  AHA_REQUIRE(ns > 0 && ns <= kMaxStreams, "prefill: between 1 and 32 streams per call");
   AHA_REQUIRE(q > 0 && M <= d.max_tokens, "prefill: streams * q exceeds max_tokens of the model handle");
   AHA_REQUIRE(mask_mode == AHA_MASK_SDPA || mask_mode == AHA_MASK_FA2, "prefill: unknown mask mode");
   std::vector<UpdatePlan> plans(ns);
   RopeTableArgs ra{};
+  // every check comes before the first cache mutation: a rejected call leaves all caches as they were
   for (int s = 0; s < ns; ++s) {
     aha_cache_s* c = caches[s];
     AHA_REQUIRE(c != nullptr, "prefill: NULL cache");
     AHA_REQUIRE(c->kvh == kvh && c->d == hd, "prefill: cache geometry does not match the model");
     AHA_REQUIRE(q <= c->max_chunk, "prefill: chunk longer than the cache's max_chunk");
+    AHA_REQUIRE(c->cap == caches[0]->cap, "prefill: all caches of one call must share window / max_chunk");
     for (int t = 0; t < s; ++t) AHA_REQUIRE(caches[t] != c, "prefill: the same cache given for two streams");
-    for (int l = 0; l < d.layers; ++l) TRY(cache_ensure_layer(c, l));
+  }
+  for (int s = 0; s < ns; ++s) {
+    aha_cache_s* c = caches[s];
+    for (int l = 0; l < d.layers; ++l) TRY(cache_ensure_layer(c, l));      // (allocation only, no state change)
     for (int l = 1; l < d.layers; ++l)
       AHA_REQUIRE(c->layers[l].populated == c->layers[0].populated && c->layers[l].len == c->layers[0].len &&
                       c->layers[l].ring_base == c->layers[0].ring_base,
                   "prefill: cache layers are not in lockstep");
     TRY(cache_plan_update(c, c->layers[0], q, &plans[s]));
     ra.pos0[s] = plans[s].L;   // position_ids = arange(L, L+q), L = get_seq_length()
+    if (ns > 1) TRY(cache_ensure_device_views(c, d.layers));
   }
   TRY(op_rope_table(ra, ns, q, hd, m->inv_freq, m->ws_cos, m->ws_sin, st));
   for (int s = 0; s < ns; ++s) {
     aha_cache_s* c = caches[s];
     TRY(cache_layer0_bookkeeping(c, plans[s], m->ws_cos + (size_t)s * q * hd, m->ws_sin + (size_t)s * q * hd, st));
     for (int l = 0; l < d.layers; ++l) TRY(cache_compact(c, l, plans[s], st));
-    TRY(cache_rerotate(c, 0, d.layers, plans[s], st));   // every layer's kept keys in one launch
+    if (ns == 1) TRY(cache_rerotate(c, 0, d.layers, plans[s], st));   // every layer's kept keys in one launch
   }
-  // RMSNorm folded around the GEMMs when the call runs in the skinny orientation (at most 256 tokens)
-  const bool fold = m->fold_norm && M <= 256;
+  if (ns > 1) TRY(cache_rerotate_batched(caches, plans.data(), ns, d.layers, st));   // ... of every stream
+  // RMSNorm folded around the GEMMs when the call runs in the skinny orientation (at most 832 tokens)
+  const bool fold = m->fold_norm && M <= kGemmSkinnyMaxTokens;
   int ss_na = 1, ss_nb = 1;          // partial rows per token in ws_ss_a / ws_ss_b
   if (fold) TRY(op_copy_sumsq(x_in, m->ws_x, m->ws_ss_a, M, H, st));
   else AHA_CUDA(cudaMemcpyAsync(m->ws_x, x_in, (size_t)M * H * sizeof(bf16), cudaMemcpyDeviceToDevice, st));
@@ -403,21 +410,23 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
     const NormFold nf_down{nullptr, 0, m->ws_ss_a, &ss_na, ss_ld, d.rms_eps};
     if (!(skip & 8)) TRY(linear(fold ? m->ws_x : m->ws_h, M, H, w.qkv_w, m->qkv_cols, H, m->ws_qkv, m->qkv_cols, GEMM_ACT_NONE, w.qkv_b, nullptr, 0, 0, 0, st, &pf, fold ? &nf_qkv : nullptr));
     RopeAppendArgs aa{};
-    int cap = caches[0]->cap;
+    const int cap = caches[0]->cap;
     for (int s = 0; s < ns; ++s) {
       aha_cache_s* c = caches[s];
-      AHA_REQUIRE(c->cap == cap, "prefill: all caches of one call must share window / max_chunk");
       aa.s[s] = RopeAppendStream{c->layers[l].k, c->layers[l].v, plans[s].store_begin, plans[s].store_end,
                                  plans[s].store_phys0, plans[s].wrap_end, plans[s].R};
     }
     if (!(skip & 2)) TRY(op_rope_append(m->ws_qkv, m->ws_cos, m->ws_sin, m->ws_qbuf, aa, ns, q, nh, kvh, hd, cap, st));
+    // ONE attention launch covers all streams of the call: every stream is a segment with its own mask geometry and
+    // (their cache slabs being separate allocations) its own device-resident K / V tensor maps
+    ap.k = caches[0]->layers[l].k; ap.v = caches[0]->layers[l].v;
+    ap.k_rows_total = ap.v_rows_total = (long long)kvh * cap;
+    ap.k_ld = ap.v_ld = hd; ap.k_head_rows = cap;
+    ap.n_segs = ns;
     for (int s = 0; s < ns; ++s) {
       aha_cache_s* c = caches[s];
       const UpdatePlan& p = plans[s];
-      ap.k = c->layers[l].k; ap.v = c->layers[l].v;
-      ap.k_rows_total = ap.v_rows_total = (long long)kvh * c->cap;
-      ap.k_ld = ap.v_ld = hd; ap.k_head_rows = c->cap;
-      AttnSeg& sg = ap.segs[0];
+      AttnSeg& sg = ap.segs[s];
       sg.q_row0 = s * kvh * q * G;
       sg.k_row0 = sg.v_row0 = 0;
       sg.klen = p.klen;
@@ -425,11 +434,16 @@ int prefill(aha_model_s* m, const aha_cache_t* caches, int ns, const bf16* x_in,
       const bool ring = c->policy != AHA_POLICY_STATIC && p.klen <= c->W;
       sg.ring_S = c->S; sg.ring_R = ring ? c->R : 0; sg.ring_base = p.new_base;
       sg.out_row0 = s * q;
-      static const int pf_attn = getenv("AHA_PF_ATTN") ? atoi(getenv("AHA_PF_ATTN")) : 0;
-      ap.pf = pf_attn ? wsm.take(wsm.end_of(4 * l)) : L2Prefetch{};
-      ap.pf_early = pf_attn == 2;
-      if (!(skip & 4)) TRY(op_attention(ap, st));
+      sg.k_tmap = sg.v_tmap = nullptr;
+      if (ns > 1) {
+        sg.k_tmap = (const char*)c->tmaps_dev + (size_t)(2 * l) * 128;       // sizeof(CUtensorMap) == 128
+        sg.v_tmap = (const char*)c->tmaps_dev + (size_t)(2 * l + 1) * 128;
+      }
     }
+    static const int pf_attn = getenv("AHA_PF_ATTN") ? atoi(getenv("AHA_PF_ATTN")) : 0;
+    ap.pf = pf_attn ? wsm.take(wsm.end_of(4 * l)) : L2Prefetch{};
+    ap.pf_early = pf_attn == 2;
+    if (!(skip & 4)) TRY(op_attention(ap, st));
     pf = take_g(4 * l + 1);
     if (!(skip & 16)) TRY(linear(m->ws_attn, M, qd, w.o_w, H, qd, m->ws_x, H, GEMM_ACT_NONE, nullptr, m->ws_x, H, 0, 0, st, &pf, fold ? &nf_o : nullptr));
     if (!fold && !(skip & 1)) TRY(op_rmsnorm(m->ws_x, m->fold_norm ? m->ones : w.post_ln, m->ws_h, M, H, d.rms_eps, st));

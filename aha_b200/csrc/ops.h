@@ -16,7 +16,7 @@ int op_patchify(const uint8_t* frames_u8, const bf16* pixels, bf16* out, int n, 
 int op_pool(const bf16* x, bf16* out, int frames, int side, int channels, int stride, int mode, cudaStream_t st);
 int pool_out_side(int side, int stride, int mode);
 // cos/sin [n_streams][q][d] bf16 at positions pos0[s] + i
-struct RopeTableArgs { int pos0[16]; };
+struct RopeTableArgs { int pos0[32]; };
 int op_rope_table(const RopeTableArgs& a, int n_streams, int q, int d, const float* inv_freq_dev, bf16* cos_out,
                   bf16* sin_out, cudaStream_t st);
 int op_embed_assemble(const bf16* table, const int64_t* ids, int n_ids, const bf16* frame_embeds, int n_frame_tokens,
@@ -38,6 +38,8 @@ struct AttnSeg {           // one (stream or frame) attention problem
   int off;                 // allowed(i, j) <=> logical(j) <= off + i
   int ring_S, ring_R, ring_base;  // physical slot p -> logical j: p < S ? p : S + (p - S - base + R) % R   (R == 0: j = p)
   int out_row0;            // first output token row
+  const void* k_tmap;      // device-resident CUtensorMap of THIS segment's K / V (streams with separate cache slabs in one
+  const void* v_tmap;      // launch); null: the launch-wide maps built from AttnProblem::k / v
 };
 struct AttnProblem {
   const bf16* q; int q_rows_total; int q_ld;   // Q matrix [rows, q_ld]; head h / kv-group columns start at q_col0 + idx * q_col_step
@@ -62,6 +64,9 @@ struct AttnProblem {
   int kv_prefetch;          // key-split launches: request the K / V tiles into L2 before griddepcontrol.wait
   int ws_zero_n;
   int no_split;             // 1: never split the key axis (the kernel's splits wait for each other; see gemm_bf16)
+  int merge_last;           // key-split launches whose CTAs are not all co-resident: nobody waits, the LAST split to arrive
+                            // at the group's (self-resetting) counter merges every chunk (filled in by op_attention)
+  int* ws_pcounters;
   int pf_early;             // 1: request them at kernel entry, 0: after this CTA's own K/V loads are in flight
   int n_segs;
   AttnSeg segs[32];

@@ -158,7 +158,9 @@ class LiveInferForBenchmark:
         self.query_queue.append((video_time, query_ids.reshape(1, -1).to(self.model.device)))
 
     # ---- one chunk (test/inference.py:196-262) ----
-    def _encode_frame(self):
+    def _next_frame_chunk(self):
+        """First half of _encode_frame (test/inference.py:196-214): pops the next frame and assembles its chunk
+        [1, q, H] = cat(embed_tokens(last_ids), frame_embeds).  Returns (video_time, chunk, had_ids)."""
         video_time, frame_embeds = self.frame_embeds_queue.popleft()
         ready = self._ready_events.pop(id(frame_embeds), None)
         if ready is not None:
@@ -170,16 +172,25 @@ class LiveInferForBenchmark:
             self.last_ids = torch.cat([self.last_ids, self._added_stream_prompt_ids], dim=1)     # test/inference.py:205-206
         else:       # last_role is stream, now we just input another frame
             self.last_ids = torch.tensor([[]], device=self.model.device, dtype=torch.long)
-        x = self.model.assemble_chunk(self.last_ids, frame_embeds)
+        if self.last_ids.numel() == 0:
+            return video_time, frame_embeds.view(1, -1, self.hidden_size), False
+        return video_time, self.model.assemble_chunk(self.last_ids, frame_embeds), True
+
+    def _frame_done(self, video_time, past_key_values):
+        """Second half of _encode_frame (test/inference.py:218-229): adopts the cache, records the frame."""
+        self.past_key_values = past_key_values
+        self.last_role = 'stream'
+        self._times.append(video_time)
+        self._n_scored += 1
+
+    def _encode_frame(self):
+        video_time, x, _ = self._next_frame_chunk()
         if self._n_scored >= self._max_frames:
             raise RuntimeError("score buffer full: raise max_frames")
         slot = self._score_buf[self._n_scored:self._n_scored + 1]
         out = self.model(inputs_embeds=x, use_cache=True, past_key_values=self.past_key_values, return_dict=True,
                          scores_out=slot)
-        self.past_key_values = out.past_key_values
-        self.last_role = 'stream'
-        self._times.append(video_time)
-        self._n_scored += 1
+        self._frame_done(video_time, out.past_key_values)
         return out
 
     def _encode_query(self):
@@ -209,30 +220,38 @@ class LiveInferForBenchmark:
         self.last_role = 'assistant'
         return output_ids[0].tolist()
 
+    def _after_frame_scores(self, inf: float, rel: float):
+        """Response trigger of the loop (test/inference.py:306-319) for one scored frame."""
+        scores = dict(informative_score=inf, relevance_score=rel)
+        stream_end_score = sum(v for k, v in scores.items() if k in self.score_heads)
+        self.stream_end_prob_list.append(stream_end_score)
+        self.stream_end_score_sum += stream_end_score
+        if isinstance(self.running_list_length, int) and self.running_list_length > 0:
+            self.stream_end_prob_list = self.stream_end_prob_list[-self.running_list_length:]
+        need = False
+        if self.stream_end_score_sum_threshold is not None and self.stream_end_score_sum > self.stream_end_score_sum_threshold:
+            need = True
+            self.stream_end_score_sum = 0
+        if self.stream_end_prob_threshold is not None and stream_end_score > self.stream_end_prob_threshold:
+            need = True
+        if need:
+            self.response_needed.append(self.video_time)
+            if self._added_stream_generation_ids is not None:
+                response = self._generate_response()
+                self.model_response_list.append({'time': self.video_time, 'content': response, 'role': 'assistant'})
+
+    @property
+    def _wants_decisions(self) -> bool:
+        return self.stream_end_prob_threshold is not None or self.stream_end_score_sum_threshold is not None
+
     def input_one_frame(self):
         """One iteration of the loop (test/live_infer_for_video.py:135-176)."""
         if self.query_queue and self.video_time >= self.query_queue[0][0]:
             self._encode_query()
         self._encode_frame()
-        if self.stream_end_prob_threshold is not None or self.stream_end_score_sum_threshold is not None:
+        if self._wants_decisions:
             inf, rel, unc = self._score_buf[self._n_scored - 1].tolist()       # one sync, only when a decision is due
-            scores = dict(informative_score=inf, relevance_score=rel)
-            stream_end_score = sum(v for k, v in scores.items() if k in self.score_heads)
-            self.stream_end_prob_list.append(stream_end_score)
-            self.stream_end_score_sum += stream_end_score
-            if isinstance(self.running_list_length, int) and self.running_list_length > 0:
-                self.stream_end_prob_list = self.stream_end_prob_list[-self.running_list_length:]
-            need = False
-            if self.stream_end_score_sum_threshold is not None and self.stream_end_score_sum > self.stream_end_score_sum_threshold:
-                need = True
-                self.stream_end_score_sum = 0
-            if self.stream_end_prob_threshold is not None and stream_end_score > self.stream_end_prob_threshold:
-                need = True
-            if need:
-                self.response_needed.append(self.video_time)
-                if self._added_stream_generation_ids is not None:
-                    response = self._generate_response()
-                    self.model_response_list.append({'time': self.video_time, 'content': response, 'role': 'assistant'})
+            self._after_frame_scores(inf, rel)
         self.video_time += 1 / self.frame_fps
 
     def inference(self):

@@ -169,6 +169,8 @@ class VideoHeadLiveLlavaQwenForCausalLM:
         n_f = 0 if frame_embeds is None else int(frame_embeds.shape[-2])
         out = torch.empty(1, n_ids + n_f, self.config.hidden_size, dtype=torch.bfloat16, device=self.device)
         idt = None if n_ids == 0 else ids.reshape(-1).to(device=self.device, dtype=torch.int64).contiguous()
+        if n_ids and (int(idt.min()) < 0 or int(idt.max()) >= self.config.vocab_size):
+            raise IndexError("index out of range in self")      # what torch's embedding raises (the kernel does not check)
         fe = None if n_f == 0 else frame_embeds.to(self.device).contiguous()
         with torch.cuda.device(self.device):
             _lib.check(_lib.load().aha_assemble_chunk(self._h, _lib.ptr(idt), n_ids, _lib.ptr(fe), n_f, _lib.ptr(out),

@@ -208,7 +208,7 @@ def preprocess_lut() -> np.ndarray:
 
 def preprocess(frames_u8: torch.Tensor) -> torch.Tensor:
     """uint8 [T,3,S,S] -> float32 [T,3,S,S] in [-1, 1]."""
-    lut = torch.from_numpy(preprocess_lut())
+    lut = torch.from_numpy(preprocess_lut()).to(frames_u8.device)
     return lut[frames_u8.long()]
 
 
@@ -390,6 +390,7 @@ class OracleKVCache:
 # ----------------------------------------------------------------------------------------------
 def rope_cos_sin(positions: torch.Tensor, head_dim: int, theta: float, dtype) -> Tuple[torch.Tensor, torch.Tensor]:
     inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).float() / head_dim))
+    inv_freq = inv_freq.to(positions.device)         # (computed on the host either way: same fp32 bits on any device)
     freqs = positions.float()[:, None] * inv_freq[None, :]
     emb = torch.cat((freqs, freqs), dim=-1)
     return emb.cos().to(dtype)[None], emb.sin().to(dtype)[None]      # [1, q, d]
@@ -421,7 +422,7 @@ def qwen2_prefill(w: Dict[str, torch.Tensor], dims: AhaDims, cache: OracleKVCach
     dt = x.dtype
     q = x.shape[1]
     L = cache.get_seq_length()
-    pos = torch.arange(L, L + q, dtype=torch.int64)
+    pos = torch.arange(L, L + q, dtype=torch.int64, device=x.device)
     cos, sin = rope_cos_sin(pos, dims.head_dim, dims.rope_theta, dt)
     nh, nkv, d = dims.heads, dims.kv_heads, dims.head_dim
     klen0 = None
@@ -440,8 +441,8 @@ def qwen2_prefill(w: Dict[str, torch.Tensor], dims: AhaDims, cache: OracleKVCach
         if klen0 is None:
             klen0 = klen
         off = L if mask_mode == "sdpa" else klen - q
-        jj = torch.arange(klen)[None, :]
-        ii = torch.arange(q)[:, None]
+        jj = torch.arange(klen, device=x.device)[None, :]
+        ii = torch.arange(q, device=x.device)[:, None]
         allowed = jj <= (off + ii)
         Kr = K.repeat_interleave(nh // nkv, dim=1)
         Vr = V.repeat_interleave(nh // nkv, dim=1)
