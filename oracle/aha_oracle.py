@@ -22,8 +22,15 @@ It is a plain-PyTorch (CPU) restatement of the reference's algorithm, function b
 Parity pin: the reference ships no golden vectors.  The pieces of the reference that import
 in the authoring container (the three cache classes, the vendored SigLIP tower and image processor, scipy) were
 executed there against this restatement by `oracle/validate_against_reference.py`, and the outputs are committed
-as fixtures under `tests/golden/` by `tests/golden/make_golden.py`.  The Qwen2 decoder glue is pinned only by
-reading transformers 4.49 ("parity unpinned" for that piece).
+as fixtures under `tests/golden/` by `tests/golden/make_golden.py`.  The Qwen2 decoder restatement is pinned by
+execution too (tests/test_oracle_qwen2_pin.py, tests/golden/make_golden_qwen2.py): bit-exact in fp32 and bf16 against
+the installed transformers `Qwen2Model` (eager attention, DynamicCache) chunk by chunk, and - for the 4.49-only
+semantics (positions from get_seq_length(), mask sliced to the Klen the cache returns, cos / sin handed to update()) -
+against HF's own Qwen2DecoderLayer / rotary / norm modules driven with the reference's three cache classes and the 4.49
+additive mask, through eviction + re-rotation, the bidirectional regime of a full cache and the frozen static prefix.
+What remains restated without an executable counterpart: mm_projector + pooling glue (two Linear calls and
+F.interpolate), the three Linear heads and the _encode_frame loop (the modules that hold them import peft /
+bitsandbytes / deepspeed, absent here).
 """
 from __future__ import annotations
 

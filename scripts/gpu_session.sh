@@ -5,7 +5,7 @@ TAG=${1:-s}; shift
 OUT=gpurun_out
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > $OUT/${TAG}_gpu.txt 2>&1
-timeout 1200 python -m pytest tests -m gpu -q -x --timeout 600 "$@" > $OUT/${TAG}_pytest.log 2>&1
+timeout 1200 python -m pytest tests -m gpu -q --maxfail 8 --timeout 600 "$@" > $OUT/${TAG}_pytest.log 2>&1
 echo "pytest rc=$?" >> $OUT/${TAG}_pytest.log
 tail -5 $OUT/${TAG}_pytest.log
 timeout 600 python bench.py --steps 20 --warmup 5 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err
