@@ -1150,6 +1150,251 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The same batched decoder GEMM on CTA PAIRS (tcgen05.mma.cta_group::2, M = 256).  The single-CTA persistent kernel above
+// is bound by L2 -> SM bandwidth: a 128 x 208 tile pulls 42 KB per 416 tensor-pipe cycles (101 B/clk per SM, 15 KB/clk
+// over the chip against the ~6.3 KB/clk the L2 slices deliver) - measured 610 TFLOP/s = 0.43 of the cuBLAS peak.
+// A pair of CTAs (the two SMs of a TPC) takes two neighbouring weight tiles and ALL tokens of a 416-token group: every
+// CTA loads its own 128 weight rows (16 KB) and only HALF of the token rows of each 208-token MMA (2 x 104 rows, 26 KB)
+// per k-block, the tensor cores read the other half from the partner's shared memory: 42 KB per 832 cycles = 50 B/clk.
+// Per CTA the accumulator is 128 features x 416 tokens (two 208-column halves, 416 of the 512 TMEM columns): there is no
+// second accumulator, so the epilogue of an item is not hidden under the next item's main loop; epilogue group g (four
+// warps) drains token half g.  Items = (weight-tile pair, k split, token group); split-K merges are last-arriver as above.
+// ---------------------------------------------------------------------------------------------------------------------
+struct PPCfg {
+  static constexpr int kStages = 5;
+  static constexpr int kHalfRows = kPsBN / 2;                       // token rows of one MMA half held by one CTA
+  static constexpr int kABytes = kBlockM * kBlockK * 2;             // 16384
+  static constexpr int kBHalfBytes = kHalfRows * kBlockK * 2;       // 13312 (13 swizzle atoms)
+  static constexpr int kBBytes = 2 * kBHalfBytes;
+  static constexpr int kStageBytes = kABytes + kBBytes;             // 43008 per CTA
+  static constexpr int kGroupTokens = 2 * kPsBN;                    // 416
+  static constexpr int kEpiWarps = 8;
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
+  static constexpr int kEpiWarpBytes = 1280;
+  static constexpr int kMaxTokens = 832;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiWarpBytes + kMaxTokens * 4 + 256 + 1024;
+};
+
+template <int kAct>
+__global__ void __launch_bounds__(PPCfg::kThreads, 1)
+gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                      const GemmParams p, const int pairs, const int groups) {
+  using C = PPCfg;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ float sq_red[2][4][16];
+  __shared__ int last_flag[2];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + C::kStages * C::kABytes;
+  uint8_t* smem_epi = smem + C::kStages * C::kStageBytes;
+  float* rstd_all = reinterpret_cast<float*>(smem_epi + C::kEpiWarps * C::kEpiWarpBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(rstd_all + C::kMaxTokens);   // used in the leader only
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tmem_full = empty_bar + C::kStages;     // [1]
+  uint64_t* tmem_empty = tmem_full + 1;             // [1], counted in the leader only (both CTAs' epilogue warps arrive)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();           // 0 = leader
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  const int n_items = pairs * groups * p.splits;
+  // item -> (weight-tile pair, split, token group); this CTA's weight tile is 2 * pair + rank
+  auto decode = [&](int it, int& a0, int& b0, int& kb0, int& kb1, int& tile_lin, int& split, int& halves) {
+    const int g = it % groups, r = it / groups;
+    split = r % p.splits;
+    const int pr = r / p.splits;
+    a0 = (2 * pr + (int)rank) * kBlockM; b0 = g * C::kGroupTokens;
+    kb0 = split * p.kb_per_split; kb1 = min(kb_total, kb0 + p.kb_per_split);
+    tile_lin = (2 * pr + (int)rank) * groups + g;
+    halves = (p.Nb - b0 > kPsBN) ? 2 : 1;
+  };
+  const uint64_t pol_a = l2_policy_evict_first(), pol_b = l2_policy_evict_last();
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, 2 * C::kEpiWarps);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc_pair<512>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();        // both CTAs' barriers are initialised before any remote arrival / TMA completion can reach them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs): own weight rows + own half of the token rows, counted by the leader's barrier =====
+    if (lane == 0) {
+      // The weight tiles do not depend on any earlier kernel: the first ring of them (first item only) is requested
+      // before griddepcontrol.wait, i.e. while the previous kernel on the stream may still be running (PDL).
+      int pre = 0;
+      if (cluster_id < n_items) {
+        int a0, b0, kb0, kb1, tl_, sp_, halves;
+        decode(cluster_id, a0, b0, kb0, kb1, tl_, sp_, halves);
+        pre = min(C::kStages, kb1 - kb0);
+        const uint32_t stage_tx = 2u * (uint32_t)(C::kABytes + halves * C::kBHalfBytes);     // both CTAs' bytes
+        for (int kb = 0; kb < pre; ++kb) {
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[kb], stage_tx);
+          tma_load_2d_pair_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], (kb0 + kb) * kBlockK, a0, pol_a);
+        }
+      }
+      pdl_wait();
+      uint32_t cnt = 0;
+      for (int it = cluster_id; it < n_items; it += n_clusters) {
+        int a0, b0, kb0, kb1, tl_, sp_, halves;
+        decode(it, a0, b0, kb0, kb1, tl_, sp_, halves);
+        const uint32_t stage_tx = 2u * (uint32_t)(C::kABytes + halves * C::kBHalfBytes);
+        for (int kb = kb0; kb < kb1; ++kb, ++cnt) {
+          const int s = cnt % C::kStages;
+          if (cnt >= (uint32_t)pre) {
+            mbar_wait(&empty_bar[s], ((cnt / C::kStages) & 1) ^ 1);
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[s], stage_tx);
+            tma_load_2d_pair_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kb * kBlockK, a0, pol_a);
+          }
+          for (int h = 0; h < halves; ++h)
+            tma_load_2d_pair_hint(smem_b + s * C::kBBytes + h * C::kBHalfBytes, &tmap_b, &full_bar[s], kb * kBlockK,
+                                  b0 + h * kPsBN + (int)rank * C::kHalfRows, pol_b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: the leader's elected lane drives the tensor cores of both SMs =====
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16_f32(2 * kBlockM, kPsBN);
+      uint32_t cnt = 0, tl = 0;
+      for (int it = cluster_id; it < n_items; it += n_clusters, ++tl) {
+        int a0, b0, kb0, kb1, tl_, sp_, halves;
+        decode(it, a0, b0, kb0, kb1, tl_, sp_, halves);
+        mbar_wait(tmem_empty, (tl & 1) ^ 1);       // both CTAs' epilogues have drained the accumulator
+        tc_fence_after();
+        for (int kb = kb0; kb < kb1; ++kb, ++cnt) {
+          const int s = cnt % C::kStages;
+          mbar_wait(&full_bar[s], (cnt / C::kStages) & 1);
+          tc_fence_after();
+          const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + s * C::kABytes));
+          for (int h = 0; h < halves; ++h) {
+            const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + s * C::kBBytes + h * C::kBHalfBytes));
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k)
+              umma_f16_ss_pair(tmem_base + h * kPsBN, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                               (kb != kb0 || k != 0) ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[s], 0b11);    // frees the stage in both CTAs
+        }
+        umma_commit_pair(tmem_full, 0b11);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue (both CTAs): warp (w & 3) owns TMEM lanes 32*(w&3).., group (w - 4) / 4 owns token half g =====
+    const int ew = warp & 3, grp = (warp - 4) >> 2;
+    const int i = ew * 32 + lane;
+    const int bar_id = 1 + grp;
+    uint8_t* stage_warp = smem_epi + (warp - 4) * C::kEpiWarpBytes;
+    const uint32_t tmem_empty_leader = mapa_shared(smem_u32(tmem_empty), 0);
+    pdl_wait();   // residuals, norm partials and the output buffer belong to earlier kernels until here
+    if (p.rs_partials) {
+      for (int t = threadIdx.x - 128; t < C::kMaxTokens; t += 32 * C::kEpiWarps) {
+        float sum = 0.f;
+        if (t < p.Nb)
+          for (int r = 0; r < p.rs_n; ++r) sum += __ldcg(p.rs_partials + (size_t)r * p.rs_ld + t);
+        rstd_all[t] = (t < p.Nb) ? rsqrtf(sum * p.rs_inv_cols + p.rs_eps) : 0.f;
+      }
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+    }
+    uint32_t tl = 0;
+    for (int it = cluster_id; it < n_items; it += n_clusters, ++tl) {
+      int a0, b0, kb0, kb1, tile_lin, split, halves;
+      decode(it, a0, b0, kb0, kb1, tile_lin, split, halves);
+      mbar_wait(tmem_full, tl & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
+      const int feat = a0 + i;
+      const bool fvalid = feat < p.Ma;
+      const bool tile_valid = a0 < p.Ma;
+      const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
+      const bool staged = swap_staged_ok(p, a0) && !p.sumsq_out;
+      const int ncols = min(C::kGroupTokens, p.Nb - b0);
+      const int col_begin = grp * kPsBN, my_end = min(col_begin + kPsBN, ncols);
+      if (p.splits == 1) {
+#pragma unroll 1
+        for (int jc = col_begin; jc < my_end; jc += 16) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(taddr + jc, r);
+          tmem_ld_wait();
+          float acc[16];
+#pragma unroll
+          for (int t = 0; t < 16; ++t) acc[t] = __uint_as_float(r[t]);
+          if (p.rs_partials) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
+          }
+          if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
+          else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+          if (p.sumsq_out && tile_valid) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(tmem_empty_leader);
+      } else {
+        constexpr size_t kSplitStride = (size_t)C::kGroupTokens * kBlockM;
+        float* part = p.ws_partial + ((size_t)tile_lin * p.splits + split) * kSplitStride + i;
+#pragma unroll 1
+        for (int jc = col_begin; jc < my_end; jc += 16) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(taddr + jc, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int t = 0; t < 16; ++t) __stcg(part + (jc + t) * kBlockM, __uint_as_float(r[t]));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(tmem_empty_leader);   // the accumulator is free: the rest works on the parked copy
+        __threadfence();
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        if (ew == 0 && lane == 0) {
+          int* cnt = p.ws_pcounters + tile_lin * 2 + grp;
+          const int old = atomicAdd(cnt, 1);
+          const int last = (old == p.splits - 1) ? 1 : 0;
+          if (last) *cnt = 0;                              // self-resetting: nobody else touches it in this launch
+          last_flag[grp] = last;
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        if (last_flag[grp]) {
+          __threadfence();
+          const float* base = p.ws_partial + (size_t)tile_lin * p.splits * kSplitStride + i;
+#pragma unroll 1
+          for (int jc = col_begin; jc < my_end; jc += 16) {
+            float acc[16];
+#pragma unroll
+            for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+            reduce_splits_dyn(base + jc * kBlockM, kSplitStride, p.splits, acc);
+            if (p.rs_partials) {
+#pragma unroll
+              for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
+            }
+            if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
+            else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+            if (p.sumsq_out && tile_valid) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncwarp();
+  cluster_sync_all();      // the partner's tensor-core reads of this CTA's shared memory / writes to its TMEM are over
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<512>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // =====================================================================================
@@ -1371,6 +1616,36 @@ int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const G
 }
 }  // namespace
 
+namespace {
+template <int kAct>
+int launch_swap_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int pairs, int groups, int sm_count,
+                     cudaStream_t stream) {
+  using C = PPCfg;
+  static bool attr_done[16] = {false};
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 16 && !attr_done[dev]) {
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_pair_kernel<kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_pair_kernel<kAct>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_done[dev] = true;
+  }
+  const int n_clusters = std::min(pairs * groups * p.splits, sm_count / 2);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * n_clusters); cfg.blockDim = dim3(C::kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 2 : 1;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_swap_pair_kernel<kAct>, ta, tb, p, pairs, groups));
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+}  // namespace
+
 // ---- bring-up: phase stamps (SM cycles) of CTA (0,0,0) of the most recent launch of each (grid.x, grid.z) class ----
 static unsigned long long* g_gemm_ts = nullptr;   // [64 slots][8]
 static std::map<std::pair<int, int>, int> g_gemm_ts_slot;
@@ -1490,7 +1765,58 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
   else      { p.Ma = c.tokens; p.Nb = c.features; a = c.x; lda = c.ldx; b = c.w; ldb = c.ldw; }
 
-  // Persistent skinny path: batched decoder steps (256 < tokens <= 832)
+  // Batched decoder steps (256 < tokens <= 832) on CTA pairs (AHA_PS_PAIR=0: the single-CTA persistent kernel below)
+  static const int use_pair = getenv("AHA_PS_PAIR") ? atoi(getenv("AHA_PS_PAIR")) : 1;
+  if (swap && c.tokens > 256 && use_pair && c.force_bn != 208) {
+    const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, pairs = (tiles_a + 1) / 2;
+    const int groups = (p.Nb + PPCfg::kGroupTokens - 1) / PPCfg::kGroupTokens;
+    const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+    const int n_clusters = w->sm_count / 2;
+    if (c.sumsq_tiles) *c.sumsq_tiles = tiles_a;
+    int splits = c.force_splits;
+    if (splits <= 0) {
+      // every cluster should get the same number of k-blocks; an item pays for its (unhidden) epilogue, a split item for
+      // parking / merging its partial tile as well (in units of one k-block = 832 tensor-pipe cycles)
+      static const int max_env = getenv("AHA_PS_SPLITS") ? atoi(getenv("AHA_PS_SPLITS")) : 8;
+      long best_cost = -1;
+      for (int s = 1; s <= max_env && s <= kb_total; ++s) {
+        const int kb_per = (kb_total + s - 1) / s;
+        if ((kb_total + kb_per - 1) / kb_per != s || (s > 1 && kb_per < 8)) continue;
+        const long items = (long)pairs * groups * s;
+        const long cost = ((items + n_clusters - 1) / n_clusters) * (kb_per + (s > 1 ? 13 : 7));
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
+      }
+    }
+    if (splits > kb_total) splits = kb_total;
+    int kb_per = (kb_total + splits - 1) / splits;
+    splits = (kb_total + kb_per - 1) / kb_per;
+    const size_t tile_floats = (size_t)PPCfg::kGroupTokens * kBlockM;
+    while (splits > 1 && ((size_t)2 * pairs * groups * splits * tile_floats * sizeof(float) > GemmWorkspace::kPartialBytes ||
+                          2 * pairs * groups * 2 > 4096)) {
+      --splits;
+      kb_per = (kb_total + splits - 1) / splits;
+      splits = (kb_total + kb_per - 1) / kb_per;
+    }
+    p.splits = splits; p.kb_per_split = kb_per; p.dbg = 0;
+    if (splits > 1) {
+      GemmSplitScratch sc;
+      int src = split_scratch(w, stream, &sc, false); if (src) return src;
+      p.ws_partial = sc.partial; p.ws_pcounters = sc.pcounters;
+    }
+    CUtensorMap ta, tb;
+    int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
+    rc = get_tmap(b, p.Nb, p.K, ldb, PPCfg::kHalfRows, &tb); if (rc) return rc;
+    ProfSlot* slot = prof_begin(5, stream);
+    rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_pair<GEMM_ACT_SILU_MUL>(ta, tb, p, pairs, groups, w->sm_count, stream)
+                                    : launch_swap_pair<GEMM_ACT_NONE>(ta, tb, p, pairs, groups, w->sm_count, stream);
+    if (slot) {
+      const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * 2;
+      prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,
+               2.0 * c.tokens * (double)c.features * c.K);
+    }
+    return rc;
+  }
+  // Persistent skinny path, single CTAs (kept as the comparison point; force_bn = 208 selects it)
   if (swap && c.tokens > 256) {
     const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, tiles_b = (p.Nb + kPsBN - 1) / kPsBN;
     const int tiles = tiles_a * tiles_b;

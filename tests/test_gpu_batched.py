@@ -14,11 +14,11 @@ from aha_b200 import _lib
 pytestmark = pytest.mark.gpu
 
 
-def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1):
+def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1, bn=0):
     T, K = x.shape
     F_ = w.shape[0]
     _lib.check(_lib.load().aha_gemm_bf16(_lib.ptr(x), T, K, _lib.ptr(w), F_, K, K, _lib.ptr(out), out.shape[1], 0, 0, act,
-                                         _lib.ptr(bias), _lib.ptr(res), out.shape[1] if res is not None else 0, 0, swap, 0,
+                                         _lib.ptr(bias), _lib.ptr(res), out.shape[1] if res is not None else 0, 0, swap, bn,
                                          splits, _lib.stream_ptr()))
 
 
@@ -33,8 +33,13 @@ def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1):
     (257, 2048, 1024, 3, 2),
     (832, 3584, 3584, 0, 0),      # four column tiles
     (600, 1536, 8960, 3, 4),
+    (392, 896, 3584, 0, 2),       # 7 weight tiles: the last CTA pair has only one valid tile
+    (430, 3584, 2048, 0, 1),      # second token group with a single 208-token half
 ])
-def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits):
+@pytest.mark.parametrize("bn", [0, 208], ids=["cta_pair", "single_cta"])
+def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits, bn):
+    """bn = 0: the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 weight rows x 416 tokens per pair); bn = 208: the
+    single-CTA persistent kernel (128 x 208 tiles, two accumulators)."""
     torch.manual_seed(21)
     x = (torch.randn(T, K, device=cuda) * 0.5).bfloat16()
     w = (torch.randn(F_, K, device=cuda) / K ** 0.5).bfloat16()
@@ -44,7 +49,7 @@ def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits):
     outs = []
     for _ in range(2):
         out = torch.full((T, Fo), float("nan"), dtype=torch.bfloat16, device=cuda) if res is None else res.clone()
-        _gemm(x, w, out, act, bias, out if res is not None else None, splits)       # residual aliases the output
+        _gemm(x, w, out, act, bias, out if res is not None else None, splits, bn=bn)       # residual aliases the output
         outs.append(out)
     torch.cuda.synchronize()
     assert torch.equal(outs[0], outs[1]), "the split merge must be deterministic"
