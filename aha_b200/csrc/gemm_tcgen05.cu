@@ -176,9 +176,11 @@ __device__ __forceinline__ void epi_swap16(const GemmParams& p, int feat, bool f
 // [16 tokens][32 features] block (16 features after SiLU*mul) goes through a small shared-memory tile so that it
 // leaves as 16-byte pieces - 8x fewer global memory instructions than the 2-byte per-token stores, the residual is
 // read the same way.  Same arithmetic and rounding order as epi_swap16.
+// `sq_warp` (plain epilogue only): this warp's 16 per-token sums of squares of the values it stores (its 32 features),
+// the producer side of the folded RMSNorm - four lanes hold the four 16-byte pieces of a token, two shuffles add them.
 template <int kAct>
 __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* stage_warp, int a0, int ew, int lane,
-                                                  float bias, int tok0, float (&acc)[16]) {
+                                                  float bias, int tok0, float (&acc)[16], float* sq_warp = nullptr) {
   constexpr int kFeat = (kAct == GEMM_ACT_SILU_MUL) ? 16 : 32;
   constexpr int kPitch = kFeat * 2 + 16;
   constexpr int kPieces = kFeat / 8;            // 16-byte pieces per token
@@ -212,6 +214,7 @@ __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* 
 #pragma unroll
   for (int idx = lane; idx < 16 * kPieces; idx += 32) {
     const int t = idx / kPieces, pc = idx % kPieces;
+    float ss = 0.f;
     if (t < ntok) {
       uint4 u = *reinterpret_cast<const uint4*>(stage_warp + t * kPitch + pc * 16);
       const int token = tok0 + t, f = fbase + pc * 8;
@@ -228,6 +231,15 @@ __device__ __forceinline__ void epi_swap16_staged(const GemmParams& p, uint8_t* 
         u = make_uint4(w[0], w[1], w[2], w[3]);
       }
       st_v4(out + (size_t)token * p.ldo + f, u);
+      if (kAct == GEMM_ACT_NONE && sq_warp) {
+        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+        ss = a.x * a.x + a.y * a.y + b.x * b.x + b.y * b.y + c.x * c.x + c.y * c.y + d.x * d.x + d.y * d.y;
+      }
+    }
+    if (kAct == GEMM_ACT_NONE && sq_warp) {      // (kPieces == 4: lanes 4j .. 4j+3 hold token j of this pass)
+      ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+      ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+      if (pc == 0) sq_warp[t] = ss;
     }
   }
   __syncwarp();
@@ -248,6 +260,16 @@ __device__ __forceinline__ void emit_sumsq16(const GemmParams& p, float (*sq_red
   if (ew == 0 && lane < ntok)
     p.sumsq_out[(size_t)tile * p.sumsq_ld + tok0 + lane] = sq_red[0][lane] + sq_red[1][lane] + sq_red[2][lane] + sq_red[3][lane];
   asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+}
+
+// Finishes the staged form of the sums of squares: the four warps of an epilogue group have each left their 16 per-token
+// partials in sq[ew][.]; one barrier, then warp 0 adds them in warp order and writes the tile's partial.  The caller
+// alternates between two `sq` buffers from chunk to chunk, so one barrier per chunk is enough.
+__device__ __forceinline__ void finish_sumsq16(const GemmParams& p, float (*sq)[16], int ew, int lane, int tok0, int tile,
+                                               int bar_id) {
+  asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+  if (ew == 0 && lane < min(16, p.Nb - tok0))
+    p.sumsq_out[(size_t)tile * p.sumsq_ld + tok0 + lane] = sq[0][lane] + sq[1][lane] + sq[2][lane] + sq[3][lane];
 }
 
 // Split-K merge of one 16-column chunk: the partials of all S splits are requested before the first use (one L2 round
@@ -943,7 +965,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
                             const GemmParams p, const int tiles_a, const int tiles_b) {
   using C = PSCfg;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ float sq_red[2][4][16];
+  __shared__ float sq_red[2][2][4][16];      // [epilogue group][chunk parity][warp][token]
   __shared__ int last_flag[2];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
@@ -1062,7 +1084,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       }
       asm volatile("bar.sync 3, 256;" ::: "memory");
     }
-    uint32_t tl = 0;
+    uint32_t tl = 0, sq_cnt = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++tl) {
       int a0, b0, kb0, kb1, tile_lin, split;
       decode(it, a0, b0, kb0, kb1, tile_lin, split);
@@ -1073,7 +1095,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       const int feat = a0 + i;
       const bool fvalid = feat < p.Ma;
       const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
-      const bool staged = swap_staged_ok(p, a0) && !p.sumsq_out;
+      const bool staged = swap_staged_ok(p, a0);
       const int ncols = min(kPsBN, p.Nb - b0);
       const int my_end = min(col_end, ncols);
       if (p.splits == 1) {
@@ -1089,9 +1111,14 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
 #pragma unroll
             for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
           }
-          if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
-          else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
-          if (p.sumsq_out) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          if (staged) {
+            float (*sq)[16] = sq_red[grp][sq_cnt++ & 1];     // running parity: consecutive chunks never share a buffer
+            epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc, p.sumsq_out ? sq[ew] : nullptr);
+            if (p.sumsq_out) finish_sumsq16(p, sq, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          } else {
+            epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+            if (p.sumsq_out) emit_sumsq16(p, sq_red[grp][0], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -1133,9 +1160,14 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
 #pragma unroll
               for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
             }
-            if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
-            else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
-            if (p.sumsq_out) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+            if (staged) {
+              float (*sq)[16] = sq_red[grp][sq_cnt++ & 1];     // running parity: consecutive chunks never share a buffer
+              epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc, p.sumsq_out ? sq[ew] : nullptr);
+              if (p.sumsq_out) finish_sumsq16(p, sq, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+            } else {
+              epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+              if (p.sumsq_out) emit_sumsq16(p, sq_red[grp][0], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+            }
           }
         }
       }
@@ -1183,7 +1215,7 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
                       const GemmParams p, const int pairs, const int groups) {
   using C = PPCfg;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ float sq_red[2][4][16];
+  __shared__ float sq_red[2][2][4][16];      // [epilogue group][chunk parity][warp][token]
   __shared__ int last_flag[2];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
@@ -1306,7 +1338,7 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
       }
       asm volatile("bar.sync 3, 256;" ::: "memory");
     }
-    uint32_t tl = 0;
+    uint32_t tl = 0, sq_cnt = 0;
     for (int it = cluster_id; it < n_items; it += n_clusters, ++tl) {
       int a0, b0, kb0, kb1, tile_lin, split, halves;
       decode(it, a0, b0, kb0, kb1, tile_lin, split, halves);
@@ -1317,7 +1349,7 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
       const bool fvalid = feat < p.Ma;
       const bool tile_valid = a0 < p.Ma;
       const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
-      const bool staged = swap_staged_ok(p, a0) && !p.sumsq_out;
+      const bool staged = swap_staged_ok(p, a0);
       const int ncols = min(C::kGroupTokens, p.Nb - b0);
       const int col_begin = grp * kPsBN, my_end = min(col_begin + kPsBN, ncols);
       if (p.splits == 1) {
@@ -1333,9 +1365,14 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
 #pragma unroll
             for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
           }
-          if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
-          else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
-          if (p.sumsq_out && tile_valid) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          if (staged) {
+            float (*sq)[16] = sq_red[grp][sq_cnt++ & 1];     // running parity: consecutive chunks never share a buffer
+            epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc, p.sumsq_out ? sq[ew] : nullptr);
+            if (p.sumsq_out) finish_sumsq16(p, sq, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          } else {
+            epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+            if (p.sumsq_out && tile_valid) emit_sumsq16(p, sq_red[grp][0], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -1377,9 +1414,14 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
 #pragma unroll
               for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
             }
-            if (staged) epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc);
-            else epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
-            if (p.sumsq_out && tile_valid) emit_sumsq16(p, sq_red[grp], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+            if (staged) {
+              float (*sq)[16] = sq_red[grp][sq_cnt++ & 1];     // running parity: consecutive chunks never share a buffer
+              epi_swap16_staged<kAct>(p, stage_warp, a0, ew, lane, bias, b0 + jc, acc, p.sumsq_out ? sq[ew] : nullptr);
+              if (p.sumsq_out) finish_sumsq16(p, sq, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+            } else {
+              epi_swap16<kAct>(p, feat, fvalid, bias, i, b0 + jc, acc);
+              if (p.sumsq_out && tile_valid) emit_sumsq16(p, sq_red[grp][0], acc, fvalid, ew, lane, b0 + jc, a0 / kBlockM, bar_id);
+            }
           }
         }
       }
