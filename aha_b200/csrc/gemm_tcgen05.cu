@@ -1078,8 +1078,18 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     if (p.rs_partials) {
       for (int t = threadIdx.x - 128; t < C::kMaxTokens; t += 32 * C::kEpiWarps) {
         float sum = 0.f;
-        if (t < p.Nb)
-          for (int r = 0; r < p.rs_n; ++r) sum += __ldcg(p.rs_partials + (size_t)r * p.rs_ld + t);
+        if (t < p.Nb) {
+          // partial sums in tile order (the order the one-shot kernel adds them in), eight loads in flight at a time:
+          // one dependent L2 round trip per partial would take longer than the first item's main loop
+#pragma unroll 1
+          for (int r0 = 0; r0 < p.rs_n; r0 += 8) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = (r0 + j < p.rs_n) ? __ldcg(p.rs_partials + (size_t)(r0 + j) * p.rs_ld + t) : 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sum += v[j];
+          }
+        }
         rstd_all[t] = (t < p.Nb) ? rsqrtf(sum * p.rs_inv_cols + p.rs_eps) : 0.f;
       }
       asm volatile("bar.sync 3, 256;" ::: "memory");
@@ -1332,8 +1342,18 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
     if (p.rs_partials) {
       for (int t = threadIdx.x - 128; t < C::kMaxTokens; t += 32 * C::kEpiWarps) {
         float sum = 0.f;
-        if (t < p.Nb)
-          for (int r = 0; r < p.rs_n; ++r) sum += __ldcg(p.rs_partials + (size_t)r * p.rs_ld + t);
+        if (t < p.Nb) {
+          // partial sums in tile order (the order the one-shot kernel adds them in), eight loads in flight at a time:
+          // one dependent L2 round trip per partial would take longer than the first item's main loop
+#pragma unroll 1
+          for (int r0 = 0; r0 < p.rs_n; r0 += 8) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = (r0 + j < p.rs_n) ? __ldcg(p.rs_partials + (size_t)(r0 + j) * p.rs_ld + t) : 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sum += v[j];
+          }
+        }
         rstd_all[t] = (t < p.Nb) ? rsqrtf(sum * p.rs_inv_cols + p.rs_eps) : 0.f;
       }
       asm volatile("bar.sync 3, 256;" ::: "memory");
