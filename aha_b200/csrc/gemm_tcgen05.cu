@@ -1827,9 +1827,10 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   if (swap) { p.Ma = c.features; p.Nb = c.tokens; a = c.w; lda = c.ldw; b = c.x; ldb = c.ldx; }
   else      { p.Ma = c.tokens; p.Nb = c.features; a = c.x; lda = c.ldx; b = c.w; ldb = c.ldw; }
 
-  // Batched decoder steps (256 < tokens <= 832) on CTA pairs (AHA_PS_PAIR=0: the single-CTA persistent kernel below)
-  static const int use_pair = getenv("AHA_PS_PAIR") ? atoi(getenv("AHA_PS_PAIR")) : 1;
-  if (swap && c.tokens > 256 && use_pair && c.force_bn != 208) {
+  // Batched decoder steps (256 < tokens <= 832) on CTA pairs: opt-in (AHA_PS_PAIR=1 or force_bn = 416); the default is the
+  // single-CTA persistent kernel below
+  static const int use_pair = getenv("AHA_PS_PAIR") ? atoi(getenv("AHA_PS_PAIR")) : 0;   // measured slower in the step (its epilogue is not hidden): opt-in
+  if (swap && c.tokens > 256 && (use_pair || c.force_bn == 416) && c.force_bn != 208) {
     const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, pairs = (tiles_a + 1) / 2;
     const int groups = (p.Nb + PPCfg::kGroupTokens - 1) / PPCfg::kGroupTokens;
     const int kb_total = (p.K + kBlockK - 1) / kBlockK;

@@ -1,12 +1,12 @@
 """Times the four decoder GEMMs of a batched step (T tokens) with weights rotating through copies larger than the L2:
-    python scripts/gpu_gemm_batched.py [T] [bn ...]      bn: 0 = CTA-pair kernel, 208 = single-CTA persistent kernel"""
+    python scripts/gpu_gemm_batched.py [T] [bn ...]      bn: 416 = CTA-pair kernel, 208 = single-CTA persistent kernel"""
 import sys
 import torch
 sys.path.insert(0, ".")
 from aha_b200 import _lib
 
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 392
-bns = [int(a) for a in sys.argv[2:]] or [0, 208]
+bns = [int(a) for a in sys.argv[2:]] or [416, 208]
 dev = torch.device("cuda:0")
 lib = _lib.load()
 shapes = [("qkv", 4608, 3584, 0), ("o", 3584, 3584, 0), ("gate|up", 37888, 3584, 3), ("down", 3584, 18944, 0)]

@@ -36,9 +36,9 @@ def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1, bn=0):
     (392, 896, 3584, 0, 2),       # 7 weight tiles: the last CTA pair has only one valid tile
     (430, 3584, 2048, 0, 1),      # second token group with a single 208-token half
 ])
-@pytest.mark.parametrize("bn", [0, 208], ids=["cta_pair", "single_cta"])
+@pytest.mark.parametrize("bn", [416, 208], ids=["cta_pair", "single_cta"])
 def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits, bn):
-    """bn = 0: the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 weight rows x 416 tokens per pair); bn = 208: the
+    """bn = 416: the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 weight rows x 416 tokens per pair); bn = 208: the
     single-CTA persistent kernel (128 x 208 tiles, two accumulators)."""
     torch.manual_seed(21)
     x = (torch.randn(T, K, device=cuda) * 0.5).bfloat16()
