@@ -36,6 +36,7 @@ namespace {
 constexpr int kTile = 128;          // query rows per CTA == keys per tile
 constexpr int kAtomBytes = 16384;   // one [128 rows][64 bf16] swizzled box
 constexpr int kStagesKV = 2;
+constexpr int kPBufs = 2;           // P tiles in shared memory
 constexpr int kAttnThreads = 384;   // warps 0-3: TMA / MMA / TMEM, warps 4-11: softmax (two threads per query row)
 constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
@@ -46,9 +47,11 @@ struct AttnSmem {
   static __host__ __device__ int k_off(int DB) { return DB * kAtomBytes; }
   static __host__ __device__ int v_off(int DB) { return DB * kAtomBytes * (1 + kStagesKV); }
   static __host__ __device__ int p_off(int DB) { return DB * kAtomBytes * (1 + 2 * kStagesKV); }
-  static __host__ __device__ int bar_off(int DB) { return p_off(DB) + 2 * kAtomBytes; }
+  static __host__ __device__ int bar_off(int DB) { return p_off(DB) + kPBufs * 2 * kAtomBytes; }   // two P tiles (see the softmax loop)
   static __host__ __device__ int xch_off(int DB) { return bar_off(DB) + 256; }      // float [2][2][128] row-statistics exchange
-  static __host__ __device__ int total(int DB) { return xch_off(DB) + 2048 + 1024; }
+  // no alignment slack: 7 x 32 KB of tiles + 2.25 KB is all a CTA can have; the dynamic window of a kernel without static
+  // shared memory starts 1024-aligned (checked at kernel entry)
+  static __host__ __device__ int total(int DB) { return xch_off(DB) + 2048; }
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -77,8 +80,9 @@ __device__ __noinline__ uint32_t visible_mask32(const AttnSeg& seg, int p0, int 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                  const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ AttnProblem p, const int splits) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) { if (threadIdx.x == 0) printf("aha_b200: attention shared memory is not 1024-byte aligned\n"); __trap(); }
   const int DB = (p.d_pad + 63) >> 6;
   uint8_t* sQ = smem + AttnSmem::q_off();
   uint8_t* sK = smem + AttnSmem::k_off(DB);
@@ -91,11 +95,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint64_t* k_full = bars + 1;         // kStagesKV
   uint64_t* k_empty = bars + 3;        // kStagesKV
   uint64_t* s_full = bars + 5;         // 2
-  uint64_t* p_full = bars + 7;         // 1 (128 arrivals)
-  uint64_t* pv_done = bars + 8;        // 1
-  uint64_t* v_full = bars + 9;         // kStagesKV
-  uint64_t* v_empty = bars + 11;       // kStagesKV
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint64_t* p_full = bars + 7;         // kPBufs (256 arrivals each)
+  uint64_t* pv_done = bars + 9;        // kPBufs: P.V of tile t commits to pv_done[t & 1]
+  uint64_t* v_full = bars + 11;        // kStagesKV
+  uint64_t* v_empty = bars + 13;       // kStagesKV
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
   float* xch = reinterpret_cast<float*>(smem + AttnSmem::xch_off(DB));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -121,8 +125,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
     }
     mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
-    mbar_init(p_full, 256);
-    mbar_init(pv_done, 1);
+    for (int b = 0; b < kPBufs; ++b) { mbar_init(&p_full[b], 256); mbar_init(&pv_done[b], 1); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_slot);
@@ -230,9 +233,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           if (it + 1 < nkt) issue_qk(it + 1);
           const int s = it % kStagesKV;
           mbar_wait(&v_full[s], (it / kStagesKV) & 1);
-          mbar_wait(p_full, it & 1);
+          mbar_wait(&p_full[it & 1], (it >> 1) & 1);
           tc_fence_after();
-          const uint32_t pa = smem_u32(sP), va = smem_u32(sV + s * stage_bytes);
+          const uint32_t pa = smem_u32(sP + (it & 1) * 2 * kAtomBytes), va = smem_u32(sV + s * stage_bytes);
           for (int ks = 0; ks < kTile / 16; ++ks) {
             const uint64_t da = make_kmajor_sw128_desc(pa + (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32);
             // V tile is MN-major: 64-column blocks kAtomBytes apart (LBO), 8-key groups 1024 B apart (SBO)
@@ -240,7 +243,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             umma_f16_ss(tmem_base + kColO, da, db, idesc_pv, (it | ks) != 0);
           }
           umma_commit(&v_empty[s]);
-          umma_commit(pv_done);
+          umma_commit(&pv_done[it & 1]);
         }
       }
     } else if (warp >= 4) {
@@ -248,8 +251,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const int limit = seg.off + tok;           // logical key index must be <= limit
       const float sl2 = p.scale * 1.4426950408889634f;
       const bool all_visible = seg.off >= seg.klen - 1;
-      uint8_t* prow = sP + row * 128;
+      // Two P tiles: the probabilities of tile t go to buffer t & 1, so the exponentials of tile t + 1 are computed and
+      // stored while the tensor pipe still multiplies P(t) by V(t).  With one buffer every tile paid for softmax, P.V and
+      // two barrier round trips in sequence (4460 cycles per tile at 8192 keys, tensor pipe 28 % busy, XU pipe 28 %).
       for (int it = 0; it < nkt; ++it) {
+        uint8_t* prow = sP + (it & 1) * 2 * kAtomBytes + row * 128;
         const int kt = kt0 + it;
         mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
@@ -296,9 +302,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           m_used = tmax;
           rescale = true;
         }
-        // P smem and O are owned by the tensor pipe until P.V of the previous tile has completed
-        if (it > 0) mbar_wait(pv_done, (it - 1) & 1);
+        // this tile's P buffer is owned by the tensor pipe until P.V of tile it - 2 has completed
+        if (it >= 2) mbar_wait(&pv_done[it & 1], ((it >> 1) - 1) & 1);
         if (it > 0 && __any_sync(0xffffffffu, rescale)) {
+          // O may only be rescaled between two P.V products: wait for the previous one (the MMAs complete in order) ...
+          mbar_wait(&pv_done[(it - 1) & 1], ((it - 1) >> 1) & 1);
           tc_fence_after();
 #pragma unroll 1
           for (int cc = half * 16; cc < p.d_pad; cc += 32) {
@@ -336,7 +344,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         l_sum += acc_l;
         fence_proxy_async();
         tc_fence_before();
-        mbar_arrive(p_full);
+        mbar_arrive(&p_full[it & 1]);
         dbg_stamp(ts, 4 + 2 * min(it, 1));
         if (it == 2) { dbg_stamp(ts, 9); }
         if (it == 1) { dbg_stamp(ts, 10); }
@@ -348,7 +356,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         asm volatile("bar.sync %0, 64;" ::"r"(2 + ew) : "memory");
         l_sum = x[row] + x[128 + row];
       }
-      mbar_wait(pv_done, (nkt - 1) & 1);   // O complete
+      mbar_wait(&pv_done[(nkt - 1) & 1], ((nkt - 1) >> 1) & 1);   // O complete
       tc_fence_after();
       dbg_stamp(ts, 7);
     }
