@@ -515,8 +515,9 @@ class LiveInferOracle:
         self.w, self.dims, self.dtype = w, dims, dtype
         self.cache_args = dict(alt_cache=alt_cache, window_length=window_length, num_sink_tokens=num_sink_tokens,
                                sink_cache=sink_cache, n_sys=n_sys)
-        self.start_ids = synthetic_prompt_ids(n_sys, dims.vocab, prompt_seed)
-        self.query_ids = synthetic_prompt_ids(n_query, dims.vocab, prompt_seed + 1) if n_query > 0 else None
+        self.device = w["model.embed_tokens.weight"].device      # the oracle runs where its weights live
+        self.start_ids = synthetic_prompt_ids(n_sys, dims.vocab, prompt_seed).to(self.device)
+        self.query_ids = synthetic_prompt_ids(n_query, dims.vocab, prompt_seed + 1).to(self.device) if n_query > 0 else None
         self.frame_fps = frame_fps
         self.mask_mode = mask_mode
         self.score_heads = list(score_heads)
@@ -531,10 +532,11 @@ class LiveInferOracle:
         self.init_vision_time = False
         self.debug_data_list: List[dict] = []
         self.trace: List[dict] = []           # per-chunk integer trace (positions, Klen, cache ids)
+        self.hidden_last: List[torch.Tensor] = []   # final-norm hidden state of the last token of every frame chunk (fp32)
         self.stream_end_score_sum = 0.0
 
     def input_video_stream(self, frames_u8: torch.Tensor, batch_size: int = 32):
-        pv = preprocess(frames_u8).to(self.dtype)
+        pv = preprocess(frames_u8.to(self.device)).to(self.dtype)
         nt = self.dims.frame_num_tokens
         for b in range(0, len(pv), batch_size):
             emb = visual_embed(self.w, self.dims, pv[b:b + batch_size]).split(nt)
@@ -564,11 +566,12 @@ class LiveInferOracle:
             last_ids = self.start_ids
             self.init_vision_time = True
         else:
-            last_ids = torch.zeros(1, 0, dtype=torch.int64)
+            last_ids = torch.zeros(1, 0, dtype=torch.int64, device=self.device)
         x = torch.cat([self._embed(last_ids).view(1, -1, self.dims.hidden), emb.view(1, -1, self.dims.hidden)], dim=1)
         out = qwen2_prefill(self.w, self.dims, self.cache, x, self.mask_mode, want_logits=self.want_logits)
         self._record("frame", out)
         self.last_out = out
+        self.hidden_last.append(out.hidden[0, -1].float().cpu())
         return frame_scores(out)
 
     def inference(self):
@@ -582,6 +585,32 @@ class LiveInferOracle:
             self.stream_end_score_sum += sum(v for k, v in scores.items() if k in self.score_heads)
             self.video_time += 1 / self.frame_fps
         return self.debug_data_list
+
+
+def aligned_heads(w: Dict[str, torch.Tensor], hidden_last: List[torch.Tensor], logit_std=(1.0, 1.0, 0.3),
+                  skip: int = 2) -> Dict[str, torch.Tensor]:
+    """TEST CONSTRUCTION, not part of the reference: score heads with a trained model's spread on random-init weights.
+    With N(0, 0.02) heads the per-frame scores of a random-init model are nearly flat: the head direction is random, so it
+    picks up 1/H of the frame-to-frame variance of the final hidden state while bf16 rounding noise is isotropic, and
+    rank correlation measures the noise.  A trained head points where the frames differ; this returns a copy of `w` whose
+    three heads lie along the first three principal directions of the given final hidden states (one per frame, e.g. of
+    an fp32 oracle run), scaled so the head outputs have the given standard deviations over those frames.  Everything
+    else - and the arithmetic every implementation runs - is unchanged; all implementations under test get the SAME
+    weights.  The first `skip` frames (the chunk that carries the system prompt is an outlier) are left out of the fit."""
+    Hm = torch.stack([h.float().cpu() for h in hidden_last[skip:]])
+    Hc = Hm - Hm.mean(0, keepdim=True)
+    _, _, Vt = torch.linalg.svd(Hc, full_matrices=False)
+    out = dict(w)
+    dt, dev = w["relevance_head.weight"].dtype, w["relevance_head.weight"].device
+    dirs = []
+    for k in range(3):
+        v = Vt[k]
+        dirs.append(v * (logit_std[k] / max(float((Hc @ v).std()), 1e-12)))
+    # informative = softmax over two logits: +-v/2 gives logit difference v.h
+    out["informative_head.weight"] = torch.stack([-0.5 * dirs[0], 0.5 * dirs[0]]).to(dt).to(dev)
+    out["relevance_head.weight"] = dirs[1][None].to(dt).to(dev)
+    out["uncertainty_head.weight"] = dirs[2][None].to(dt).to(dev)
+    return out
 
 
 # ----------------------------------------------------------------------------------------------
