@@ -139,10 +139,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   // overlaps their HBM latency with that kernel (the new rows land in the same L2 lines, so the TMA loads after the wait
   // read current data).
   static_assert(kStagesKV >= 1, "");
-  if (warp == 3 && lane == 0 && splits > 1 && p.kv_prefetch) {
+  if (warp == 3 && lane == 0 && p.kv_prefetch) {
     const int k_row = seg.k_row0 + blk * p.k_head_rows, k_col = p.k_col0 + blk * p.k_col_step;
     const int v_row = seg.v_row0 + blk * p.k_head_rows, v_col = p.v_col0 + blk * p.v_col_step;
-    for (int it = 0; it < nkt; ++it) {
+    // (at most kv_prefetch tiles ahead: a long key axis is requested in a rolling window by the producers below - all of
+    // it at once would not fit the L2 next to the other CTAs' windows)
+    for (int it = 0; it < min(nkt, p.kv_prefetch); ++it) {
       const int key0 = (kt0 + it) * kTile;
       for (int b = 0; b < DB; ++b) {
         tma_prefetch_2d(tmk, k_col + b * 64, k_row + key0);
@@ -184,6 +186,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int it = 0; it < nkt; ++it) {
           const int s = it % kStagesKV;
           const uint32_t ph = (it / kStagesKV) & 1;
+          // rolling L2 window: with two ring stages a tile is requested one tile period before it is needed, which is about
+          // the HBM latency - the period then stretches to the latency (2.4 us per tile at 8192 keys, tensor pipe 28 % busy)
+          if (p.kv_prefetch && it + p.kv_prefetch < nkt)
+            for (int b = 0; b < DB; ++b) tma_prefetch_2d(tmk, k_col + b * 64, k_row + (kt0 + it + p.kv_prefetch) * kTile);
           mbar_wait(&k_empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&k_full[s], stage_bytes);
           const int key0 = (kt0 + it) * kTile;
@@ -201,6 +207,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int it = 0; it < nkt; ++it) {
           const int s = it % kStagesKV;
           const uint32_t ph = (it / kStagesKV) & 1;
+          if (p.kv_prefetch && it + p.kv_prefetch < nkt)
+            for (int b = 0; b < DB; ++b) tma_prefetch_2d(tmv, v_col + b * 64, v_row + (kt0 + it + p.kv_prefetch) * kTile);
           mbar_wait(&v_empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&v_full[s], stage_bytes);
           const int key0 = (kt0 + it) * kTile;
@@ -668,7 +676,8 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
-  { static const int kvpf = getenv("AHA_KV_PF") ? atoi(getenv("AHA_KV_PF")) : 1; p.kv_prefetch = kvpf; }
+  // K / V tiles requested into L2 ahead of the TMA ring (0: off); the short key axes of the single-stream step fit whole
+  { static const int kvpf = getenv("AHA_KV_PF") ? atoi(getenv("AHA_KV_PF")) : 6; p.kv_prefetch = (splits > 1 || max_tiles >= 16) ? kvpf : 0; }
   // per-launch timing for bench.py's roofline leg: class 3 = many-tile batched attention (SigLIP), 4 = chunk versus cache
   ProfSlot* slot = prof_begin(ctas >= sm_count ? 3 : 4, st);
   AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));

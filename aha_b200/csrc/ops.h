@@ -61,7 +61,7 @@ struct AttnProblem {
   float* ws_partial;        // key-split scratch (filled in by op_attention): per CTA [128][d_pad] fp32 O, then m[128], l[128]
   int* ws_counters;         // arrival counter per (segment, block, query tile) in this launch's bank (see gemm.h)
   int* ws_zero;             // the other counter bank, zeroed by this launch
-  int kv_prefetch;          // key-split launches: request the K / V tiles into L2 before griddepcontrol.wait
+  int kv_prefetch;          // key-split launches: K / V tiles requested into L2 ahead of the TMA ring (before griddepcontrol.wait, then rolling)
   int ws_zero_n;
   int no_split;             // 1: never split the key axis (the kernel's splits wait for each other; see gemm_bf16)
   int merge_last;           // key-split launches whose CTAs are not all co-resident: nobody waits, the LAST split to arrive
