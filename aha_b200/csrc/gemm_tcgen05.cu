@@ -1894,7 +1894,8 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
         const int kb_per = (kb_total + s - 1) / s;
         if ((kb_total + kb_per - 1) / kb_per != s || (s > 1 && kb_per < 8)) continue;
         const long items = (long)tiles * s;
-        const long cost = ((items + w->sm_count - 1) / w->sm_count) * (kb_per + (s > 1 ? 8 : 2));
+        // (measured in the batched step: with residual + sum-of-squares epilogues, down runs faster split 2 ways than 5)
+        const long cost = ((items + w->sm_count - 1) / w->sm_count) * (kb_per + (s > 1 ? 14 + 6 * s : 2));
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
       }
     }

@@ -1,7 +1,9 @@
 // Highlight post-processing on the score stream: find_ticks of test/live_infer_for_video.py:195-228 and
 // test/live_video/infer_live_video.py:70-91, i.e. scipy.signal.savgol_filter(x, 15, 3) -> thresh = mean + 0.5*std ->
 // scipy.signal.find_peaks(height=thresh, prominence, distance), as ONE kernel: one 256-thread block per stream, float64
-// throughout (the reference works on a Python float list -> np.float64).
+// throughout (the reference works on a Python float list -> np.float64).  The smoothed signal, the candidate peaks and
+// their state stay in shared memory (two blocks per SM at 10 000 samples); mean and std are added up in numpy's pairwise
+// order, so the height threshold is bit-identical to the reference's.
 //
 // Algorithmic bytes per stream: read T*8 B of scores, write the peak list (+ T*8 B smoothed when asked for).
 // The find_peaks stages are exact restatements of scipy/signal/_peak_finding_utils.pyx:
@@ -19,18 +21,6 @@ __constant__ double cTail[7][15];
 
 constexpr int kPPThreads = 256;
 
-__device__ __forceinline__ double block_sum_d(double v, double* red) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  __syncthreads();
-  if (lane == 0) red[w] = v;
-  __syncthreads();
-  double r = 0.0;
-  for (int i = 0; i < kPPThreads / 32; ++i) r += red[i];
-  return r;
-}
-
 // exclusive block scan of one int per thread; returns the exclusive prefix, *total gets the block sum
 __device__ __forceinline__ int block_exscan(int v, int* sh, int* total) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -46,21 +36,100 @@ __device__ __forceinline__ int block_exscan(int v, int* sh, int* total) {
   return base + inc - v;
 }
 
+// ---- numpy's pairwise summation (numpy/_core/src/umath/loops_utils.h.src, DOUBLE_pairwise_sum), which is what
+// smoothed.mean() and smoothed.std() of the reference add up with: blocks of at most 128 elements are summed with eight
+// interleaved accumulators, larger ranges are split at n/2 rounded down to a multiple of 8 and the halves added.
+// Reproducing the association order makes mean, std and therefore the height threshold BIT-IDENTICAL to numpy's, so a peak
+// whose smoothed height sits exactly on the threshold is kept or dropped exactly as scipy does.
+struct PwLeaf { int start, len; };
+
+// leaf table of the recursion over n elements, in left-to-right order (one thread); returns the leaf count
+__device__ int pw_build_leaves(int n, PwLeaf* leaves, int cap) {
+  int stack_start[48], stack_len[48];
+  int sp = 0, nl = 0;
+  stack_start[0] = 0; stack_len[0] = n; sp = 1;
+  while (sp > 0) {
+    --sp;
+    const int st = stack_start[sp], ln = stack_len[sp];
+    if (ln <= 128) { if (nl < cap) leaves[nl] = PwLeaf{st, ln}; ++nl; continue; }
+    int n2 = ln / 2; n2 -= n2 % 8;
+    // right half first onto the stack so that the left half is expanded first (leaves come out in order)
+    stack_start[sp] = st + n2; stack_len[sp] = ln - n2; ++sp;
+    stack_start[sp] = st; stack_len[sp] = n2; ++sp;
+  }
+  return nl;
+}
+
+template <bool kCentered>
+__device__ __forceinline__ double pw_elem(const double* y, int i, double mean) {
+  if (!kCentered) return y[i];
+  const double d = __dsub_rn(y[i], mean);
+  return __dmul_rn(d, d);
+}
+
+template <bool kCentered>
+__device__ double pw_leaf_sum(const double* y, PwLeaf lf, double mean) {
+  const double* a = y;
+  const int o = lf.start, n = lf.len;
+  if (n < 8) {
+    double res = 0.0;
+    for (int i = 0; i < n; ++i) res = __dadd_rn(res, pw_elem<kCentered>(a, o + i, mean));
+    return res;
+  }
+  double r[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r[j] = pw_elem<kCentered>(a, o + j, mean);
+  int i = 8;
+  for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], pw_elem<kCentered>(a, o + i + j, mean));
+  }
+  double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                         __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+  for (; i < n; ++i) res = __dadd_rn(res, pw_elem<kCentered>(a, o + i, mean));
+  return res;
+}
+
+// adds the leaf sums in the recursion's order (one thread): same splitting rule, leaves consumed left to right
+__device__ double pw_combine(const double* leaf_sums, int n, int* next_leaf) {
+  if (n <= 128) return leaf_sums[(*next_leaf)++];
+  int n2 = n / 2; n2 -= n2 % 8;
+  const double a = pw_combine(leaf_sums, n2, next_leaf);
+  const double b = pw_combine(leaf_sums, n - n2, next_leaf);
+  return __dadd_rn(a, b);
+}
+
+__device__ __forceinline__ double warp_min_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// kSmem: the smoothed signal, the candidate list and its state live in shared memory (T up to ~21 000 samples); otherwise
+// in the per-stream global workspaces.  Algorithmic bytes per stream: T * 8 read, the peak list written.
+template <bool kSmem>
 __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __restrict__ scores, int T, double prominence,
                                                                int distance, const double* __restrict__ thresh_in,
                                                                int32_t* __restrict__ peaks_out, int max_peaks,
                                                                int32_t* __restrict__ n_peaks, double* __restrict__ smoothed,
-                                                               double* __restrict__ thresh_out, int32_t* __restrict__ cand_ws,
-                                                               int8_t* __restrict__ state_ws, int cand_cap) {
-  __shared__ double red[kPPThreads / 32];
+                                                               double* __restrict__ thresh_out, double* __restrict__ y_ws,
+                                                               int32_t* __restrict__ cand_ws, int8_t* __restrict__ state_ws,
+                                                               int cand_cap, int leaf_cap) {
+  extern __shared__ __align__(16) uint8_t pp_smem[];
   __shared__ int sh_i[kPPThreads / 32];
   __shared__ int sh_flag;
+  __shared__ int sh_nleaves;
+  __shared__ double sh_val;
   const int s = blockIdx.x;
   const double* x = scores + (size_t)s * T;
-  double* y = smoothed + (size_t)s * T;
-  int32_t* cand = cand_ws + (size_t)s * cand_cap;
-  int8_t* state = state_ws + (size_t)s * cand_cap;
-  const int tid = threadIdx.x;
+  // shared-memory carve-up: leaf table + leaf sums always; y / cand / state when they fit
+  PwLeaf* leaves = reinterpret_cast<PwLeaf*>(pp_smem);
+  double* leaf_sums = reinterpret_cast<double*>(pp_smem + (size_t)leaf_cap * sizeof(PwLeaf));
+  uint8_t* after = reinterpret_cast<uint8_t*>(leaf_sums + leaf_cap);
+  double* y = kSmem ? reinterpret_cast<double*>(after) : y_ws + (size_t)s * T;
+  int32_t* cand = kSmem ? reinterpret_cast<int32_t*>(after + (size_t)T * 8) : cand_ws + (size_t)s * cand_cap;
+  int8_t* state = kSmem ? reinterpret_cast<int8_t*>(after + (size_t)T * 8 + (size_t)cand_cap * 4) : state_ws + (size_t)s * cand_cap;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // ---- A. Savitzky-Golay(15, 3), mode='interp' ----
   for (int i = tid; i < T; i += kPPThreads) {
@@ -79,20 +148,32 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
       for (int k = 0; k < 15; ++k) v = __dadd_rn(v, __dmul_rn(cTail[r][k], x[T - 15 + k]));
     }
     y[i] = v;
+    if (kSmem && smoothed) smoothed[(size_t)s * T + i] = v;
   }
+  if (tid == 0) sh_nleaves = pw_build_leaves(T, leaves, leaf_cap);
   __syncthreads();
 
-  // ---- B. threshold = mean + 0.5 * std (ddof = 0) of the smoothed signal ----
+  // ---- B. threshold = mean + 0.5 * std (ddof = 0) of the smoothed signal, in numpy's summation order ----
   double th;
   const bool auto_thresh = (thresh_in == nullptr) || isnan(thresh_in[s]);
-  {
-    double acc = 0.0;
-    for (int i = tid; i < T; i += kPPThreads) acc += y[i];
-    const double mean = block_sum_d(acc, red) / (double)T;
-    acc = 0.0;
-    for (int i = tid; i < T; i += kPPThreads) { const double dl = y[i] - mean; acc += dl * dl; }
-    const double var = block_sum_d(acc, red) / (double)T;
-    th = auto_thresh ? mean + 0.5 * sqrt(var) : thresh_in[s];
+  if (auto_thresh) {
+    const int nl = min(sh_nleaves, leaf_cap);
+    for (int l = tid; l < nl; l += kPPThreads) leaf_sums[l] = pw_leaf_sum<false>(y, leaves[l], 0.0);
+    __syncthreads();
+    if (tid == 0) { int nx = 0; sh_val = __ddiv_rn(pw_combine(leaf_sums, T, &nx), (double)T); }
+    __syncthreads();
+    const double mean = sh_val;
+    for (int l = tid; l < nl; l += kPPThreads) leaf_sums[l] = pw_leaf_sum<true>(y, leaves[l], mean);
+    __syncthreads();
+    if (tid == 0) {
+      int nx = 0;
+      const double var = __ddiv_rn(pw_combine(leaf_sums, T, &nx), (double)T);
+      sh_val = __dadd_rn(mean, __dmul_rn(0.5, sqrt(var)));
+    }
+    __syncthreads();
+    th = sh_val;
+  } else {
+    th = thresh_in[s];
   }
   if (tid == 0 && thresh_out) thresh_out[s] = th;
 
@@ -159,15 +240,30 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
     __syncthreads();
   }
 
-  // ---- E. prominence over the full signal (wlen=None), then the final ordered compaction ----
-  for (int k = tid; k < m; k += kPPThreads) {
-    if (state[k] != 1) continue;
+  // ---- E. prominence over the full signal (wlen=None): one WARP per kept peak walks outwards 32 samples at a time
+  //         (the walk of a high peak crosses most of the signal: one thread per peak took a dependent load per sample) ----
+  for (int k = warp; k < m; k += kPPThreads / 32) {
+    if (state[k] != 1) continue;                                  // (warp-uniform)
     const int pk = cand[k];
     const double h = y[pk];
     double lmin = h, rmin = h;
-    for (int i = pk; i >= 0 && y[i] <= h; --i) lmin = fmin(lmin, y[i]);
-    for (int i = pk; i < T && y[i] <= h; ++i) rmin = fmin(rmin, y[i]);
-    if (!(h - fmax(lmin, rmin) >= prominence)) state[k] = 2;
+    for (int base = pk; base >= 0; base -= 32) {                  // left: i = pk, pk-1, ... while y[i] <= h
+      const int i = base - lane;
+      const double v = (i >= 0) ? y[i] : h;
+      const uint32_t higher = __ballot_sync(0xffffffffu, i >= 0 && v > h);
+      const int stop = higher ? __ffs(higher) - 1 : 32;           // first lane (nearest sample) that is strictly higher
+      lmin = fmin(lmin, warp_min_d(lane < stop ? v : h));
+      if (higher) break;
+    }
+    for (int base = pk; base < T; base += 32) {                   // right
+      const int i = base + lane;
+      const double v = (i < T) ? y[i] : h;
+      const uint32_t higher = __ballot_sync(0xffffffffu, i < T && v > h);
+      const int stop = higher ? __ffs(higher) - 1 : 32;
+      rmin = fmin(rmin, warp_min_d(lane < stop ? v : h));
+      if (higher) break;
+    }
+    if (lane == 0 && !(h - fmax(lmin, rmin) >= prominence)) state[k] = 2;
   }
   __syncthreads();
   const int cseg = (m + kPPThreads - 1) / kPPThreads;
@@ -200,19 +296,41 @@ int op_find_ticks(const double* scores, int n_streams, int T, double prominence,
     g_tables_loaded[dev] = true;
   }
   const int cand_cap = T / 2 + 1;  // strict local maxima are at least 2 samples apart
+  const int leaf_cap = T / 48 + 8; // leaves of numpy's pairwise recursion hold 57 .. 128 elements
+  const size_t base_smem = (size_t)leaf_cap * (sizeof(int) * 2 + sizeof(double));
+  const size_t full_smem = base_smem + (size_t)T * 8 + (size_t)cand_cap * 5 + 16;
+  const bool in_smem = full_smem <= 225 * 1024;
   double* y_ws = nullptr;
   int32_t* cand_ws = nullptr;
   int8_t* state_ws = nullptr;
-  if (!smoothed) AHA_CUDA(cudaMallocAsync(&y_ws, (size_t)n_streams * T * sizeof(double), st));
-  AHA_CUDA(cudaMallocAsync(&cand_ws, (size_t)n_streams * cand_cap * sizeof(int32_t), st));
-  AHA_CUDA(cudaMallocAsync(&state_ws, (size_t)n_streams * cand_cap, st));
-  find_ticks_kernel<<<n_streams, kPPThreads, 0, st>>>(scores, T, prominence, distance, thresh, peaks, max_peaks, n_peaks,
-                                                      smoothed ? smoothed : y_ws, thresh_out, cand_ws, state_ws, cand_cap);
+  if (!in_smem) {
+    if (!smoothed) AHA_CUDA(cudaMallocAsync(&y_ws, (size_t)n_streams * T * sizeof(double), st));
+    AHA_CUDA(cudaMallocAsync(&cand_ws, (size_t)n_streams * cand_cap * sizeof(int32_t), st));
+    AHA_CUDA(cudaMallocAsync(&state_ws, (size_t)n_streams * cand_cap, st));
+    AHA_REQUIRE(base_smem <= 200 * 1024, "find_ticks: signal too long");
+    static bool attr_g[16] = {false};
+    if (dev < 16 && !attr_g[dev]) {
+      AHA_CUDA(cudaFuncSetAttribute(find_ticks_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_g[dev] = true;
+    }
+    find_ticks_kernel<false><<<n_streams, kPPThreads, base_smem, st>>>(scores, T, prominence, distance, thresh, peaks, max_peaks,
+                                                                      n_peaks, smoothed, thresh_out, smoothed ? smoothed : y_ws,
+                                                                      cand_ws, state_ws, cand_cap, leaf_cap);
+  } else {
+    static bool attr_s[16] = {false};
+    if (dev < 16 && !attr_s[dev]) {
+      AHA_CUDA(cudaFuncSetAttribute(find_ticks_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+      attr_s[dev] = true;
+    }
+    find_ticks_kernel<true><<<n_streams, kPPThreads, full_smem, st>>>(scores, T, prominence, distance, thresh, peaks, max_peaks,
+                                                                     n_peaks, smoothed, thresh_out, nullptr, nullptr, nullptr,
+                                                                     cand_cap, leaf_cap);
+  }
   ++g_aha_launch_count;
   cudaError_t e = cudaGetLastError();
   if (y_ws) cudaFreeAsync(y_ws, st);
-  cudaFreeAsync(cand_ws, st);
-  cudaFreeAsync(state_ws, st);
+  if (cand_ws) cudaFreeAsync(cand_ws, st);
+  if (state_ws) cudaFreeAsync(state_ws, st);
   if (e != cudaSuccess) return aha_cuda_fail(e, "find_ticks_kernel", __FILE__, __LINE__);
   return AHA_OK;
 }

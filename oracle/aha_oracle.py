@@ -422,9 +422,23 @@ class PrefillOut:
 
 
 def qwen2_prefill(w: Dict[str, torch.Tensor], dims: AhaDims, cache: OracleKVCache, inputs_embeds: torch.Tensor,
-                  mask_mode: str = "sdpa", want_logits: bool = True, attn_impl: str = "eager") -> PrefillOut:
+                  mask_mode: str = "sdpa", want_logits: bool = True, attn_impl: str = "eager",
+                  lora: Optional[Dict[str, Tuple[torch.Tensor, torch.Tensor, float]]] = None) -> PrefillOut:
     """One chunk [1,q,H] against the cache.  mask_mode 'sdpa': allowed(i,j) <=> j <= L+i (mask sliced to Klen
-    columns); 'fa2': bottom-right aligned causal j <= i + (Klen - q)."""
+    columns); 'fa2': bottom-right aligned causal j <= i + (Klen - q).
+    `lora`: {module name: (A [r, in], B [out, r], alpha / r)} - UNMERGED adapters as the reference runs them through peft
+    (models/modeling_live.py:153-173): y = base(x) + lora_B(lora_A(x)) * scaling, every op in the model dtype."""
+    if lora:
+        _linear = F.linear
+
+        def lin(x_, weight, bias=None):
+            y = _linear(x_, weight, bias)
+            for name, (A_, B_, sc) in lora.items():
+                if w.get(name + ".weight") is weight:
+                    return y + _linear(_linear(x_, A_), B_) * sc
+            return y
+    else:
+        lin = F.linear
     x = inputs_embeds
     dt = x.dtype
     q = x.shape[1]
@@ -437,9 +451,9 @@ def qwen2_prefill(w: Dict[str, torch.Tensor], dims: AhaDims, cache: OracleKVCach
         p = f"model.layers.{li}."
         res = x
         h = rms_norm(x, w[p + "input_layernorm.weight"], dims.rms_eps)
-        qs = F.linear(h, w[p + "self_attn.q_proj.weight"], w[p + "self_attn.q_proj.bias"]).view(1, q, nh, d).transpose(1, 2)
-        ks = F.linear(h, w[p + "self_attn.k_proj.weight"], w[p + "self_attn.k_proj.bias"]).view(1, q, nkv, d).transpose(1, 2)
-        vs = F.linear(h, w[p + "self_attn.v_proj.weight"], w[p + "self_attn.v_proj.bias"]).view(1, q, nkv, d).transpose(1, 2)
+        qs = lin(h, w[p + "self_attn.q_proj.weight"], w[p + "self_attn.q_proj.bias"]).view(1, q, nh, d).transpose(1, 2)
+        ks = lin(h, w[p + "self_attn.k_proj.weight"], w[p + "self_attn.k_proj.bias"]).view(1, q, nkv, d).transpose(1, 2)
+        vs = lin(h, w[p + "self_attn.v_proj.weight"], w[p + "self_attn.v_proj.bias"]).view(1, q, nkv, d).transpose(1, 2)
         c, s = cos[:, None], sin[:, None]
         qs = (qs * c) + (rotate_half(qs) * s)
         ks = (ks * c) + (rotate_half(ks) * s)
@@ -461,10 +475,10 @@ def qwen2_prefill(w: Dict[str, torch.Tensor], dims: AhaDims, cache: OracleKVCach
             a = F.softmax(a, dim=-1, dtype=torch.float32).to(dt)
             o = torch.matmul(a, Vr)
         o = o.transpose(1, 2).reshape(1, q, nh * d)
-        x = res + F.linear(o, w[p + "self_attn.o_proj.weight"])
+        x = res + lin(o, w[p + "self_attn.o_proj.weight"])
         res = x
         h = rms_norm(x, w[p + "post_attention_layernorm.weight"], dims.rms_eps)
-        h = F.linear(F.silu(F.linear(h, w[p + "mlp.gate_proj.weight"])) * F.linear(h, w[p + "mlp.up_proj.weight"]),
+        h = lin(F.silu(lin(h, w[p + "mlp.gate_proj.weight"])) * lin(h, w[p + "mlp.up_proj.weight"]),
                      w[p + "mlp.down_proj.weight"])
         x = res + h
     x = rms_norm(x, w["model.norm.weight"], dims.rms_eps)

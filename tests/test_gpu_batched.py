@@ -275,3 +275,42 @@ def test_stream_group_equals_separate_drivers(cuda):
             d = np.abs(np.array([r[key] for r in a]) - np.array([r[key] for r in b])).max()
             assert d <= 2e-2, (s, key, d)
         assert torch.equal(lives[s].past_key_values.provenance(0), sep[s][0].past_key_values.provenance(0))
+
+
+def test_lora_merged_engine_equals_unmerged_oracle(cuda):
+    """N2 (models/modeling_live.py:153-173): the reference runs its r = 16 / alpha = 32 adapters UNMERGED through peft on
+    q/k/v/o/gate/up/down of every decoder layer; the engine streams one folded matrix per projection
+    (merge_lora_state_dict).  Merged engine against the oracle running the unmerged adapters, through a stream that
+    evicts and re-rotates."""
+    from oracle import aha_oracle as o
+    dims, cfg = o.dims_preset("micro72"), A.config_preset("micro72")
+    w = o.init_weights(dims, seed=4, dtype=torch.bfloat16)
+    g = torch.Generator().manual_seed(8)
+    adapter, lora = {}, {}
+    r, alpha = 16, 32.0
+    for li in range(dims.layers):
+        for mod in ("self_attn.q_proj", "self_attn.k_proj", "self_attn.v_proj", "self_attn.o_proj", "mlp.gate_proj",
+                    "mlp.up_proj", "mlp.down_proj"):
+            name = f"model.layers.{li}.{mod}"
+            out_f, in_f = w[name + ".weight"].shape
+            A_ = (torch.randn(r, in_f, generator=g) * 0.05).bfloat16()
+            B_ = (torch.randn(out_f, r, generator=g) * 0.05).bfloat16()
+            adapter[f"base_model.model.{name}.lora_A.default.weight"] = A_
+            adapter[f"base_model.model.{name}.lora_B.default.weight"] = B_
+            lora[name] = (A_, B_, alpha / r)
+    merged = A.merge_lora_state_dict(w, adapter, lora_alpha=alpha, r=r)
+    assert not torch.equal(merged["model.layers.0.mlp.down_proj.weight"], w["model.layers.0.mlp.down_proj.weight"])
+    model = A.VideoHeadLiveLlavaQwenForCausalLM(cfg, merged, device=cuda, max_tokens=64, max_frames=2, logits_mode="none")
+    q, W, S = cfg.frame_num_tokens, 40, 4
+    cache = model.new_cache("default_sink", W, S, max_chunk=32)
+    ref_c = o.make_cache("default_sink", W, S)
+    torch.manual_seed(12)
+    for t in range(8):
+        x = (torch.randn(1, q + (3 if t == 0 else 0), cfg.hidden_size) * 0.5).bfloat16()
+        out = model(inputs_embeds=x.to(cuda), past_key_values=cache)
+        ref = o.frame_scores(o.qwen2_prefill(w, dims, ref_c, x, want_logits=False, lora=lora))
+        got = out.frame_scores[0].float().cpu().numpy()
+        assert cache.get_seq_length() == ref_c.get_seq_length()
+        assert abs(got[0] - ref[0]) <= 2e-2 and abs(got[1] - ref[1]) <= 2e-2, (t, got, ref)
+        assert abs(np.log(got[2]) - np.log(ref[2])) <= 3e-2, (t, got, ref)
+    assert torch.equal(cache.provenance(0).cpu().long(), ref_c.ids[0])
