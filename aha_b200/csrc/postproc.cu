@@ -108,6 +108,11 @@ __device__ __forceinline__ double warp_min_d(double v) {
 // kSmem: the smoothed signal, the candidate list and its state live in shared memory (T up to ~21 000 samples); otherwise
 // in the per-stream global workspaces.  Algorithmic bytes per stream: T * 8 read, the peak list written.
 template <bool kSmem>
+struct PPIdx { typedef int32_t type; };
+template <>
+struct PPIdx<true> { typedef uint16_t type; };
+
+template <bool kSmem>
 __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __restrict__ scores, int T, double prominence,
                                                                int distance, const double* __restrict__ thresh_in,
                                                                int32_t* __restrict__ peaks_out, int max_peaks,
@@ -117,7 +122,6 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
                                                                int cand_cap, int leaf_cap) {
   extern __shared__ __align__(16) uint8_t pp_smem[];
   __shared__ int sh_i[kPPThreads / 32];
-  __shared__ int sh_flag;
   __shared__ int sh_nleaves;
   __shared__ double sh_val;
   const int s = blockIdx.x;
@@ -127,8 +131,13 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   double* leaf_sums = reinterpret_cast<double*>(pp_smem + (size_t)leaf_cap * sizeof(PwLeaf));
   uint8_t* after = reinterpret_cast<uint8_t*>(leaf_sums + leaf_cap);
   double* y = kSmem ? reinterpret_cast<double*>(after) : y_ws + (size_t)s * T;
-  int32_t* cand = kSmem ? reinterpret_cast<int32_t*>(after + (size_t)T * 8) : cand_ws + (size_t)s * cand_cap;
-  int8_t* state = kSmem ? reinterpret_cast<int8_t*>(after + (size_t)T * 8 + (size_t)cand_cap * 4) : state_ws + (size_t)s * cand_cap;
+  // candidate positions and their height order: 16-bit in shared memory (T < 32768 there), 32-bit in the global fallback
+  typedef typename PPIdx<kSmem>::type idx_t;
+  idx_t* cand = kSmem ? reinterpret_cast<idx_t*>(after + (size_t)T * 8)
+                      : reinterpret_cast<idx_t*>(cand_ws + (size_t)s * 2 * cand_cap);
+  idx_t* ord = cand + cand_cap;
+  int8_t* state = kSmem ? reinterpret_cast<int8_t*>(after + (size_t)T * 8 + (size_t)cand_cap * 2 * sizeof(idx_t))
+                        : state_ws + (size_t)s * cand_cap;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // ---- A. Savitzky-Golay(15, 3), mode='interp' ----
@@ -192,7 +201,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
           const int pk = (i + a - 1) / 2;
           if (y[pk] >= th) {
             if (pass == 0) ++cnt;
-            else { if (wr < cand_cap) { cand[wr] = pk; state[wr] = 0; } ++wr; }
+            else { if (wr < cand_cap) { cand[wr] = (idx_t)pk; state[wr] = 1; } ++wr; }
           }
         }
       }
@@ -202,41 +211,31 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   __syncthreads();
   const int m = min(cnt, cand_cap);
 
-  // ---- D. distance: parallel fixed point of the greedy highest-first suppression ----
+  // ---- D. distance (scipy _select_by_peak_distance): peaks are visited from the highest down, a visited peak that is
+  //         still kept removes every peak closer than `distance`.  The visiting order comes from a rank count (m^2 / 256
+  //         comparisons per thread; equal heights: the larger index first), the greedy pass itself is sequential - a few
+  //         hundred steps on shared memory.  (The first version iterated a parallel fixed point: one round per link of the
+  //         longest chain of ever higher neighbours, a hundred rounds of four barriers on a noisy slope.) ----
   if (distance > 1) {
-    for (int round = 0; round < m + 1; ++round) {
-      if (tid == 0) sh_flag = 0;
-      __syncthreads();
-      // phase 1: undecided peaks that dominate their undecided neighbourhood become kept (state 3 = kept this round)
-      for (int k = tid; k < m; k += kPPThreads) {
-        if (state[k] != 0) continue;
-        const int pk = cand[k];
-        const double hk = y[pk];
-        bool dominated = false;
-        for (int j = k - 1; j >= 0 && pk - cand[j] < distance; --j)
-          if ((state[j] == 0 || state[j] == 3) && (y[cand[j]] > hk)) { dominated = true; break; }          // equal height: larger index wins
-        for (int j = k + 1; !dominated && j < m && cand[j] - pk < distance; ++j)
-          if ((state[j] == 0 || state[j] == 3) && (y[cand[j]] >= hk)) dominated = true;
-        if (!dominated) state[k] = 3;
+    for (int k = tid; k < m; k += kPPThreads) {
+      const double hk = y[cand[k]];
+      int rank = 0;
+      for (int j = 0; j < m; ++j) {
+        const double hj = y[cand[j]];
+        rank += (hj > hk) || (hj == hk && j > k);
       }
-      __syncthreads();
-      // phase 2: drop undecided peaks within `distance` of a peak kept this round
-      for (int k = tid; k < m; k += kPPThreads) {
-        if (state[k] != 0) continue;
-        const int pk = cand[k];
-        bool drop = false;
-        for (int j = k - 1; j >= 0 && pk - cand[j] < distance; --j) if (state[j] == 3) { drop = true; break; }
-        for (int j = k + 1; !drop && j < m && cand[j] - pk < distance; ++j) if (state[j] == 3) drop = true;
-        if (drop) state[k] = 2; else sh_flag = 1;
-      }
-      __syncthreads();
-      for (int k = tid; k < m; k += kPPThreads) if (state[k] == 3) state[k] = 1;
-      const int again = sh_flag;
-      __syncthreads();
-      if (!again) break;
+      ord[rank] = (idx_t)k;
     }
-  } else {
-    for (int k = tid; k < m; k += kPPThreads) state[k] = 1;
+    __syncthreads();
+    if (tid == 0) {
+      for (int r = 0; r < m; ++r) {
+        const int j = ord[r];
+        if (state[j] != 1) continue;
+        const int pj = cand[j];
+        for (int k = j - 1; k >= 0 && pj - (int)cand[k] < distance; --k) state[k] = 2;
+        for (int k = j + 1; k < m && (int)cand[k] - pj < distance; ++k) state[k] = 2;
+      }
+    }
     __syncthreads();
   }
 
@@ -273,7 +272,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   int total = 0;
   int wr = block_exscan(mine, sh_i, &total);
   for (int k = k0; k < k1; ++k)
-    if (state[k] == 1) { if (wr < max_peaks) peaks_out[(size_t)s * max_peaks + wr] = cand[k]; ++wr; }
+    if (state[k] == 1) { if (wr < max_peaks) peaks_out[(size_t)s * max_peaks + wr] = (int32_t)cand[k]; ++wr; }
   if (tid == 0) n_peaks[s] = (cnt > cand_cap) ? 0x7fffffff : total;
 }
 
@@ -298,14 +297,14 @@ int op_find_ticks(const double* scores, int n_streams, int T, double prominence,
   const int cand_cap = T / 2 + 1;  // strict local maxima are at least 2 samples apart
   const int leaf_cap = T / 48 + 8; // leaves of numpy's pairwise recursion hold 57 .. 128 elements
   const size_t base_smem = (size_t)leaf_cap * (sizeof(int) * 2 + sizeof(double));
-  const size_t full_smem = base_smem + (size_t)T * 8 + (size_t)cand_cap * 5 + 16;
-  const bool in_smem = full_smem <= 225 * 1024;
+  const size_t full_smem = base_smem + (size_t)T * 8 + (size_t)cand_cap * 5 + 16;      // y, cand + ord (16-bit), state
+  const bool in_smem = full_smem <= 225 * 1024 && T < 32768;
   double* y_ws = nullptr;
   int32_t* cand_ws = nullptr;
   int8_t* state_ws = nullptr;
   if (!in_smem) {
     if (!smoothed) AHA_CUDA(cudaMallocAsync(&y_ws, (size_t)n_streams * T * sizeof(double), st));
-    AHA_CUDA(cudaMallocAsync(&cand_ws, (size_t)n_streams * cand_cap * sizeof(int32_t), st));
+    AHA_CUDA(cudaMallocAsync(&cand_ws, (size_t)n_streams * 2 * cand_cap * sizeof(int32_t), st));     // positions + height order
     AHA_CUDA(cudaMallocAsync(&state_ws, (size_t)n_streams * cand_cap, st));
     AHA_REQUIRE(base_smem <= 200 * 1024, "find_ticks: signal too long");
     static bool attr_g[16] = {false};
