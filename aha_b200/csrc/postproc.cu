@@ -12,6 +12,8 @@
 //   within `distance` of a kept peak is dropped, until nothing is undecided) -> prominence over the full signal.
 #include "ops.h"
 #include "savgol_tables.h"
+#include <cstdio>
+#include <cstdlib>
 
 namespace {
 
@@ -99,9 +101,24 @@ __device__ double pw_combine(const double* leaf_sums, int n, int* next_leaf) {
   return __dadd_rn(a, b);
 }
 
-__device__ __forceinline__ double warp_min_d(double v) {
+// IEEE doubles ordered as unsigned 64-bit integers (sign bit flipped for non-negative values, all bits for negative ones):
+// every comparison of the peak logic runs on these keys - the FP64 pipe of the B200's CUDA cores issues a warp instruction
+// only every ~16 cycles per scheduler (measured: the all-double version of this kernel was bound by DSETP / DMNMX / DADD
+// issue, 0.4 ms per 10 000-sample stream), 64-bit integer compares cost two ALU instructions.
+__device__ __forceinline__ unsigned long long dkey(double v) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dkey_inv(unsigned long long k) {
+  const unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+  return __longlong_as_double((long long)b);
+}
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long w = __shfl_xor_sync(0xffffffffu, v, o);
+    v = w < v ? w : v;
+  }
   return v;
 }
 
@@ -119,7 +136,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
                                                                int32_t* __restrict__ n_peaks, double* __restrict__ smoothed,
                                                                double* __restrict__ thresh_out, double* __restrict__ y_ws,
                                                                int32_t* __restrict__ cand_ws, int8_t* __restrict__ state_ws,
-                                                               int cand_cap, int leaf_cap) {
+                                                               int cand_cap, int leaf_cap, int dbg) {
   extern __shared__ __align__(16) uint8_t pp_smem[];
   __shared__ int sh_i[kPPThreads / 32];
   __shared__ int sh_nleaves;
@@ -139,6 +156,8 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   int8_t* state = kSmem ? reinterpret_cast<int8_t*>(after + (size_t)T * 8 + (size_t)cand_cap * 2 * sizeof(idx_t))
                         : state_ws + (size_t)s * cand_cap;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  long long t_[8];      // bring-up (AHA_PP_DBG=1): stage stamps of block 0
+  t_[0] = clock64();
 
   // ---- A. Savitzky-Golay(15, 3), mode='interp' ----
   for (int i = tid; i < T; i += kPPThreads) {
@@ -162,6 +181,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   if (tid == 0) sh_nleaves = pw_build_leaves(T, leaves, leaf_cap);
   __syncthreads();
 
+  t_[1] = clock64();
   // ---- B. threshold = mean + 0.5 * std (ddof = 0) of the smoothed signal, in numpy's summation order ----
   double th;
   const bool auto_thresh = (thresh_in == nullptr) || isnan(thresh_in[s]);
@@ -186,6 +206,14 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   }
   if (tid == 0 && thresh_out) thresh_out[s] = th;
 
+  __syncthreads();
+  // from here on the signal is only compared: keep it as orderable integer keys (in place; -0.0 == +0.0 is the one
+  // equality the keys would miss, so zeros are normalised)
+  unsigned long long* yk = reinterpret_cast<unsigned long long*>(y);
+  for (int i = tid; i < T; i += kPPThreads) { const double v = y[i]; yk[i] = dkey(v == 0.0 ? 0.0 : v); }
+  const unsigned long long thk = dkey(th == 0.0 ? 0.0 : th);
+  __syncthreads();
+  t_[2] = clock64();
   // ---- C. strict local maxima with plateau midpoints, filtered by height, compacted in position order ----
   const int seg = (T + kPPThreads - 1) / kPPThreads;
   const int i0 = max(1, tid * seg), i1 = min(T - 1, (tid + 1) * seg);
@@ -194,12 +222,12 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
     int wr = 0, total = 0;
     if (pass == 1) wr = block_exscan(cnt, sh_i, &total);
     for (int i = i0; i < i1; ++i) {
-      if (y[i - 1] < y[i]) {
+      if (yk[i - 1] < yk[i]) {
         int a = i + 1;
-        while (a < T - 1 && y[a] == y[i]) ++a;
-        if (y[a] < y[i]) {
+        while (a < T - 1 && yk[a] == yk[i]) ++a;
+        if (yk[a] < yk[i]) {
           const int pk = (i + a - 1) / 2;
-          if (y[pk] >= th) {
+          if (yk[pk] >= thk) {
             if (pass == 0) ++cnt;
             else { if (wr < cand_cap) { cand[wr] = (idx_t)pk; state[wr] = 1; } ++wr; }
           }
@@ -211,6 +239,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   __syncthreads();
   const int m = min(cnt, cand_cap);
 
+  t_[3] = clock64();
   // ---- D. distance (scipy _select_by_peak_distance): peaks are visited from the highest down, a visited peak that is
   //         still kept removes every peak closer than `distance`.  The visiting order comes from a rank count (m^2 / 256
   //         comparisons per thread; equal heights: the larger index first), the greedy pass itself is sequential - a few
@@ -218,53 +247,70 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   //         longest chain of ever higher neighbours, a hundred rounds of four barriers on a noisy slope.) ----
   if (distance > 1) {
     for (int k = tid; k < m; k += kPPThreads) {
-      const double hk = y[cand[k]];
+      const unsigned long long hk = yk[cand[k]];
       int rank = 0;
       for (int j = 0; j < m; ++j) {
-        const double hj = y[cand[j]];
+        const unsigned long long hj = yk[cand[j]];
         rank += (hj > hk) || (hj == hk && j > k);
       }
       ord[rank] = (idx_t)k;
     }
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0) {
+      // the greedy pass, one warp: the lanes clear the neighbours of a kept peak 32 at a time
       for (int r = 0; r < m; ++r) {
         const int j = ord[r];
-        if (state[j] != 1) continue;
+        if (state[j] != 1) continue;                               // (warp-uniform: shared memory, ordered by __syncwarp)
         const int pj = cand[j];
-        for (int k = j - 1; k >= 0 && pj - (int)cand[k] < distance; --k) state[k] = 2;
-        for (int k = j + 1; k < m && (int)cand[k] - pj < distance; ++k) state[k] = 2;
+        for (int k0 = j - 1; k0 >= 0; k0 -= 32) {
+          const int k = k0 - lane;
+          const bool in = k >= 0 && pj - (int)cand[k] < distance;
+          if (in) state[k] = 2;
+          if (!__all_sync(0xffffffffu, in)) break;
+        }
+        for (int k0 = j + 1; k0 < m; k0 += 32) {
+          const int k = k0 + lane;
+          const bool in = k < m && (int)cand[k] - pj < distance;
+          if (in) state[k] = 2;
+          if (!__all_sync(0xffffffffu, in)) break;
+        }
+        __syncwarp();
       }
     }
     __syncthreads();
   }
 
+  t_[4] = clock64();
   // ---- E. prominence over the full signal (wlen=None): one WARP per kept peak walks outwards 32 samples at a time
   //         (the walk of a high peak crosses most of the signal: one thread per peak took a dependent load per sample) ----
   for (int k = warp; k < m; k += kPPThreads / 32) {
     if (state[k] != 1) continue;                                  // (warp-uniform)
     const int pk = cand[k];
-    const double h = y[pk];
-    double lmin = h, rmin = h;
+    const unsigned long long h = yk[pk];
+    unsigned long long lmin = h, rmin = h;
     for (int base = pk; base >= 0; base -= 32) {                  // left: i = pk, pk-1, ... while y[i] <= h
       const int i = base - lane;
-      const double v = (i >= 0) ? y[i] : h;
+      const unsigned long long v = (i >= 0) ? yk[i] : h;
       const uint32_t higher = __ballot_sync(0xffffffffu, i >= 0 && v > h);
       const int stop = higher ? __ffs(higher) - 1 : 32;           // first lane (nearest sample) that is strictly higher
-      lmin = fmin(lmin, warp_min_d(lane < stop ? v : h));
+      const unsigned long long mn = warp_min_u64(lane < stop ? v : h);
+      lmin = mn < lmin ? mn : lmin;
       if (higher) break;
     }
     for (int base = pk; base < T; base += 32) {                   // right
       const int i = base + lane;
-      const double v = (i < T) ? y[i] : h;
+      const unsigned long long v = (i < T) ? yk[i] : h;
       const uint32_t higher = __ballot_sync(0xffffffffu, i < T && v > h);
       const int stop = higher ? __ffs(higher) - 1 : 32;
-      rmin = fmin(rmin, warp_min_d(lane < stop ? v : h));
+      const unsigned long long mn = warp_min_u64(lane < stop ? v : h);
+      rmin = mn < rmin ? mn : rmin;
       if (higher) break;
     }
-    if (lane == 0 && !(h - fmax(lmin, rmin) >= prominence)) state[k] = 2;
+    // scipy: prominence = x[peak] - max(left_min, right_min), kept if >= the bound (one double subtraction per peak)
+    if (lane == 0 && !(__dsub_rn(dkey_inv(h), dkey_inv(lmin > rmin ? lmin : rmin)) >= prominence)) state[k] = 2;
   }
   __syncthreads();
+  t_[5] = clock64();
   const int cseg = (m + kPPThreads - 1) / kPPThreads;
   const int k0 = min(m, tid * cseg), k1 = min(m, (tid + 1) * cseg);
   int mine = 0;
@@ -274,6 +320,13 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   for (int k = k0; k < k1; ++k)
     if (state[k] == 1) { if (wr < max_peaks) peaks_out[(size_t)s * max_peaks + wr] = (int32_t)cand[k]; ++wr; }
   if (tid == 0) n_peaks[s] = (cnt > cand_cap) ? 0x7fffffff : total;
+  if (!kSmem && smoothed) {      // (the global path kept the signal in the caller's `smoothed` buffer: back to doubles)
+    __syncthreads();
+    for (int i = tid; i < T; i += kPPThreads) y[i] = dkey_inv(yk[i]);
+  }
+  if (dbg && tid == 0 && s == 0)
+    printf("find_ticks block 0: m=%d kept=%d cycles A %lld B %lld C %lld D %lld E %lld F %lld\n", m, total, t_[1] - t_[0], t_[2] - t_[1],
+           t_[3] - t_[2], t_[4] - t_[3], t_[5] - t_[4], clock64() - t_[5]);
 }
 
 bool g_tables_loaded[16] = {false};
@@ -294,6 +347,7 @@ int op_find_ticks(const double* scores, int n_streams, int T, double prominence,
     AHA_CUDA(cudaMemcpyToSymbol(cTail, kSavgolTail, sizeof(kSavgolTail)));
     g_tables_loaded[dev] = true;
   }
+  static const int dbg = getenv("AHA_PP_DBG") ? atoi(getenv("AHA_PP_DBG")) : 0;
   const int cand_cap = T / 2 + 1;  // strict local maxima are at least 2 samples apart
   const int leaf_cap = T / 48 + 8; // leaves of numpy's pairwise recursion hold 57 .. 128 elements
   const size_t base_smem = (size_t)leaf_cap * (sizeof(int) * 2 + sizeof(double));
@@ -314,7 +368,7 @@ int op_find_ticks(const double* scores, int n_streams, int T, double prominence,
     }
     find_ticks_kernel<false><<<n_streams, kPPThreads, base_smem, st>>>(scores, T, prominence, distance, thresh, peaks, max_peaks,
                                                                       n_peaks, smoothed, thresh_out, smoothed ? smoothed : y_ws,
-                                                                      cand_ws, state_ws, cand_cap, leaf_cap);
+                                                                      cand_ws, state_ws, cand_cap, leaf_cap, dbg);
   } else {
     static bool attr_s[16] = {false};
     if (dev < 16 && !attr_s[dev]) {
@@ -323,7 +377,7 @@ int op_find_ticks(const double* scores, int n_streams, int T, double prominence,
     }
     find_ticks_kernel<true><<<n_streams, kPPThreads, full_smem, st>>>(scores, T, prominence, distance, thresh, peaks, max_peaks,
                                                                      n_peaks, smoothed, thresh_out, nullptr, nullptr, nullptr,
-                                                                     cand_cap, leaf_cap);
+                                                                     cand_cap, leaf_cap, dbg);
   }
   ++g_aha_launch_count;
   cudaError_t e = cudaGetLastError();
