@@ -69,6 +69,30 @@ __device__ __forceinline__ double pw_elem(const double* y, int i, double mean) {
   return __dmul_rn(d, d);
 }
 
+// The same leaf sum by EIGHT lanes (lane j of the group owns accumulator r[j] of numpy's unrolled loop, i.e. the elements
+// j, j + 8, ...): consecutive lanes read consecutive elements (one thread per leaf walked 1 KB apart: a 32-way bank
+// conflict) and the dependent chain is 16 additions instead of 128.  Result in every lane of the group.
+template <bool kCentered>
+__device__ __forceinline__ double pw_leaf_sum8(const double* y, PwLeaf lf, double mean, int sub) {
+  const int o = lf.start, n = lf.len;
+  double res;
+  if (n < 8) {
+    res = 0.0;
+    for (int i = 0; i < n; ++i) res = __dadd_rn(res, pw_elem<kCentered>(y, o + i, mean));
+    return res;
+  }
+  const int n8 = n - (n % 8);
+  double r = pw_elem<kCentered>(y, o + sub, mean);
+  for (int i = 8 + sub; i < n8; i += 8) r = __dadd_rn(r, pw_elem<kCentered>(y, o + i, mean));
+  // ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7)): xor-butterfly over the 8 lanes adds exactly these pairs
+  r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 1));
+  r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 2));
+  r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 4));
+  res = r;
+  for (int i = n8; i < n; ++i) res = __dadd_rn(res, pw_elem<kCentered>(y, o + i, mean));
+  return res;
+}
+
 template <bool kCentered>
 __device__ double pw_leaf_sum(const double* y, PwLeaf lf, double mean) {
   const double* a = y;
@@ -187,12 +211,21 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   const bool auto_thresh = (thresh_in == nullptr) || isnan(thresh_in[s]);
   if (auto_thresh) {
     const int nl = min(sh_nleaves, leaf_cap);
-    for (int l = tid; l < nl; l += kPPThreads) leaf_sums[l] = pw_leaf_sum<false>(y, leaves[l], 0.0);
+    // (all 32 lanes of a warp run the same trip count: the leaf index is clamped, surplus groups do not store)
+    for (int l0 = 0; l0 < nl; l0 += kPPThreads / 8) {
+      const int l = l0 + (tid >> 3);
+      const double v = pw_leaf_sum8<false>(y, leaves[min(l, nl - 1)], 0.0, tid & 7);
+      if (l < nl && (tid & 7) == 0) leaf_sums[l] = v;
+    }
     __syncthreads();
     if (tid == 0) { int nx = 0; sh_val = __ddiv_rn(pw_combine(leaf_sums, T, &nx), (double)T); }
     __syncthreads();
     const double mean = sh_val;
-    for (int l = tid; l < nl; l += kPPThreads) leaf_sums[l] = pw_leaf_sum<true>(y, leaves[l], mean);
+    for (int l0 = 0; l0 < nl; l0 += kPPThreads / 8) {
+      const int l = l0 + (tid >> 3);
+      const double v = pw_leaf_sum8<true>(y, leaves[min(l, nl - 1)], mean, tid & 7);
+      if (l < nl && (tid & 7) == 0) leaf_sums[l] = v;
+    }
     __syncthreads();
     if (tid == 0) {
       int nx = 0;
@@ -215,7 +248,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
   __syncthreads();
   t_[2] = clock64();
   // ---- C. strict local maxima with plateau midpoints, filtered by height, compacted in position order ----
-  const int seg = (T + kPPThreads - 1) / kPPThreads;
+  const int seg = ((T + kPPThreads - 1) / kPPThreads) | 1;   // odd: the lanes' 8-byte reads then fall into distinct banks
   const int i0 = max(1, tid * seg), i1 = min(T - 1, (tid + 1) * seg);
   int cnt = 0;
   for (int pass = 0; pass < 2; ++pass) {
