@@ -170,9 +170,22 @@ class _NativeCache(Cache):
         return self._export(int(layer_idx))
 
 
+class _SlidingFlag(list):
+    """`is_sliding = True` of the reference's SinkCache (test/sink_cache.py:8) in a form transformers >= 4.54 can also
+    consume: there `Cache.is_sliding` is a per-layer list that the mask builder searches (`False in cache.is_sliding`)."""
+
+    def __init__(self):
+        super().__init__([True])
+
+    def __eq__(self, other):
+        return other is True or list.__eq__(self, other)
+
+    __hash__ = None
+
+
 class SinkCache(_NativeCache):
     """test/sink_cache.py:7-164."""
-    is_sliding = True
+    is_sliding = _SlidingFlag()
     _policy = _lib.POLICY_SINK
 
     def __init__(self, window_length: int, num_sink_tokens: int, num_layers: int = 0, max_chunk: Optional[int] = None) -> None:

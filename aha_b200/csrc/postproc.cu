@@ -93,36 +93,25 @@ __device__ __forceinline__ double pw_leaf_sum8(const double* y, PwLeaf lf, doubl
   return res;
 }
 
-template <bool kCentered>
-__device__ double pw_leaf_sum(const double* y, PwLeaf lf, double mean) {
-  const double* a = y;
-  const int o = lf.start, n = lf.len;
-  if (n < 8) {
-    double res = 0.0;
-    for (int i = 0; i < n; ++i) res = __dadd_rn(res, pw_elem<kCentered>(a, o + i, mean));
-    return res;
+// adds the leaf sums in the recursion's order (one thread): same splitting rule, leaves consumed left to right.  Iterative
+// (explicit node and value stacks): the recursive form cost ~250 cycles per call in local-memory frames.
+__device__ double pw_combine(const double* leaf_sums, int n) {
+  int node_n[64];
+  unsigned char node_post[64];
+  double val[64];
+  int sp = 0, vp = 0, li = 0;
+  node_n[0] = n; node_post[0] = 0; sp = 1;
+  while (sp > 0) {
+    --sp;
+    const int ln = node_n[sp];
+    if (node_post[sp]) { const double b = val[--vp]; const double a = val[--vp]; val[vp++] = __dadd_rn(a, b); continue; }
+    if (ln <= 128) { val[vp++] = leaf_sums[li++]; continue; }
+    int n2 = ln / 2; n2 -= n2 % 8;
+    node_n[sp] = ln; node_post[sp] = 1; ++sp;            // add the two halves once both are on the value stack
+    node_n[sp] = ln - n2; node_post[sp] = 0; ++sp;       // right half (popped second)
+    node_n[sp] = n2; node_post[sp] = 0; ++sp;            // left half (popped first)
   }
-  double r[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) r[j] = pw_elem<kCentered>(a, o + j, mean);
-  int i = 8;
-  for (; i < n - (n % 8); i += 8) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], pw_elem<kCentered>(a, o + i + j, mean));
-  }
-  double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
-                         __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
-  for (; i < n; ++i) res = __dadd_rn(res, pw_elem<kCentered>(a, o + i, mean));
-  return res;
-}
-
-// adds the leaf sums in the recursion's order (one thread): same splitting rule, leaves consumed left to right
-__device__ double pw_combine(const double* leaf_sums, int n, int* next_leaf) {
-  if (n <= 128) return leaf_sums[(*next_leaf)++];
-  int n2 = n / 2; n2 -= n2 % 8;
-  const double a = pw_combine(leaf_sums, n2, next_leaf);
-  const double b = pw_combine(leaf_sums, n - n2, next_leaf);
-  return __dadd_rn(a, b);
+  return val[0];
 }
 
 // IEEE doubles ordered as unsigned 64-bit integers (sign bit flipped for non-negative values, all bits for negative ones):
@@ -218,7 +207,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
       if (l < nl && (tid & 7) == 0) leaf_sums[l] = v;
     }
     __syncthreads();
-    if (tid == 0) { int nx = 0; sh_val = __ddiv_rn(pw_combine(leaf_sums, T, &nx), (double)T); }
+    if (tid == 0) sh_val = __ddiv_rn(pw_combine(leaf_sums, T), (double)T);
     __syncthreads();
     const double mean = sh_val;
     for (int l0 = 0; l0 < nl; l0 += kPPThreads / 8) {
@@ -228,8 +217,7 @@ __global__ void __launch_bounds__(kPPThreads) find_ticks_kernel(const double* __
     }
     __syncthreads();
     if (tid == 0) {
-      int nx = 0;
-      const double var = __ddiv_rn(pw_combine(leaf_sums, T, &nx), (double)T);
+      const double var = __ddiv_rn(pw_combine(leaf_sums, T), (double)T);
       sh_val = __dadd_rn(mean, __dmul_rn(0.5, sqrt(var)));
     }
     __syncthreads();

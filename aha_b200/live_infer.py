@@ -41,7 +41,54 @@ def round_numbers(data, n):
 
 
 class LiveInferForBenchmark:
-    def __init__(self, model: VideoHeadLiveLlavaQwenForCausalLM, start_ids: torch.Tensor,
+    def __init__(self, model_or_args, *args, **kwargs):
+        """Two constructor forms:
+          LiveInferForBenchmark(model, start_ids, ...)                                  an engine handle + prompt ids
+          LiveInferForBenchmark(args, peft_model_id=None, sink_cache=False, alt_cache="default_sink")
+                                                                                        the reference's own signature
+        (test/inference.py:39): `args` is a LiveTestArguments-like object (models/arguments_live.py:40-75); the model and
+        the tokenizer come from aha_b200.build_model_and_tokenizer(**asdict(args)), extra keyword arguments
+        (state_dict=, config=, tokenizer=, device=, max_tokens= ...) are passed through to it."""
+        if isinstance(model_or_args, VideoHeadLiveLlavaQwenForCausalLM):
+            self._init_native(model_or_args, *args, **kwargs)
+        else:
+            self._init_from_args(model_or_args, *args, **kwargs)
+
+    def _init_from_args(self, args, peft_model_id=None, sink_cache=False, alt_cache="default_sink", **build_kw):
+        import dataclasses
+        from .compat import build_model_and_tokenizer
+        kw = dataclasses.asdict(args) if dataclasses.is_dataclass(args) else dict(vars(args))
+        assert not (kw.get("bf16") and kw.get("fp16")), "only one of --bf16 true and --fp16 true can be set"
+        kw = {k: v for k, v in kw.items() if k in ("llm_pretrained", "lora_pretrained", "lora_alpha", "lora_r",
+                                                     "attn_implementation", "video_pooling_stride", "frame_resolution")}
+        kw.update(build_kw)
+        if peft_model_id and os.path.isdir(str(peft_model_id)) and not kw.get("lora_pretrained"):
+            kw["lora_pretrained"] = peft_model_id
+        self.peft_model_id = peft_model_id
+        model, self.tokenizer = build_model_and_tokenizer(is_training=False, set_vision_inside=True,
+                                                          torch_dtype=torch.bfloat16, **kw)
+        self.image_processor = model.get_vision_tower().image_processor
+        g = lambda name, default=None: getattr(args, name, default)
+        self.system_prompt = g("system_prompt", "")
+        thr = (g("threshold_z"), g("stream_end_prob_threshold"), g("stream_end_score_sum_threshold"))
+        if sum(t is not None for t in thr) != 1:          # test/inference.py:84-85
+            raise ValueError("only one of --stream_end_prob_threshold, --threshold_z and --stream_end_score_sum_threshold "
+                             f"can be set. However, they are: {thr[1]}, {thr[0]}, {thr[2]}")
+        tok, dev = self.tokenizer, model.device
+        start_ids = tok.apply_chat_template([{'role': 'system', 'content': self.system_prompt}], return_tensors='pt').to(dev)
+        stream_ids = tok.apply_chat_template([{}], add_stream_prompt=True, return_tensors='pt').to(dev)
+        gen_ids = tok.apply_chat_template([{}], add_stream_generation_prompt=True, return_tensors='pt').to(dev)
+        heads = g("score_heads", "relevance_score,informative_score")
+        self._init_native(model, start_ids, added_stream_prompt_ids=stream_ids, sink_cache=sink_cache, alt_cache=alt_cache,
+                          frame_fps=g("frame_fps", 2) if g("frame_fps", 2) > 0 else 2.0,
+                          score_heads=heads.split(',') if isinstance(heads, str) else heads,
+                          stream_end_prob_threshold=g("stream_end_prob_threshold"),
+                          stream_end_score_sum_threshold=g("stream_end_score_sum_threshold"),
+                          running_list_length=g("running_list_length", 20),
+                          added_stream_generation_ids=None if g("grounding_mode", False) else gen_ids,
+                          repetition_penalty=g("repetition_penalty"), remove_assistant_turns=g("remove_assistant_turns", False))
+
+    def _init_native(self, model: VideoHeadLiveLlavaQwenForCausalLM, start_ids: torch.Tensor,
                  added_stream_prompt_ids: Optional[torch.Tensor] = None, sink_cache: bool = False,
                  alt_cache: str = "default_sink", window_length: int = 2048, num_sink_tokens: int = 32,
                  frame_fps: float = 2.0, score_heads=("relevance_score", "informative_score"),
@@ -51,6 +98,10 @@ class LiveInferForBenchmark:
                  repetition_penalty: Optional[float] = None, remove_assistant_turns: bool = False,
                  max_new_tokens: int = 200):
         self.model = model
+        self.sink_cache, self.alt_cache = sink_cache, alt_cache
+        if not hasattr(self, "tokenizer"):
+            self.tokenizer = None
+            self.image_processor = model.get_vision_tower().image_processor
         self.overlap_vision = overlap_vision and os.environ.get("AHA_OVERLAP_VISION", "1") != "0"
         self.model.eval()
         cfg = model.config
@@ -114,6 +165,8 @@ class LiveInferForBenchmark:
     def input_video_stream(self, video_frames: torch.Tensor, batch_size: int = 32):
         """uint8 [T, 3, S, S]; embeds stay on the device.  With `overlap_vision` the batches are enqueued on the model's
         vision stream and this call returns at once; every batch carries an event that `_encode_frame` waits for."""
+        if video_frames.dtype == torch.float32:           # image_processor.preprocess(...)['pixel_values'] (test/inference.py:176)
+            video_frames = video_frames.to(self.model.device).to(torch.bfloat16)
         if not (self.overlap_vision and video_frames.is_cuda):
             for b in range(0, len(video_frames), batch_size):
                 emb = self.model.visual_embed(video_frames[b:b + batch_size]).split(self.frame_num_tokens)
@@ -137,12 +190,15 @@ class LiveInferForBenchmark:
                         self._ready_events[id(f)] = (f, ev)                            # first frame of a batch carries its event
         _lib.load().aha_set_sm_sharing(0)
 
-    def load_one_frame(self, frame: Optional[torch.Tensor] = None, frame_object=None):
+    def load_one_frame(self, frame: Optional[torch.Tensor] = None, frame_object=None, frame_path=None):
         """`frame`: a canvas [3, 384, 384] uint8 that is already resized and padded.  `frame_object` (the reference's
         keyword, test/live_infer_for_video.py:98-119): a decoded RGB picture of any size - PIL image, HWC numpy array or
         HWC uint8 tensor - resized (PIL bicubic, bit-identical), padded and transposed on the device (aha_b200/ingest.py)."""
+        if frame_path is not None and frame_object is None and frame is None:
+            from PIL import Image
+            frame_object = Image.open(frame_path).convert("RGB")        # test/live_infer_for_video.py:102-103
         if (frame is None) == (frame_object is None):
-            raise ValueError("give exactly one of frame / frame_object")
+            raise ValueError("give exactly one of frame / frame_object / frame_path")
         if frame_object is not None:
             from .ingest import load_one_frame as _ingest_one
             if not isinstance(frame_object, torch.Tensor):
@@ -153,8 +209,14 @@ class LiveInferForBenchmark:
         self.frame_embeds_queue.append((self.video_time if not self.frame_embeds_queue else
                                         self.frame_embeds_queue[-1][0] + self.frame_interval, emb))
 
-    def input_query_stream(self, query_ids: torch.Tensor, video_time: float = 0.0):
-        """The reference tokenises a chat turn (test/inference.py:157-167); without a tokenizer the ids are given."""
+    def input_query_stream(self, query_ids, video_time: float = 0.0):
+        """Token ids of one query, or the reference's `conversation` list of turns ({'role': 'user', 'content', 'time'},
+        test/inference.py:188-191) - those are tokenised by the chat template when they are encoded (:250)."""
+        if isinstance(query_ids, (list, tuple)) and query_ids and isinstance(query_ids[0], dict):
+            for turn in query_ids:
+                if turn.get('role') == 'user':
+                    self.query_queue.append((turn.get('time', 0), turn['content']))
+            return
         self.query_queue.append((video_time, query_ids.reshape(1, -1).to(self.model.device)))
 
     # ---- one chunk (test/inference.py:196-262) ----
@@ -195,6 +257,12 @@ class LiveInferForBenchmark:
 
     def _encode_query(self):
         _, ids = self.query_queue.popleft()
+        if isinstance(ids, str):
+            if self.tokenizer is None:
+                raise RuntimeError("a text query needs a tokenizer (construct the driver from args, or pass token ids)")
+            ids = self.tokenizer.apply_chat_template([{'role': 'user', 'content': ids}], add_stream_prompt=True,
+                                                     add_stream_query_prompt=self.last_role == 'stream',
+                                                     return_tensors='pt').to(self.model.device)
         x = self.model.assemble_chunk(ids, None)
         out = self.model(inputs_embeds=x, use_cache=True, past_key_values=self.past_key_values, return_dict=True)
         self.past_key_values = out.past_key_values
@@ -254,7 +322,7 @@ class LiveInferForBenchmark:
             self._after_frame_scores(inf, rel)
         self.video_time += 1 / self.frame_fps
 
-    def inference(self):
+    def inference(self, verbose=False, total=None):
         """test/inference.py:283-334; fills `debug_data_list` with one dict per frame."""
         if self.overlap_vision and self._ready_events:
             # vision batches are in flight on the vision stream: run the decoder steps on the high-priority stream so the
@@ -288,4 +356,64 @@ class LiveInferForBenchmark:
         return _find_ticks(scores, fps, min_separation, prominence, thresh, verbose, device=self.model.device)
 
 
-LiveInferForDemo = LiveInferForBenchmark
+class LiveInferForDemo(LiveInferForBenchmark):
+    """test/live_infer_for_video.py:80-229: the one-frame-at-a-time driver of the interactive demo."""
+
+    def __init__(self, model_or_args, peft_model_id=None, query=None, **kw):
+        if isinstance(model_or_args, VideoHeadLiveLlavaQwenForCausalLM):
+            super().__init__(model_or_args, peft_model_id, **kw)       # (model, start_ids, ...)
+        else:
+            super().__init__(model_or_args, peft_model_id, **kw)
+        self.system_prompt = ("A multimodal AI assistant is helping users with some activities. Below is their conversation, "
+                              "interleaved with the list of video frames received by the assistant.")
+        self.frame_idx = 0
+
+    def encode_given_query(self, query):
+        """test/live_infer_for_video.py:89-95: a user turn typed into the demo page, encoded at once."""
+        self.query_queue.appendleft((self.video_time, query))
+        out = self._encode_query()
+        self.last_ids = out.logits[:, -1:].argmax(dim=-1)
+        return out
+
+    def input_one_frame(self):
+        """test/live_infer_for_video.py:135-176: one frame in, its record out (one device->host read per frame - the demo
+        decides after every frame whether to answer)."""
+        self._encode_frame()
+        inf, rel, unc = self._score_buf[self._n_scored - 1].tolist()
+        self.frame_idx += 1
+        ret = dict(frame_idx=self.frame_idx, time=round(self.video_time, 1), uncertainty_score=unc,
+                   informative_score=inf, relevance_score=rel)
+        n_resp = len(self.model_response_list)
+        if self._wants_decisions:
+            self._after_frame_scores(inf, rel)
+        ret['response'] = self.model_response_list[-1]['content'] if len(self.model_response_list) > n_resp else None
+        self.video_time += 1 / self.frame_fps
+        return ret
+
+    def input_video(self, video_path, query, fps=None):
+        """test/live_infer_for_video.py:179-193: decode (OpenCV, on the host), then resize / border / colour order on the
+        device (aha_b200.ingest, bit-identical to the reference's cv2 calls), the whole clip through the loop."""
+        import cv2
+        import numpy as np
+        from .ingest import load_video_for_testing
+        cap = cv2.VideoCapture(video_path)
+        input_fps = cap.get(cv2.CAP_PROP_FPS)
+        frames = []
+        while cap.isOpened():
+            ok, fr = cap.read()
+            if not ok:
+                break
+            frames.append(fr)
+        cap.release()
+        if not frames:
+            raise ValueError(f"no frames decoded from {video_path}")
+        raw = torch.from_numpy(np.stack(frames))
+        out_fps = fps if fps and fps > 0 else 400 / (len(frames) / input_fps)
+        video_frames, out_fps, _ = load_video_for_testing(raw, input_fps, output_fps=out_fps, max_num_frames=400,
+                                                          device=self.model.device)
+        self.set_fps(fps=out_fps)
+        self.input_video_stream(video_frames)
+        self.input_query_stream([{"role": "system", "content": self.system_prompt},
+                                 {'role': 'user', 'content': query, 'time': 0}])
+        self.inference(verbose=True, total=len(video_frames))
+        return round_numbers(self.debug_data_list, 3), self.model_response_list

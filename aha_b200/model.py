@@ -118,6 +118,16 @@ class VideoHeadLiveLlavaQwenForCausalLM:
     def get_input_embeddings(self):
         return _InputEmbeddings(self)
 
+    def get_vision_tower(self):
+        """`model.get_vision_tower().image_processor` (test/inference.py:51): the SigLIP image processor of the reference,
+        for callers that run it themselves; `visual_embed` also takes the raw uint8 frames and fuses it in."""
+        if getattr(self, "_vision_tower", None) is None:
+            from .compat import _VisionTower
+            self._vision_tower = _VisionTower(self.config.vision.image_size)
+        return self._vision_tower
+
+    dtype = torch.bfloat16
+
     def new_cache(self, alt_cache="default_sink", window_length=2048, num_sink_tokens=32, sink_cache=False, n_sys=0,
                   max_chunk=None):
         """_init_cache (test/inference.py:133-155) with the slabs allocated up front for this model's geometry."""
