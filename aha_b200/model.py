@@ -53,7 +53,7 @@ class _InputEmbeddings:
         if flat.numel():
             _lib.check(_lib.load().aha_assemble_chunk(self._m._h, _lib.ptr(flat), flat.numel(), None, 0, _lib.ptr(out),
                                                       _lib.stream_ptr()))
-        return out.view(*shape, -1)
+        return out.view(*shape, self._m.config.hidden_size)
 
 
 class VideoHeadLiveLlavaQwenForCausalLM:

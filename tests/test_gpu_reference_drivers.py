@@ -159,7 +159,10 @@ def test_reference_constructor_signature(cuda, built):
     with pytest.raises(ValueError):
         A.LiveInferForBenchmark(dataclasses.replace(_Args(), stream_end_prob_threshold=0.5), state_dict=w, config=cfg,
                                 tokenizer=tok, device=cuda)
-    demo = A.LiveInferForDemo(_Args(), None, state_dict=w, config=cfg, tokenizer=tok, device=cuda, max_tokens=64, max_frames=8)
+    # (the device resize needs a canvas side that is a multiple of 4: a 112-pixel variant of the small config)
+    cfg4 = dataclasses.replace(cfg, vision=dataclasses.replace(cfg.vision, image_size=112), frame_resolution=112)
+    w4 = A.random_init_state_dict(cfg4, seed=1, device=cuda)
+    demo = A.LiveInferForDemo(_Args(), None, state_dict=w4, config=cfg4, tokenizer=tok, device=cuda, max_tokens=64, max_frames=8)
     from PIL import Image
     rng = np.random.default_rng(0)
     recs = []
