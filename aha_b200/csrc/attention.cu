@@ -38,7 +38,7 @@ constexpr int kAtomBytes = 16384;   // one [128 rows][64 bf16] swizzled box
 constexpr int kStagesKV = 2;
 constexpr int kPBufs = 2;           // P tiles in shared memory
 constexpr int kAttnThreads = 384;   // warps 0-3: TMA / MMA / TMEM, warps 4-11: softmax (two threads per query row)
-constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256;   // O of the even key tiles at kColO, of the odd ones at kColO + 128
+constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct AttnSmem {
@@ -125,7 +125,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
     }
     mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
-    for (int b = 0; b < kPBufs; ++b) { mbar_init(&p_full[b], 128); mbar_init(&pv_done[b], 1); }
+    for (int b = 0; b < kPBufs; ++b) { mbar_init(&p_full[b], 256); mbar_init(&pv_done[b], 1); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_slot);
@@ -161,13 +161,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   pdl_launch_dependents();
   dbg_stamp(ts, 2);
 
-  // softmax-thread state (meaningful in warps 4-11).  The eight softmax warps form TWO groups that take the key tiles in
-  // turn (`half` 0: even tiles, 1: odd tiles; lane l of warps w and w + 4 owns the same query row = TMEM lane).  Each
-  // group runs its own online softmax - its own running maximum, row sum and O accumulator - so the groups never
-  // exchange anything inside the loop: while one waits for its next scores and scans them for the maximum, the other
-  // keeps the exponential unit busy.  (All eight warps on the same tile went through load / maximum / exchange barrier /
-  // exponentials in lockstep: 2000 cycles per tile of which the XU pipe was busy 1024.)  The two partial results of a
-  // row are combined like two key splits when the loop is over.
+  // softmax-thread state (meaningful in warps 4-11).  A query row is shared by two threads, lane l of warps w and w + 4
+  // (same TMEM lane quadrant): `half` picks the 64 of the tile's 128 key columns the thread owns, and the 16-column
+  // blocks of O it rescales / stores.  With one thread per row the four softmax warps - one per scheduler, every
+  // latency exposed - were the critical path of the kernel (2.2 us per key tile against 0.3 us of tensor work).
   const int ew = warp & 3;
   const int half = warp >= 8 ? 1 : 0;
   const int row = ew * 32 + lane;            // tile row == TMEM lane
@@ -176,7 +173,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const int tok = m / p.group;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
   float m_used = -INFINITY, l_sum = 0.f;
-  float w_e = 1.f, w_o = 0.f;      // weights of the even- / odd-tile accumulators of this row (set when the loop is over)
 
   if (nkt > 0) {
     if (warp == 0) {
@@ -241,20 +237,18 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         };
         mbar_wait(q_full, 0);
         issue_qk(0);
-        if (nkt > 1) issue_qk(1);
         for (int it = 0; it < nkt; ++it) {
+          if (it + 1 < nkt) issue_qk(it + 1);
           const int s = it % kStagesKV;
-          mbar_wait(&p_full[it & 1], (it >> 1) & 1);     // group it & 1 has written P(it) and is done with S[it & 1] ...
-          tc_fence_after();
-          if (it + 2 < nkt) issue_qk(it + 2);            // ... so its next scores go first: P.V is off the critical path
           mbar_wait(&v_full[s], (it / kStagesKV) & 1);
+          mbar_wait(&p_full[it & 1], (it >> 1) & 1);
           tc_fence_after();
           const uint32_t pa = smem_u32(sP + (it & 1) * 2 * kAtomBytes), va = smem_u32(sV + s * stage_bytes);
           for (int ks = 0; ks < kTile / 16; ++ks) {
             const uint64_t da = make_kmajor_sw128_desc(pa + (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32);
             // V tile is MN-major: 64-column blocks kAtomBytes apart (LBO), 8-key groups 1024 B apart (SBO)
             const uint64_t db = make_mnmajor_sw128_desc(va + (uint32_t)ks * 2048, kAtomBytes, 1024);
-            umma_f16_ss(tmem_base + kColO + (uint32_t)(it & 1) * 128u, da, db, idesc_pv, (it >= 2 || ks != 0) ? 1u : 0u);
+            umma_f16_ss(tmem_base + kColO, da, db, idesc_pv, (it | ks) != 0);
           }
           umma_commit(&v_empty[s]);
           umma_commit(&pv_done[it & 1]);
@@ -265,52 +259,50 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const int limit = seg.off + tok;           // logical key index must be <= limit
       const float sl2 = p.scale * 1.4426950408889634f;
       const bool all_visible = seg.off >= seg.klen - 1;
-      const uint32_t s_addr = lane_addr + (half ? kColS1 : kColS0);      // this group's score buffer
-      const uint32_t o_addr = lane_addr + kColO + (uint32_t)half * 128u;   // ... and O accumulator
-      uint8_t* prow = sP + half * 2 * kAtomBytes + row * 128;              // ... and P tile
-      for (int it = half; it < nkt; it += 2) {
+      // Two P tiles: the probabilities of tile t go to buffer t & 1, so the exponentials of tile t + 1 are computed and
+      // stored while the tensor pipe still multiplies P(t) by V(t).  With one buffer every tile paid for softmax, P.V and
+      // two barrier round trips in sequence (4460 cycles per tile at 8192 keys, tensor pipe 28 % busy, XU pipe 28 %).
+      for (int it = 0; it < nkt; ++it) {
+        uint8_t* prow = sP + (it & 1) * 2 * kAtomBytes + row * 128;
         const int kt = kt0 + it;
-        mbar_wait(&s_full[half], (it >> 1) & 1);
+        mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
         dbg_stamp(ts, 3 + 2 * min(it, 1));
-        // visibility of the tile's 128 key slots for this row (all ones on the fast path)
-        uint32_t vm[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-        bool masked = false;
+        if (it == 2) { dbg_stamp(ts, 8); }
+        const int col0 = half * 64;
+        const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0) + col0;
+        uint32_t sv[64];
+        tmem_ld_32x32b_x32p(s_addr, sv);
+        tmem_ld_32x32b_x32p(s_addr + 32, sv + 32);
+        tmem_ld_wait();
         if (all_visible && kt * kTile + kTile > seg.klen) {
           // ragged last tile without a causal limit (SigLIP's 729 keys, a full cache): only slots >= klen are masked
-          const int nvalid = seg.klen - kt * kTile;
+          const int nvalid = seg.klen - kt * kTile - col0;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const int nv = nvalid - c * 32;
-            vm[c] = nv >= 32 ? 0xffffffffu : nv <= 0 ? 0u : ((1u << nv) - 1u);
-          }
-          masked = true;
+          for (int t = 0; t < 64; ++t)
+            if (t >= nvalid) sv[t] = 0xff800000u;   // -inf
         } else if (!all_visible) {
-          // slow path (growing cache: causal limit through the ring geometry)
+          // slow path (growing cache: causal limit through the ring geometry): knock masked scores out before the statistics
 #pragma unroll
-          for (int c = 0; c < 4; ++c) vm[c] = visible_mask32(seg, kt * kTile + c * 32, limit);
-          masked = true;
-        }
-        // ---- pass A: row maximum over the tile's 128 scores (four independent chains) ----
-        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+          for (int c = 0; c < 2; ++c) {
+            const uint32_t vm = visible_mask32(seg, kt * kTile + col0 + c * 32, limit);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t sv[64];
-          tmem_ld_32x32b_x32p(s_addr + c * 64, sv);
-          tmem_ld_32x32b_x32p(s_addr + c * 64 + 32, sv + 32);
-          tmem_ld_wait();
-          if (masked) {
-#pragma unroll
-            for (int t = 0; t < 64; ++t)
-              if (!((vm[2 * c + (t >> 5)] >> (t & 31)) & 1u)) sv[t] = 0xff800000u;   // -inf
-          }
-#pragma unroll
-          for (int t = 0; t < 64; t += 4) {
-            mx4[0] = fmaxf(mx4[0], __uint_as_float(sv[t]));     mx4[1] = fmaxf(mx4[1], __uint_as_float(sv[t + 1]));
-            mx4[2] = fmaxf(mx4[2], __uint_as_float(sv[t + 2])); mx4[3] = fmaxf(mx4[3], __uint_as_float(sv[t + 3]));
+            for (int t = 0; t < 32; ++t)
+              if (!((vm >> t) & 1u)) sv[c * 32 + t] = 0xff800000u;   // -inf
           }
         }
-        float tmax = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2;   // scale > 0: max commutes with the scaling
+        float tmax = -INFINITY;
+#pragma unroll
+        for (int t = 0; t < 64; ++t) tmax = fmaxf(tmax, __uint_as_float(sv[t]));
+        {
+          // row maximum over both halves: the two threads of a row then take identical rescale decisions.  The slots
+          // alternate with the tile parity; the pair barrier of tile it + 1 orders their reuse at tile it + 2.
+          float* x = xch + (it & 1) * 256;
+          x[half * 128 + row] = tmax;
+          asm volatile("bar.sync %0, 64;" ::"r"(2 + ew) : "memory");
+          tmax = fmaxf(tmax, x[(half ^ 1) * 128 + row]);
+        }
+        tmax *= sl2;                                 // scale > 0: max commutes with the scaling
         float alpha = 1.f;
         bool rescale = false;
         if (tmax > m_used + kRescaleThreshold || (m_used == -INFINITY && tmax > -INFINITY)) {
@@ -318,95 +310,65 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           m_used = tmax;
           rescale = true;
         }
-        // this group's P tile and O accumulator belong to the tensor pipe until P.V of its previous tile (it - 2) is done
-        if (it >= 2) mbar_wait(&pv_done[half], ((it >> 1) - 1) & 1);
-        if (it >= 2 && __any_sync(0xffffffffu, rescale)) {
+        // this tile's P buffer is owned by the tensor pipe until P.V of tile it - 2 has completed
+        if (it >= 2) mbar_wait(&pv_done[it & 1], ((it >> 1) - 1) & 1);
+        if (it > 0 && __any_sync(0xffffffffu, rescale)) {
+          // O may only be rescaled between two P.V products: wait for the previous one (the MMAs complete in order) ...
+          mbar_wait(&pv_done[(it - 1) & 1], ((it - 1) >> 1) & 1);
           tc_fence_after();
 #pragma unroll 1
-          for (int cc = 0; cc < p.d_pad; cc += 16) {
+          for (int cc = half * 16; cc < p.d_pad; cc += 32) {
             uint32_t r[16];
-            tmem_ld_32x32b_x16(o_addr + cc, r);
+            tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
             tmem_ld_wait();
 #pragma unroll
             for (int t = 0; t < 16; ++t) r[t] = __float_as_uint(__uint_as_float(r[t]) * alpha);
-            tmem_st_32x32b_x16(o_addr + cc, r);
+            tmem_st_32x32b_x16(lane_addr + kColO + cc, r);
           }
           tmem_st_wait();
         }
         l_sum *= alpha;
-        // ---- pass B: probabilities -> bf16 -> swizzled K-major P tile (the scores are read from TMEM a second time:
-        //      keeping 128 of them in registers between the passes would not fit) ----
+        // probabilities -> bf16 -> swizzled K-major P tile
         const float mref = (m_used == -INFINITY) ? 0.f : m_used;
         float acc_l = 0.f;
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t sv[64];
-          tmem_ld_32x32b_x32p(s_addr + c * 64, sv);
-          tmem_ld_32x32b_x32p(s_addr + c * 64 + 32, sv + 32);
-          tmem_ld_wait();
-          if (masked) {
+        for (int cc = 0; cc < 64; cc += 32) {
+          uint32_t pk[16];
 #pragma unroll
-            for (int t = 0; t < 64; ++t)
-              if (!((vm[2 * c + (t >> 5)] >> (t & 31)) & 1u)) sv[t] = 0xff800000u;   // -inf
+          for (int t = 0; t < 32; t += 2) {
+            const float x0 = ex2_approx(fmaf(__uint_as_float(sv[cc + t]), sl2, -mref));
+            const float x1 = ex2_approx(fmaf(__uint_as_float(sv[cc + t + 1]), sl2, -mref));
+            acc_l += x0 + x1;
+            pk[t >> 1] = pack_bf16x2(x0, x1);
           }
-          uint8_t* base = prow + c * kAtomBytes;         // key columns 64 c .. +63 are one swizzle atom of P
+          uint8_t* base = prow + half * kAtomBytes;      // key columns 64*half .. +63 are one swizzle atom of P
+          const int chunk0 = cc >> 3;
 #pragma unroll
-          for (int cc = 0; cc < 64; cc += 32) {
-            uint32_t pk[16];
-#pragma unroll
-            for (int t = 0; t < 32; t += 2) {
-              const float x0 = ex2_approx(fmaf(__uint_as_float(sv[cc + t]), sl2, -mref));
-              const float x1 = ex2_approx(fmaf(__uint_as_float(sv[cc + t + 1]), sl2, -mref));
-              acc_l += x0 + x1;
-              pk[t >> 1] = pack_bf16x2(x0, x1);
-            }
-            const int chunk0 = cc >> 3;
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-              const int sw = (chunk0 + ch) ^ (row & 7);
-              *reinterpret_cast<uint4*>(base + sw * 16) = make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
-            }
+          for (int ch = 0; ch < 4; ++ch) {
+            const int sw = (chunk0 + ch) ^ (row & 7);
+            *reinterpret_cast<uint4*>(base + sw * 16) = make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
           }
         }
         l_sum += acc_l;
         fence_proxy_async();
         tc_fence_before();
-        mbar_arrive(&p_full[half]);
+        mbar_arrive(&p_full[it & 1]);
         dbg_stamp(ts, 4 + 2 * min(it, 1));
+        if (it == 2) { dbg_stamp(ts, 9); }
+        if (it == 1) { dbg_stamp(ts, 10); }
       }
       {
-        // The two groups of a row hold two independent partial softmaxes (even / odd key tiles): combine them like two key
-        // splits.  From here on m_used / l_sum are the row's statistics and (w_e, w_o) the weights of the two accumulators.
-        float* xm = xch;
-        float* xl = xch + 256;
-        xm[half * 128 + row] = m_used;
-        xl[half * 128 + row] = l_sum;
+        // row sum = half 0's partial + half 1's partial, added in that order by both threads
+        float* x = xch + (nkt & 1) * 256;
+        x[half * 128 + row] = l_sum;
         asm volatile("bar.sync %0, 64;" ::"r"(2 + ew) : "memory");
-        const float m0 = xm[row], m1 = xm[128 + row], l0 = xl[row], l1 = xl[128 + row];
-        m_used = fmaxf(m0, m1);
-        w_e = (m0 == -INFINITY) ? 0.f : ex2_approx(m0 - m_used);
-        w_o = (m1 == -INFINITY) ? 0.f : ex2_approx(m1 - m_used);
-        l_sum = w_e * l0 + w_o * l1;
+        l_sum = x[row] + x[128 + row];
       }
-      mbar_wait(&pv_done[(nkt - 1) & 1], ((nkt - 1) >> 1) & 1);   // O complete (the MMAs complete in order)
+      mbar_wait(&pv_done[(nkt - 1) & 1], ((nkt - 1) >> 1) & 1);   // O complete
       tc_fence_after();
       dbg_stamp(ts, 7);
     }
   }
-  // 16 columns of this row's combined (still unnormalised) O: w_e * O_even + w_o * O_odd
-  const bool has_odd = nkt > 1;
-  auto load_o16 = [&](int cc, uint32_t (&r)[16]) {
-    tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
-    if (has_odd) {
-      uint32_t r1[16];
-      tmem_ld_32x32b_x16(lane_addr + kColO + 128u + cc, r1);
-      tmem_ld_wait();
-#pragma unroll
-      for (int t = 0; t < 16; ++t) r[t] = __float_as_uint(w_e * __uint_as_float(r[t]) + w_o * __uint_as_float(r1[t]));
-    } else {
-      tmem_ld_wait();
-    }
-  };
 
   if (splits == 1) {
     if (warp >= 4) {
@@ -424,7 +386,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll 1
         for (int cc = half * 16; cc < p.d_pad; cc += 32) {
           uint32_t r[16];
-          load_o16(cc, r);
+          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+          tmem_ld_wait();
           uint32_t w[8];
 #pragma unroll
           for (int t = 0; t < 8; ++t) w[t] = pack_bf16x2(__uint_as_float(r[2 * t]) * inv, __uint_as_float(r[2 * t + 1]) * inv);
@@ -452,7 +415,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         uint32_t r[16];
         if (cc == 0) dbg_stamp(ts, 13);
         if (nkt > 0) {
-          load_o16(cc, r);
+          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+          tmem_ld_wait();
         } else {
 #pragma unroll
           for (int t = 0; t < 16; ++t) r[t] = 0u;
@@ -498,15 +462,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         uint32_t r[32];
         const bool two = cc + 32 <= p.d_pad;
         if (nkt > 0) {
-          uint32_t h[16];
-          load_o16(cc, h);
+          if (two) tmem_ld_32x32b_x32p(lane_addr + kColO + cc, r);
+          else { uint32_t h[16]; tmem_ld_32x32b_x16(lane_addr + kColO + cc, h);
 #pragma unroll
-          for (int t = 0; t < 16; ++t) r[t] = h[t];
-          if (two) {
-            load_o16(cc + 16, h);
-#pragma unroll
-            for (int t = 0; t < 16; ++t) r[16 + t] = h[t];
-          }
+                 for (int t = 0; t < 16; ++t) r[t] = h[t]; }
+          tmem_ld_wait();
         } else {
 #pragma unroll
           for (int t = 0; t < 32; ++t) r[t] = 0u;
