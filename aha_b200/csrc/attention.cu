@@ -38,7 +38,7 @@ constexpr int kAtomBytes = 16384;   // one [128 rows][64 bf16] swizzled box
 constexpr int kStagesKV = 2;
 constexpr int kPBufs = 2;           // P tiles in shared memory
 constexpr int kAttnThreads = 384;   // warps 0-3: TMA / MMA / TMEM, warps 4-11: softmax (two threads per query row)
-constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256;
+constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256, kColQ = 384;   // Q: 64 columns of packed bf16 pairs
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct AttnSmem {
@@ -120,7 +120,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
   if (warp == 0 && lane == 0) { prefetch_tensormap(&tmap_q); prefetch_tensormap(tmk); prefetch_tensormap(tmv); }
   if (warp == 1 && lane == 0) {
-    mbar_init(q_full, 1);
+    mbar_init(q_full, 256);
     for (int s = 0; s < kStagesKV; ++s) {
       mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
     }
@@ -178,10 +178,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (warp == 0) {
       // ===================== TMA producer =====================
       if (elect_one()) {
-        const int q_row = seg.q_row0 + blk * p.q_block_rows + qt * kTile;
-        const int q_col = p.q_col0 + blk * p.q_col_step;
-        mbar_arrive_expect_tx(q_full, stage_bytes);
-        for (int b = 0; b < DB; ++b) tma_load_2d(sQ + b * kAtomBytes, &tmap_q, q_full, q_col + b * 64, q_row);
         const int k_row = seg.k_row0 + blk * p.k_head_rows, k_col = p.k_col0 + blk * p.k_col_step;
         for (int it = 0; it < nkt; ++it) {
           const int s = it % kStagesKV;
@@ -226,10 +222,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const int s = it % kStagesKV;
           mbar_wait(&k_full[s], (it / kStagesKV) & 1);
           tc_fence_after();
-          const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + s * stage_bytes);
+          const uint32_t ka = smem_u32(sK + s * stage_bytes);
           for (int ks = 0; ks < ksteps; ++ks) {
             const uint32_t o = (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32;
-            umma_f16_ss(tmem_base + ((it & 1) ? kColS1 : kColS0), make_kmajor_sw128_desc(qa + o),
+            // Q is the A operand in tensor memory (8 columns per K = 16 step): the tensor pipe re-read the 32 KB Q tile from
+            // shared memory for every key tile, a quarter of the kernel's shared-memory traffic
+            umma_f16_ts(tmem_base + ((it & 1) ? kColS1 : kColS0), tmem_base + kColQ + (uint32_t)ks * 8u,
                         make_kmajor_sw128_desc(ka + o), idesc_qk, ks != 0);
           }
           umma_commit(&k_empty[s]);      // the K stage is free once these MMAs have read it
@@ -256,6 +254,26 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
     } else if (warp >= 4) {
       // ===================== softmax / correction =====================
+      {
+        // This row of Q goes from global memory straight into tensor memory (no TMA, no shared memory): thread `half` of the
+        // row packs elements [64 half, 64 half + 64) into 32 columns; elements beyond d_pad and rows beyond the matrix are 0.
+        const long long q_row = (long long)seg.q_row0 + (long long)blk * p.q_block_rows + (long long)qt * kTile + row;
+        const bf16* qsrc = p.q + q_row * (long long)p.q_ld + (p.q_col0 + blk * p.q_col_step) + half * 64;
+        const bool rv = q_row < (long long)p.q_rows_total;
+        uint32_t qv[32];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          uint4 u = make_uint4(0u, 0u, 0u, 0u);
+          if (rv && half * 64 + c * 8 < p.d_pad) u = *reinterpret_cast<const uint4*>(qsrc + c * 8);
+          qv[4 * c] = u.x; qv[4 * c + 1] = u.y; qv[4 * c + 2] = u.z; qv[4 * c + 3] = u.w;
+        }
+        const uint32_t qaddr = lane_addr + kColQ + (uint32_t)half * 32u;
+        tmem_st_32x32b_x16(qaddr, *reinterpret_cast<uint32_t(*)[16]>(&qv[0]));
+        tmem_st_32x32b_x16(qaddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&qv[16]));
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(q_full);
+      }
       const int limit = seg.off + tok;           // logical key index must be <= limit
       const float sl2 = p.scale * 1.4426950408889634f;
       const bool all_visible = seg.off >= seg.klen - 1;
