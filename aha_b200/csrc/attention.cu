@@ -12,17 +12,22 @@
 //   * SigLIP self-attention (siglip_encoder.py:197-239): per (frame, head) 729 x 729, head_dim 72 padded to 80 columns.
 //
 // CTA = one 128-row query tile of one (segment, head block, key split).  Warp roles:
-//   warp 0    TMA producer: Q once, then a 2-stage ring of K tiles (128 keys each)
+//   warp 0    TMA producer of the K ring (three stages of 128 keys)
 //   warp 3    TMA producer of the V ring (a K stage is free after Q.K^T, a V stage only after P.V)
 //   warp 1    MMA issuer (one elected lane): S[b] = Q.K^T for tile kt+1 is issued before P.V of tile kt, so the
-//             tensor pipe works on the next scores while the softmax warps are busy with the current ones
-//   warp 2    TMEM allocator (512 columns: S0 | S1 | O)
+//             tensor pipe works on the next scores while the softmax warps are busy with the current ones.  BOTH products
+//             take their A operand from TENSOR MEMORY: Q is written there once per CTA (64 columns of packed bf16 pairs,
+//             straight from global memory), P(kt) overwrites the first 64 columns of S(kt) - shared memory carries only
+//             K and V
+//   warp 2    TMEM allocator (512 columns: S0 | S1 | O | Q)
 //   warps 4-11 softmax / correction / epilogue: TWO threads per query row (lane l of warps w and w + 4 share TMEM lane
 //             quadrant w & 3 and own 64 of the tile's 128 key columns each; row maximum and sum are exchanged through
-//             shared memory).  P is written to shared memory in the K-major 128B-swizzled layout the MMA expects; O is
-//             rescaled in TMEM only when the running maximum grows by more than 2^8 (lazy rescale), which keeps the
-//             correction off the critical path.  The unsplit epilogue leaves through a shared-memory tile as 16-byte
-//             pieces in row order.
+//             shared memory).  O is rescaled in TMEM only when the running maximum grows by more than 2^8 (lazy rescale),
+//             which keeps the correction off the critical path.  The unsplit epilogue leaves through a shared-memory tile
+//             as 16-byte pieces in row order.
+// Measured on B200 (profiles/r02_attention_notes.txt): the loop runs at about 1900 cycles per 128 x 128 tile against the
+// 1024 cycles the 16 384 exponentials of a tile need on the XU pipe (16 per clock per SM, measured); what was tried on the
+// way: two P tiles, key-tile ping-pong of two softmax groups with two O accumulators, TMEM operands (this version).
 #include "ops.h"
 #include "gemm.h"
 #include "ptx_sm100.cuh"
@@ -35,22 +40,20 @@ namespace {
 
 constexpr int kTile = 128;          // query rows per CTA == keys per tile
 constexpr int kAtomBytes = 16384;   // one [128 rows][64 bf16] swizzled box
-constexpr int kStagesKV = 2;
-constexpr int kPBufs = 2;           // P tiles in shared memory
+constexpr int kStagesKV = 3;
+constexpr int kPBufs = 2;           // P tiles (tensor memory: the first 64 columns of the two score buffers)
 constexpr int kAttnThreads = 384;   // warps 0-3: TMA / MMA / TMEM, warps 4-11: softmax (two threads per query row)
 constexpr uint32_t kColS0 = 0, kColS1 = 128, kColO = 256, kColQ = 384;   // Q: 64 columns of packed bf16 pairs
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct AttnSmem {
-  // offsets inside the 1024-aligned dynamic shared memory
-  static __host__ __device__ int q_off() { return 0; }
-  static __host__ __device__ int k_off(int DB) { return DB * kAtomBytes; }
-  static __host__ __device__ int v_off(int DB) { return DB * kAtomBytes * (1 + kStagesKV); }
-  static __host__ __device__ int p_off(int DB) { return DB * kAtomBytes * (1 + 2 * kStagesKV); }
-  static __host__ __device__ int bar_off(int DB) { return p_off(DB) + kPBufs * 2 * kAtomBytes; }   // two P tiles (see the softmax loop)
+  // offsets inside the 1024-aligned dynamic shared memory: only the K and V rings live here - Q and P are tensor-memory
+  // operands of their MMAs (see the kernel), which left room for a third stage of each ring
+  static __host__ __device__ int k_off(int DB) { return 0; }
+  static __host__ __device__ int v_off(int DB) { return DB * kAtomBytes * kStagesKV; }
+  static __host__ __device__ int bar_off(int DB) { return DB * kAtomBytes * 2 * kStagesKV; }
   static __host__ __device__ int xch_off(int DB) { return bar_off(DB) + 256; }      // float [2][2][128] row-statistics exchange
-  // no alignment slack: 7 x 32 KB of tiles + 2.25 KB is all a CTA can have; the dynamic window of a kernel without static
-  // shared memory starts 1024-aligned (checked at kernel entry)
+  // no alignment slack: the dynamic window of a kernel without static shared memory starts 1024-aligned (checked at entry)
   static __host__ __device__ int total(int DB) { return xch_off(DB) + 2048; }
 };
 
@@ -84,22 +87,21 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem_raw) & 1023u) != 0) { if (threadIdx.x == 0) printf("aha_b200: attention shared memory is not 1024-byte aligned\n"); __trap(); }
   const int DB = (p.d_pad + 63) >> 6;
-  uint8_t* sQ = smem + AttnSmem::q_off();
   uint8_t* sK = smem + AttnSmem::k_off(DB);
   uint8_t* sV = smem + AttnSmem::v_off(DB);
-  uint8_t* sP = smem + AttnSmem::p_off(DB);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AttnSmem::bar_off(DB));
   // K and V have their own rings: a K stage is free again as soon as its Q.K^T has completed (one whole softmax period
-  // before the matching P.V), so its refill has two softmax periods to land instead of one
-  uint64_t* q_full = bars;             // 1
-  uint64_t* k_full = bars + 1;         // kStagesKV
-  uint64_t* k_empty = bars + 3;        // kStagesKV
-  uint64_t* s_full = bars + 5;         // 2
-  uint64_t* p_full = bars + 7;         // kPBufs (256 arrivals each)
-  uint64_t* pv_done = bars + 9;        // kPBufs: P.V of tile t commits to pv_done[t & 1]
-  uint64_t* v_full = bars + 11;        // kStagesKV
-  uint64_t* v_empty = bars + 13;       // kStagesKV
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  // before the matching P.V), so its refill has more time to land
+  uint64_t* q_full = bars;                          // 1 (256 arrivals: the softmax threads store Q into tensor memory)
+  uint64_t* k_full = bars + 1;                      // kStagesKV
+  uint64_t* k_empty = k_full + kStagesKV;           // kStagesKV
+  uint64_t* s_full = k_empty + kStagesKV;           // 2
+  uint64_t* p_full = s_full + 2;                    // kPBufs (256 arrivals each)
+  uint64_t* pv_done = p_full + kPBufs;              // kPBufs: P.V of tile t commits to pv_done[t & 1]
+  uint64_t* v_full = pv_done + kPBufs;              // kStagesKV
+  uint64_t* v_empty = v_full + kStagesKV;           // kStagesKV
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(v_empty + kStagesKV);
+  static_assert((7 + 4 * kStagesKV) * 8 + 4 <= 256, "barrier block");
   float* xch = reinterpret_cast<float*>(smem + AttnSmem::xch_off(DB));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -241,12 +243,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           mbar_wait(&v_full[s], (it / kStagesKV) & 1);
           mbar_wait(&p_full[it & 1], (it >> 1) & 1);
           tc_fence_after();
-          const uint32_t pa = smem_u32(sP + (it & 1) * 2 * kAtomBytes), va = smem_u32(sV + s * stage_bytes);
+          const uint32_t va = smem_u32(sV + s * stage_bytes);
+          const uint32_t pt = tmem_base + ((it & 1) ? kColS1 : kColS0);     // P(it) sits in the first 64 columns of S(it)
           for (int ks = 0; ks < kTile / 16; ++ks) {
-            const uint64_t da = make_kmajor_sw128_desc(pa + (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32);
             // V tile is MN-major: 64-column blocks kAtomBytes apart (LBO), 8-key groups 1024 B apart (SBO)
             const uint64_t db = make_mnmajor_sw128_desc(va + (uint32_t)ks * 2048, kAtomBytes, 1024);
-            umma_f16_ss(tmem_base + kColO, da, db, idesc_pv, (it | ks) != 0);
+            umma_f16_ts(tmem_base + kColO, pt + (uint32_t)ks * 8u, db, idesc_pv, (it | ks) != 0);
           }
           umma_commit(&v_empty[s]);
           umma_commit(&pv_done[it & 1]);
@@ -281,7 +283,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // stored while the tensor pipe still multiplies P(t) by V(t).  With one buffer every tile paid for softmax, P.V and
       // two barrier round trips in sequence (4460 cycles per tile at 8192 keys, tensor pipe 28 % busy, XU pipe 28 %).
       for (int it = 0; it < nkt; ++it) {
-        uint8_t* prow = sP + (it & 1) * 2 * kAtomBytes + row * 128;
+        const uint32_t p_addr = lane_addr + ((it & 1) ? kColS1 : kColS0);
         const int kt = kt0 + it;
         mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
@@ -328,8 +330,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           m_used = tmax;
           rescale = true;
         }
-        // this tile's P buffer is owned by the tensor pipe until P.V of tile it - 2 has completed
-        if (it >= 2) mbar_wait(&pv_done[it & 1], ((it >> 1) - 1) & 1);
+        // (P(it) overwrites the first half of S(it) in tensor memory: both threads of the row have their scores in registers
+        // - the pair barrier above - and the P.V product that read P(it - 2) from these columns ran before Q.K^T(it) did)
         if (it > 0 && __any_sync(0xffffffffu, rescale)) {
           // O may only be rescaled between two P.V products: wait for the previous one (the MMAs complete in order) ...
           mbar_wait(&pv_done[(it - 1) & 1], ((it - 1) >> 1) & 1);
@@ -359,16 +361,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             acc_l += x0 + x1;
             pk[t >> 1] = pack_bf16x2(x0, x1);
           }
-          uint8_t* base = prow + half * kAtomBytes;      // key columns 64*half .. +63 are one swizzle atom of P
-          const int chunk0 = cc >> 3;
-#pragma unroll
-          for (int ch = 0; ch < 4; ++ch) {
-            const int sw = (chunk0 + ch) ^ (row & 7);
-            *reinterpret_cast<uint4*>(base + sw * 16) = make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
-          }
+          // keys 64 half + cc .. + 31 of this row = 16 columns of packed bf16 pairs
+          tmem_st_32x32b_x16(p_addr + (uint32_t)(half * 32 + (cc >> 1)), pk);
         }
         l_sum += acc_l;
-        fence_proxy_async();
+        tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&p_full[it & 1]);
         dbg_stamp(ts, 4 + 2 * min(it, 1));
@@ -695,7 +692,7 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
   // K / V tiles requested into L2 ahead of the TMA ring (0: off); the short key axes of the single-stream step fit whole
-  { static const int kvpf = getenv("AHA_KV_PF") ? atoi(getenv("AHA_KV_PF")) : 6; p.kv_prefetch = (splits > 1 || max_tiles >= 16) ? kvpf : 0; }
+  { static const int kvpf = getenv("AHA_KV_PF") ? atoi(getenv("AHA_KV_PF")) : 3; p.kv_prefetch = (splits > 1 || max_tiles >= 16) ? kvpf : 0; }
   // per-launch timing for bench.py's roofline leg: class 3 = many-tile batched attention (SigLIP), 4 = chunk versus cache
   ProfSlot* slot = prof_begin(ctas >= sm_count ? 3 : 4, st);
   AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));
