@@ -1939,6 +1939,8 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
       if (pbn == 0) {      // fewer wasted columns wins; ties go to the wider tile
         const int w256 = (p.Nb + 255) / 256 * 256, w192 = (p.Nb + 191) / 192 * 192;
         pbn = w192 < w256 ? 192 : 256;
+        static const int tall_bn = getenv("AHA_TALL_BN") ? atoi(getenv("AHA_TALL_BN")) : 0;   // experiment knob
+        if (tall_bn == 192 || tall_bn == 256) pbn = tall_bn;
       }
       const int tm = (p.Ma + kBlockM - 1) / kBlockM, tn = (p.Nb + pbn - 1) / pbn;
       if ((long)tm * tn >= 2L * w->sm_count || c.force_bn != 0) {
