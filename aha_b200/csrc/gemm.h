@@ -30,6 +30,8 @@ struct GemmParams {
   int* ws_counters;     // split-K arrival counter per tile, in this launch's counter bank (zero on entry)
   int* ws_zero;         // the OTHER counter bank, ws_zero_n ints: this launch zeroes it for the next split launch
   int ws_zero_n;
+  int sk_ranks;         // persistent skinny kernel, stream-K decomposition: CTAs per token tile (0: fixed split); `splits` is then
+                        // the workspace slot count per tile (the largest number of ranks that share one tile)
   int* ws_pcounters;    // persistent skinny kernel: self-resetting counter per (tile, column group), zero between launches
   unsigned long long* dbg_ts;   // bring-up: phase stamps of CTA (0,0,0), or null
   unsigned long long* dbg_all;  // bring-up: (accumulator complete, exit) of every CTA on the global ns timer, or null

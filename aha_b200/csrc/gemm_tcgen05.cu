@@ -980,23 +980,49 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_total = (p.K + kBlockK - 1) / kBlockK;
-  const int n_items = tiles_a * tiles_b * p.splits;
-  // item -> (feature tile, split, token tile); token tile fastest: the readers of one weight tile are neighbours
-  auto decode = [&](int it, int& a0, int& b0, int& kb0, int& kb1, int& tile_lin, int& split) {
-    const int tb = it % tiles_b, r = it / tiles_b;
-    split = r % p.splits;
+  // Work items of this CTA, in order.  Two decompositions:
+  //  * fixed split (p.sk_ranks == 0): item -> (feature tile, split, token tile), token tile fastest (the readers of one
+  //    weight tile are neighbours), items dealt round-robin over the CTAs;
+  //  * stream-K (p.sk_ranks = R): the CTAs of one token tile (blockIdx.x % tiles_b) share the tiles_a x kb_total k-block
+  //    units of that token tile in R equal contiguous ranges, whatever the tile boundaries: every SM carries the same number
+  //    of k-blocks (down at 392 tokens has 56 tiles of 296 k-blocks - any fixed split leaves a third of the SMs idle or
+  //    runs a second, nearly empty round).  Rank r of EVERY token tile walks the same range at the same time, so a weight
+  //    tile is still pulled by neighbours together.  A tile that spans several ranks is merged by its last arriver; the
+  //    rank's position among the tile's contributors is its split index (fixed summation order).
+  struct Item { int a0, b0, kb0, kb1, tile_lin, split, nsplit; };
+  const int sk_R = p.sk_ranks;
+  const long long sk_U = (long long)tiles_a * kb_total;
+  const int sk_r = blockIdx.x / tiles_b, sk_tb = blockIdx.x % tiles_b;
+  const long long sk_u0 = sk_R ? (sk_r * sk_U) / sk_R : 0, sk_u1 = sk_R ? ((sk_r + 1) * sk_U) / sk_R : 0;
+  auto sk_rank_of = [&](long long u) { return (int)(((u + 1) * sk_R + sk_U - 1) / sk_U) - 1; };
+  auto get_item = [&](int i, Item& it) -> bool {
+    if (sk_R) {
+      if (sk_u1 <= sk_u0) return false;
+      const int f = (int)(sk_u0 / kb_total) + i;
+      if (f > (int)((sk_u1 - 1) / kb_total)) return false;
+      const long long t0 = (long long)f * kb_total, t1 = t0 + kb_total;
+      it.a0 = f * kBlockM; it.b0 = sk_tb * kPsBN;
+      it.kb0 = (int)(max(sk_u0, t0) - t0); it.kb1 = (int)(min(sk_u1, t1) - t0);
+      it.tile_lin = f * tiles_b + sk_tb;
+      const int rf = sk_rank_of(t0), rl = sk_rank_of(t1 - 1);
+      it.split = sk_r - rf; it.nsplit = rl - rf + 1;
+      return true;
+    }
+    const int g = blockIdx.x + i * gridDim.x;
+    if (g >= tiles_a * tiles_b * p.splits) return false;
+    const int tb = g % tiles_b, r = g / tiles_b;
+    it.split = r % p.splits; it.nsplit = p.splits;
     const int f = r / p.splits;
-    a0 = f * kBlockM; b0 = tb * kPsBN;
-    kb0 = split * p.kb_per_split; kb1 = min(kb_total, kb0 + p.kb_per_split);
-    tile_lin = f * tiles_b + tb;
+    it.a0 = f * kBlockM; it.b0 = tb * kPsBN;
+    it.kb0 = it.split * p.kb_per_split; it.kb1 = min(kb_total, it.kb0 + p.kb_per_split);
+    it.tile_lin = f * tiles_b + tb;
+    return true;
   };
   const uint64_t pol_a = l2_policy_evict_first(), pol_b = l2_policy_evict_last();
   int pre = 0;
-  if ((int)blockIdx.x < n_items) {
-    int a0, b0, kb0, kb1, tl_, sp_;
-    decode(blockIdx.x, a0, b0, kb0, kb1, tl_, sp_);
-    pre = min(C::kStages, kb1 - kb0);
-  }
+  Item first{};
+  const bool have_first = get_item(0, first);
+  if (have_first) pre = min(C::kStages, first.kb1 - first.kb0);
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmap_a);
     prefetch_tensormap(&tmap_b);
@@ -1005,11 +1031,9 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     fence_barrier_init();
     // the weight tiles of the first ring do not depend on any earlier kernel: requested before griddepcontrol.wait (PDL)
     if (pre > 0) {
-      int a0, b0, kb0, kb1, tl_, sp_;
-      decode(blockIdx.x, a0, b0, kb0, kb1, tl_, sp_);
       for (int kb = 0; kb < pre; ++kb) {
         mbar_arrive_expect_tx(&full_bar[kb], C::kStageBytes);
-        tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], (kb0 + kb) * kBlockK, a0, pol_a);
+        tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], (first.kb0 + kb) * kBlockK, first.a0, pol_a);
       }
     }
   }
@@ -1025,10 +1049,10 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     if (lane == 0) {
       pdl_wait();
       uint32_t cnt = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        int a0, b0, kb0, kb1, tl_, sp_;
-        decode(it, a0, b0, kb0, kb1, tl_, sp_);
-        for (int kb = kb0; kb < kb1; ++kb, ++cnt) {
+      Item it;
+      for (int ii = 0; get_item(ii, it); ++ii) {
+        const int a0 = it.a0, b0 = it.b0;
+        for (int kb = it.kb0; kb < it.kb1; ++kb, ++cnt) {
           const int s = cnt % C::kStages;
           if (cnt < (uint32_t)pre) {           // first ring: the weight tile is already on its way
             tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, b0, pol_b);
@@ -1046,9 +1070,9 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, kPsBN);
       uint32_t cnt = 0, tl = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++tl) {
-        int a0, b0, kb0, kb1, tl_, sp_;
-        decode(it, a0, b0, kb0, kb1, tl_, sp_);
+      Item it;
+      for (int ii = 0; get_item(ii, it); ++ii, ++tl) {
+        const int kb0 = it.kb0, kb1 = it.kb1;
         const uint32_t buf = tl & 1;
         mbar_wait(&tmem_empty[buf], ((tl >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator
         tc_fence_after();
@@ -1095,9 +1119,9 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       asm volatile("bar.sync 3, 256;" ::: "memory");
     }
     uint32_t tl = 0, sq_cnt = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++tl) {
-      int a0, b0, kb0, kb1, tile_lin, split;
-      decode(it, a0, b0, kb0, kb1, tile_lin, split);
+    Item it;
+    for (int ii = 0; get_item(ii, it); ++ii, ++tl) {
+      const int a0 = it.a0, b0 = it.b0, tile_lin = it.tile_lin, split = it.split, nsplit = it.nsplit;
       const uint32_t buf = tl & 1;
       mbar_wait(&tmem_full[buf], (tl >> 1) & 1);
       tc_fence_after();
@@ -1108,7 +1132,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       const bool staged = swap_staged_ok(p, a0);
       const int ncols = min(kPsBN, p.Nb - b0);
       const int my_end = min(col_end, ncols);
-      if (p.splits == 1) {
+      if (nsplit == 1) {
 #pragma unroll 1
         for (int jc = col_begin; jc < my_end; jc += 16) {
           uint32_t r[16];
@@ -1152,7 +1176,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         if (ew == 0 && lane == 0) {
           int* cnt = p.ws_pcounters + tile_lin * 2 + grp;
           const int old = atomicAdd(cnt, 1);
-          const int last = (old == p.splits - 1) ? 1 : 0;
+          const int last = (old == nsplit - 1) ? 1 : 0;
           if (last) *cnt = 0;                              // self-resetting: nobody else touches it in this launch
           last_flag[grp] = last;
         }
@@ -1165,7 +1189,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
             float acc[16];
 #pragma unroll
             for (int t = 0; t < 16; ++t) acc[t] = 0.f;
-            reduce_splits_dyn(base + jc * kBlockM, kSplitStride, p.splits, acc);
+            reduce_splits_dyn(base + jc * kBlockM, kSplitStride, nsplit, acc);
             if (p.rs_partials) {
 #pragma unroll
               for (int t = 0; t < 16; ++t) acc[t] *= rstd_all[b0 + jc + t];
@@ -1654,7 +1678,7 @@ int dispatch_persistent(int act, const CUtensorMap& ta, const CUtensorMap& tb, c
 namespace {
 template <int kAct>
 int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_a, int tiles_b,
-                           int sm_count, cudaStream_t stream) {
+                           int grid_ctas, cudaStream_t stream) {
   using C = PSCfg;
   static bool attr_done[16] = {false};
   int dev = 0;
@@ -1665,7 +1689,7 @@ int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const G
     attr_done[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(std::min(tiles_a * tiles_b * p.splits, sm_count)); cfg.blockDim = dim3(C::kThreads);
+  cfg.gridDim = dim3(grid_ctas); cfg.blockDim = dim3(C::kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -1879,33 +1903,51 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     }
     return rc;
   }
-  // Persistent skinny path, single CTAs (kept as the comparison point; force_bn = 208 selects it)
+  // Persistent skinny path, single CTAs (the default; force_bn = 208 selects it explicitly)
   if (swap && c.tokens > 256) {
     const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, tiles_b = (p.Nb + kPsBN - 1) / kPsBN;
     const int tiles = tiles_a * tiles_b;
     const int kb_total = (p.K + kBlockK - 1) / kBlockK;
     if (c.sumsq_tiles) *c.sumsq_tiles = tiles_a;
-    int splits = c.force_splits;
-    if (splits <= 0) {
-      // every SM should get the same number of k-blocks; a split item pays for parking / merging its partial tile
-      static const int max_env = getenv("AHA_PS_SPLITS") ? atoi(getenv("AHA_PS_SPLITS")) : 8;
-      long best_cost = -1;
-      for (int s = 1; s <= max_env && s <= kb_total; ++s) {
-        const int kb_per = (kb_total + s - 1) / s;
-        if ((kb_total + kb_per - 1) / kb_per != s || (s > 1 && kb_per < 8)) continue;
-        const long items = (long)tiles * s;
-        // (measured in the batched step: with residual + sum-of-squares epilogues, down runs faster split 2 ways than 5)
-        const long cost = ((items + w->sm_count - 1) / w->sm_count) * (kb_per + (s > 1 ? 14 + 6 * s : 2));
-        if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
+    static const int use_sk = getenv("AHA_PS_STREAMK") ? atoi(getenv("AHA_PS_STREAMK")) : 1;
+    int splits = c.force_splits, kb_per = kb_total, grid_ctas = 0;
+    p.sk_ranks = 0;
+    if (splits <= 0 && use_sk) {
+      // stream-K: every CTA carries the same number of k-blocks (see the kernel).  R ranks per token tile.
+      const long long U = (long long)tiles_a * kb_total;
+      int R = std::max(1, w->sm_count / tiles_b);
+      if (U / R < 8) R = (int)std::max<long long>(1, U / 8);        // at least 8 k-blocks per CTA
+      auto rank_of = [&](long long u) { return (int)(((u + 1) * R + U - 1) / U) - 1; };
+      int cap = 1;
+      for (int f = 0; f < tiles_a; ++f)
+        cap = std::max(cap, rank_of((long long)(f + 1) * kb_total - 1) - rank_of((long long)f * kb_total) + 1);
+      if (cap == 1 || ((size_t)tiles * cap * kPsBN * kBlockM * sizeof(float) <= GemmWorkspace::kPartialBytes && tiles * 2 <= 4096)) {
+        p.sk_ranks = R; splits = cap; grid_ctas = R * tiles_b;
       }
     }
-    if (splits > kb_total) splits = kb_total;
-    int kb_per = (kb_total + splits - 1) / splits;
-    splits = (kb_total + kb_per - 1) / kb_per;
-    while (splits > 1 && ((size_t)tiles * splits * kPsBN * kBlockM * sizeof(float) > GemmWorkspace::kPartialBytes || tiles * 2 > 4096)) {
-      --splits;
+    if (!p.sk_ranks) {
+      if (splits <= 0) {
+        // fixed split: a split item pays for parking / merging its partial tile
+        static const int max_env = getenv("AHA_PS_SPLITS") ? atoi(getenv("AHA_PS_SPLITS")) : 8;
+        long best_cost = -1;
+        for (int s = 1; s <= max_env && s <= kb_total; ++s) {
+          const int kbp = (kb_total + s - 1) / s;
+          if ((kb_total + kbp - 1) / kbp != s || (s > 1 && kbp < 8)) continue;
+          const long items = (long)tiles * s;
+          // (measured in the batched step: with residual + sum-of-squares epilogues, down runs faster split 2 ways than 5)
+          const long cost = ((items + w->sm_count - 1) / w->sm_count) * (kbp + (s > 1 ? 14 + 6 * s : 2));
+          if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
+        }
+      }
+      if (splits > kb_total) splits = kb_total;
       kb_per = (kb_total + splits - 1) / splits;
       splits = (kb_total + kb_per - 1) / kb_per;
+      while (splits > 1 && ((size_t)tiles * splits * kPsBN * kBlockM * sizeof(float) > GemmWorkspace::kPartialBytes || tiles * 2 > 4096)) {
+        --splits;
+        kb_per = (kb_total + splits - 1) / splits;
+        splits = (kb_total + kb_per - 1) / kb_per;
+      }
+      grid_ctas = std::min(tiles * splits, w->sm_count);
     }
     p.splits = splits; p.kb_per_split = kb_per; p.dbg = 0;
     if (splits > 1) {
@@ -1917,8 +1959,8 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
     rc = get_tmap(b, p.Nb, p.K, ldb, kPsBN, &tb); if (rc) return rc;
     ProfSlot* slot = prof_begin(5, stream);
-    rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_a, tiles_b, w->sm_count, stream)
-                                    : launch_swap_persistent<GEMM_ACT_NONE>(ta, tb, p, tiles_a, tiles_b, w->sm_count, stream);
+    rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream)
+                                    : launch_swap_persistent<GEMM_ACT_NONE>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream);
     if (slot) {
       const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * 2;
       prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,

@@ -35,6 +35,9 @@ def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1, bn=0):
     (600, 1536, 8960, 3, 4),
     (392, 896, 3584, 0, 2),       # 7 weight tiles: the last CTA pair has only one valid tile
     (430, 3584, 2048, 0, 1),      # second token group with a single 208-token half
+    (600, 1536, 8960, 3, 0),      # three token tiles, stream-K ranges across tile boundaries (49 ranks per token tile)
+    (392, 3584, 18944, 3, 0),
+    (300, 256, 4096, 0, 0),       # two feature tiles only: fewer ranks than SMs
 ])
 @pytest.mark.parametrize("bn", [416, 208], ids=["cta_pair", "single_cta"])
 def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits, bn):
