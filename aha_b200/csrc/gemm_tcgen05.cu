@@ -929,19 +929,26 @@ gemm_tall_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
 // SiLU*mul on interleaved gate|up rows, residual, folded RMSNorm on both sides (GemmCall).
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kPsBN = 208;
-struct PSCfg {
-  static constexpr int kStages = 5;
+// BN = 208: two token tiles cover 392 tokens (the big matrices: 296 feature tiles of gate|up fill the device four times);
+// BN = 112: four token tiles - the matrices with 28 / 36 feature tiles (o_proj, down, qkv) then have 112 / 144 work items
+// WITHOUT splitting K, i.e. without parking and merging partial tiles (in the step those merges cost more than the main
+// loops they balanced: o_proj 35 us, down 69 us, qkv 28 us split 2 ways).
+template <int BN>
+struct PSCfgT {
   static constexpr int kABytes = kBlockM * kBlockK * 2;
-  static constexpr int kBBytes = kPsBN * kBlockK * 2;
+  static constexpr int kBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = BN > 128 ? 5 : 7;
   static constexpr int kEpiWarps = 8;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kEpiWarpBytes = 1280;
-  static constexpr int kMaxTokens = 832;                  // 4 column tiles
+  static constexpr int kMaxTokens = 896;                  // 4 column tiles of 208, 8 of 112 (832 tokens)
   static constexpr int kAccStride = 256;                  // TMEM columns between the two accumulators
-  static constexpr int kGroupCols = 112;                  // columns of epilogue group 0 (group 1: the other 96)
+  static constexpr int kGroupCols = BN > 128 ? 112 : 64;  // columns of epilogue group 0 (group 1: the rest)
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiWarpBytes + kMaxTokens * 4 + 256 + 1024;
+  static_assert(kBBytes % 1024 == 0 && BN % 16 == 0 && kSmemBytes <= 232448 - 1100, "tile shape");
 };
+using PSCfg = PSCfgT<kPsBN>;
 
 __device__ __forceinline__ void reduce_splits_dyn(const float* pp, size_t stride, int splits, float (&acc)[16]) {
   switch (splits) {
@@ -959,11 +966,11 @@ __device__ __forceinline__ void reduce_splits_dyn(const float* pp, size_t stride
   }
 }
 
-template <int kAct>
-__global__ void __launch_bounds__(PSCfg::kThreads, 1)
+template <int kAct, int BN>
+__global__ void __launch_bounds__(PSCfgT<BN>::kThreads, 1)
 gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                             const GemmParams p, const int tiles_a, const int tiles_b) {
-  using C = PSCfg;
+  using C = PSCfgT<BN>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ float sq_red[2][2][4][16];      // [epilogue group][chunk parity][warp][token]
   __shared__ int last_flag[2];
@@ -1001,7 +1008,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       const int f = (int)(sk_u0 / kb_total) + i;
       if (f > (int)((sk_u1 - 1) / kb_total)) return false;
       const long long t0 = (long long)f * kb_total, t1 = t0 + kb_total;
-      it.a0 = f * kBlockM; it.b0 = sk_tb * kPsBN;
+      it.a0 = f * kBlockM; it.b0 = sk_tb * BN;
       it.kb0 = (int)(max(sk_u0, t0) - t0); it.kb1 = (int)(min(sk_u1, t1) - t0);
       it.tile_lin = f * tiles_b + sk_tb;
       const int rf = sk_rank_of(t0), rl = sk_rank_of(t1 - 1);
@@ -1013,7 +1020,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     const int tb = g % tiles_b, r = g / tiles_b;
     it.split = r % p.splits; it.nsplit = p.splits;
     const int f = r / p.splits;
-    it.a0 = f * kBlockM; it.b0 = tb * kPsBN;
+    it.a0 = f * kBlockM; it.b0 = tb * BN;
     it.kb0 = it.split * p.kb_per_split; it.kb1 = min(kb_total, it.kb0 + p.kb_per_split);
     it.tile_lin = f * tiles_b + tb;
     return true;
@@ -1068,7 +1075,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, kPsBN);
+      constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, BN);
       uint32_t cnt = 0, tl = 0;
       Item it;
       for (int ii = 0; get_item(ii, it); ++ii, ++tl) {
@@ -1095,7 +1102,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     // ===== epilogue: warp (w & 3) owns TMEM lanes 32*(w&3).., group (w - 4) / 4 owns columns [0,112) or [112,208) =====
     const int ew = warp & 3, grp = (warp - 4) >> 2;
     const int i = ew * 32 + lane;
-    const int col_begin = grp ? C::kGroupCols : 0, col_end = grp ? kPsBN : C::kGroupCols;
+    const int col_begin = grp ? C::kGroupCols : 0, col_end = grp ? BN : C::kGroupCols;
     const int bar_id = 1 + grp;
     uint8_t* stage_warp = smem_epi + (warp - 4) * C::kEpiWarpBytes;
     pdl_wait();   // residuals, norm partials and the output buffer belong to earlier kernels until here
@@ -1130,7 +1137,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       const bool fvalid = feat < p.Ma;
       const float bias = (p.bias && fvalid) ? b2f(p.bias[feat]) : 0.f;
       const bool staged = swap_staged_ok(p, a0);
-      const int ncols = min(kPsBN, p.Nb - b0);
+      const int ncols = min(BN, p.Nb - b0);
       const int my_end = min(col_end, ncols);
       if (nsplit == 1) {
 #pragma unroll 1
@@ -1158,7 +1165,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[buf]);
       } else {
-        constexpr size_t kSplitStride = (size_t)kPsBN * kBlockM;
+        constexpr size_t kSplitStride = (size_t)BN * kBlockM;
         float* part = p.ws_partial + ((size_t)tile_lin * p.splits + split) * kSplitStride + i;
 #pragma unroll 1
         for (int jc = col_begin; jc < my_end; jc += 16) {
@@ -1676,16 +1683,16 @@ int dispatch_persistent(int act, const CUtensorMap& ta, const CUtensorMap& tb, c
 }  // namespace
 
 namespace {
-template <int kAct>
+template <int kAct, int BN>
 int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_a, int tiles_b,
                            int grid_ctas, cudaStream_t stream) {
-  using C = PSCfg;
+  using C = PSCfgT<BN>;
   static bool attr_done[16] = {false};
   int dev = 0;
   AHA_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 16 && !attr_done[dev]) {
-    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct, BN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_done[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
@@ -1695,7 +1702,7 @@ int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const G
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
-  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_swap_persistent_kernel<kAct>, ta, tb, p, tiles_a, tiles_b));
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_swap_persistent_kernel<kAct, BN>, ta, tb, p, tiles_a, tiles_b));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;
@@ -1854,7 +1861,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   // Batched decoder steps (256 < tokens <= 832) on CTA pairs: opt-in (AHA_PS_PAIR=1 or force_bn = 416); the default is the
   // single-CTA persistent kernel below
   static const int use_pair = getenv("AHA_PS_PAIR") ? atoi(getenv("AHA_PS_PAIR")) : 0;   // measured slower in the step (its epilogue is not hidden): opt-in
-  if (swap && c.tokens > 256 && (use_pair || c.force_bn == 416) && c.force_bn != 208) {
+  if (swap && c.tokens > 256 && (use_pair || c.force_bn == 416) && c.force_bn != 208 && c.force_bn != 112) {
     const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, pairs = (tiles_a + 1) / 2;
     const int groups = (p.Nb + PPCfg::kGroupTokens - 1) / PPCfg::kGroupTokens;
     const int kb_total = (p.K + kBlockK - 1) / kBlockK;
@@ -1905,14 +1912,22 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
   }
   // Persistent skinny path, single CTAs (the default; force_bn = 208 selects it explicitly)
   if (swap && c.tokens > 256) {
-    const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM, tiles_b = (p.Nb + kPsBN - 1) / kPsBN;
+    const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM;
+    // token tile width: 208 for the big matrices, 112 where 208-token tiles would leave most SMs without a work item
+    static const int bn_env = getenv("AHA_PS_BN") ? atoi(getenv("AHA_PS_BN")) : 0;
+    int bn_tok = kPsBN;
+    if (c.force_bn == 112 || c.force_bn == 208) bn_tok = c.force_bn;
+    else if (bn_env == 112 || bn_env == 208) bn_tok = bn_env;
+    else if ((long)tiles_a * ((p.Nb + kPsBN - 1) / kPsBN) * 5 <= (long)w->sm_count * 3) bn_tok = 112;
+    const int tiles_b = (p.Nb + bn_tok - 1) / bn_tok;
     const int tiles = tiles_a * tiles_b;
     const int kb_total = (p.K + kBlockK - 1) / kBlockK;
     if (c.sumsq_tiles) *c.sumsq_tiles = tiles_a;
-    static const int use_sk = getenv("AHA_PS_STREAMK") ? atoi(getenv("AHA_PS_STREAMK")) : 1;
+    static const int use_sk = getenv("AHA_PS_STREAMK") ? atoi(getenv("AHA_PS_STREAMK")) : 0;   // measured slower in the step: opt-in
+    // (force_splits = -1 selects it explicitly)
     int splits = c.force_splits, kb_per = kb_total, grid_ctas = 0;
     p.sk_ranks = 0;
-    if (splits <= 0 && use_sk) {
+    if (splits == -1 || (splits == 0 && use_sk)) {
       // stream-K: every CTA carries the same number of k-blocks (see the kernel).  R ranks per token tile.
       const long long U = (long long)tiles_a * kb_total;
       int R = std::max(1, w->sm_count / tiles_b);
@@ -1921,7 +1936,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
       int cap = 1;
       for (int f = 0; f < tiles_a; ++f)
         cap = std::max(cap, rank_of((long long)(f + 1) * kb_total - 1) - rank_of((long long)f * kb_total) + 1);
-      if (cap == 1 || ((size_t)tiles * cap * kPsBN * kBlockM * sizeof(float) <= GemmWorkspace::kPartialBytes && tiles * 2 <= 4096)) {
+      if (cap == 1 || ((size_t)tiles * cap * bn_tok * kBlockM * sizeof(float) <= GemmWorkspace::kPartialBytes && tiles * 2 <= 4096)) {
         p.sk_ranks = R; splits = cap; grid_ctas = R * tiles_b;
       }
     }
@@ -1942,7 +1957,7 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
       if (splits > kb_total) splits = kb_total;
       kb_per = (kb_total + splits - 1) / splits;
       splits = (kb_total + kb_per - 1) / kb_per;
-      while (splits > 1 && ((size_t)tiles * splits * kPsBN * kBlockM * sizeof(float) > GemmWorkspace::kPartialBytes || tiles * 2 > 4096)) {
+      while (splits > 1 && ((size_t)tiles * splits * bn_tok * kBlockM * sizeof(float) > GemmWorkspace::kPartialBytes || tiles * 2 > 4096)) {
         --splits;
         kb_per = (kb_total + splits - 1) / splits;
         splits = (kb_total + kb_per - 1) / kb_per;
@@ -1957,10 +1972,14 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     }
     CUtensorMap ta, tb;
     int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
-    rc = get_tmap(b, p.Nb, p.K, ldb, kPsBN, &tb); if (rc) return rc;
+    rc = get_tmap(b, p.Nb, p.K, ldb, bn_tok, &tb); if (rc) return rc;
     ProfSlot* slot = prof_begin(5, stream);
-    rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream)
-                                    : launch_swap_persistent<GEMM_ACT_NONE>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream);
+    if (bn_tok == 112)
+      rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL, 112>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream)
+                                      : launch_swap_persistent<GEMM_ACT_NONE, 112>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream);
+    else
+      rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL, kPsBN>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream)
+                                      : launch_swap_persistent<GEMM_ACT_NONE, kPsBN>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream);
     if (slot) {
       const double out_bytes = (double)c.tokens * (c.act == GEMM_ACT_SILU_MUL ? c.features / 2 : c.features) * 2;
       prof_end(slot, stream, ((double)c.features * c.K + (double)c.tokens * c.K) * 2.0 + out_bytes,

@@ -1,6 +1,6 @@
 #!/bin/bash
 # ncu launch list of ONE steady-state batched decoder step (config 3 shapes), after the same command ran clean without ncu
-export AHA_STREAMS=${AHA_STREAMS:-8} AHA_WINDOW=8192 AHA_CACHE=sliding_window AHA_PS_PAIR=${AHA_PS_PAIR:-1}
+export AHA_STREAMS=${AHA_STREAMS:-8} AHA_WINDOW=8192 AHA_CACHE=sliding_window AHA_PS_PAIR=${AHA_PS_PAIR:-0}
 TAG=${1:-c3}
 python scripts/gpu_decoder_breakdown.py 8 > gpurun_out/${TAG}_plain.log 2>&1 &&
 AHA_NCU=1 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \

@@ -37,12 +37,15 @@ def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1, bn=0):
     (430, 3584, 2048, 0, 1),      # second token group with a single 208-token half
     (600, 1536, 8960, 3, 0),      # three token tiles, stream-K ranges across tile boundaries (49 ranks per token tile)
     (392, 3584, 18944, 3, 0),
-    (300, 256, 4096, 0, 0),       # two feature tiles only: fewer ranks than SMs
+    (300, 256, 4096, 0, -1),      # two feature tiles only: fewer ranks than SMs (stream-K)
+    (392, 3584, 18944, 0, -1),    # stream-K: 296 k-blocks per tile shared by ranges of 112
+    (600, 1536, 8960, 3, -1),
 ])
-@pytest.mark.parametrize("bn", [416, 208], ids=["cta_pair", "single_cta"])
+@pytest.mark.parametrize("bn", [416, 208, 112], ids=["cta_pair", "single_cta_208", "single_cta_112"])
 def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits, bn):
     """bn = 416: the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 weight rows x 416 tokens per pair); bn = 208: the
-    single-CTA persistent kernel (128 x 208 tiles, two accumulators)."""
+    single-CTA persistent kernel with 128 x 208 tiles (two accumulators), bn = 112: the same with 128 x 112 tiles (small
+    matrices: more work items instead of split-K).  splits = -1: stream-K decomposition."""
     torch.manual_seed(21)
     x = (torch.randn(T, K, device=cuda) * 0.5).bfloat16()
     w = (torch.randn(F_, K, device=cuda) / K ** 0.5).bfloat16()
