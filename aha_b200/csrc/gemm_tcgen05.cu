@@ -1918,7 +1918,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     int bn_tok = kPsBN;
     if (c.force_bn == 112 || c.force_bn == 208) bn_tok = c.force_bn;
     else if (bn_env == 112 || bn_env == 208) bn_tok = bn_env;
-    else if ((long)tiles_a * ((p.Nb + kPsBN - 1) / kPsBN) * 5 <= (long)w->sm_count * 3) bn_tok = 112;
+    // (short K only: with 112-token tiles every weight tile is pulled by four CTAs - down (K = 18 944) measured 87 us
+    // unsplit on 112-token tiles, at the L2 -> SM bandwidth, against 69 us on 208-token tiles split two ways)
+    else if ((long)tiles_a * ((p.Nb + kPsBN - 1) / kPsBN) * 5 <= (long)w->sm_count * 3 && (p.K + kBlockK - 1) / kBlockK <= 96) bn_tok = 112;
     const int tiles_b = (p.Nb + bn_tok - 1) / bn_tok;
     const int tiles = tiles_a * tiles_b;
     const int kb_total = (p.K + kBlockK - 1) / kBlockK;
