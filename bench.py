@@ -31,6 +31,9 @@ if ROOT not in sys.path:
 # DRAM bytes per launch of the four single-stream decoder GEMMs, from the committed ncu --set full capture
 # (profiles/r01_ncu_full_decoder_v5.txt)
 NCU_TRAFFIC_BYTES_PER_LAUNCH_C2 = (33.48e6 + 26.48e6 + 275.48e6 + 141.32e6) / 4
+# the same for the four batched launches of a config-3 layer (392 tokens; profiles/r02_ncu_full_gemm_c3.txt: qkv, o_proj,
+# gate|up, down - read + write)
+NCU_TRAFFIC_BYTES_PER_LAUNCH_C3 = (36.25e6 + 31.41e6 + 281.26e6 + 157.08e6) / 4
 VISION_BATCH = 32   # the reference embeds frames in batches of 32 (test/inference.py:181)
 N_SYS = 36
 METRIC = "aggregate frames/sec (streams sharded over N B200); p50 per-frame latency"
@@ -477,7 +480,10 @@ def roofline_leg(wl, lib, K, peaks, single_stream):
         tf = bt["flops"] / (bt["ms"] / 1e3) / 1e12 if bt["ms"] > 0 else 0.0
         roof = dict(bound="tensor", kernel="gemm_swap_persistent_kernel (batched decoder GEMMs: qkv, o_proj, gate|up, down at "
                                            f"M = {49 * ns} tokens)",
-                    achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s", frac=tf / peaks["tf_sustained"], traffic=None,
+                    achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s", frac=tf / peaks["tf_sustained"],
+                    traffic=NCU_TRAFFIC_BYTES_PER_LAUNCH_C3 if (wl.cfg.hidden_size == 3584 and ns == 8) else None,
+                    traffic_source="ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over the four launches of a layer "
+                                   "(profiles/r02_ncu_full_gemm_c3.txt); algorithmic bytes are the weights + activations once",
                     peak_source=f"{peaks['source']} sustained cuBLAS bf16", launches=bt["launches"],
                     avg_launch_us=(bt["ms"] * 1e3 / bt["launches"]) if bt["launches"] else None,
                     algorithmic_flops_per_launch=(bt["flops"] / bt["launches"]) if bt["launches"] else None,
