@@ -65,6 +65,7 @@ SIGNATURES = {
     "aha_pool": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, P]),
     "aha_rope_table": (c_int, [c_int, c_int, c_int, c_float, P, P, P]),
     "aha_attention": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_float, P]),
+    "aha_attention_noalloc": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_float, P]),
 }
 
 _lib = None

@@ -708,3 +708,103 @@ int op_attention(const AttnProblem& p_in, cudaStream_t st) {
   AHA_CHECK_LAUNCH();
   return AHA_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// aha_attention_noalloc: aha_attention for callers that must not allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  Same kernel; the key-split scratch - the parked fp32 partials and the arrival
+// counters, which op_attention takes from the per-stream workspace it cudaMallocs on first use - lives in a file-scope
+// device array that every GPU loading the library holds until exit.  No counterpart in the
+// reference.
+//   * limit: kNoAllocPartialBytes (8 MiB) of partials = (query tiles x kv heads x key splits) x (128 x head_dim + 256) x 4
+//     bytes, and at most kNoAllocCounters (query tile, kv head) groups; larger problems are rejected with a ValueError.
+//   * all calls share the one array, which keeps the previous call's contents: the counters are cleared on the stream
+//     before every launch, the partials are fully overwritten before they are read.  Calls that overlap on the GPU
+//     (different streams, or several host threads) race on it - serialise them.
+//   * no cudaMalloc / cudaFree / allocating library call on this path; the launch is not timed by aha_profile_gemm.
+constexpr size_t kNoAllocPartialBytes = 8u << 20;
+constexpr int kNoAllocCounters = 1024;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocPartialBytes + kNoAllocCounters * sizeof(int)];
+
+extern "C" int aha_attention_noalloc(const void* q, const void* k, const void* v, void* out, int heads, int kv_heads, int nq,
+                                     int klen, int head_dim, int off, float scale, void* stream) {
+  AHA_REQUIRE(q && k && v && out, "aha_attention_noalloc: NULL argument");
+  AHA_REQUIRE(heads > 0 && kv_heads > 0 && heads % kv_heads == 0 && nq > 0 && klen >= 0, "aha_attention_noalloc: bad shape");
+  AHA_REQUIRE(head_dim >= 64 && head_dim % 16 == 0 && head_dim <= 128,
+              "aha_attention_noalloc: head_dim must be in {64..128}, multiple of 16");
+  cudaStream_t st = (cudaStream_t)stream;
+  // per-device set-up with that device current: in host code the array's name is only a stand-in, the kernel needs the
+  // address cudaGetSymbolAddress returns for THIS device
+  static unsigned char* scratch_dev[16] = {nullptr};
+  static int sm_counts[16] = {0};
+  static int attr_smem[16] = {0};
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  AHA_REQUIRE(dev >= 0 && dev < 16, "aha_attention_noalloc: device index out of range");
+  if (!scratch_dev[dev]) {
+    void* ptr = nullptr;
+    AHA_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+    AHA_REQUIRE(ptr != nullptr, "aha_attention_noalloc: no device address for the scratch array");
+    AHA_CUDA(cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev));
+    scratch_dev[dev] = static_cast<unsigned char*>(ptr);
+  }
+  const int G = heads / kv_heads;
+  AttnProblem p{};
+  p.q = (const bf16*)q; p.q_rows_total = kv_heads * nq * G; p.q_ld = head_dim;
+  p.k = (const bf16*)k; p.k_rows_total = (long long)kv_heads * klen; p.k_ld = head_dim;
+  p.v = (const bf16*)v; p.v_rows_total = (long long)kv_heads * klen; p.v_ld = head_dim;
+  p.q_block_rows = nq * G; p.k_head_rows = klen;
+  p.n_blocks = kv_heads; p.nq_rows = nq * G; p.group = G; p.d = head_dim; p.d_pad = head_dim;
+  p.scale = scale; p.out = (bf16*)out; p.out_ld = heads * head_dim;
+  p.n_segs = 1;
+  p.segs[0] = AttnSeg{0, 0, 0, klen, off, 0, 0, 0, 0, nullptr, nullptr};
+
+  const int DB = (p.d_pad + 63) / 64;
+  CUtensorMap tq, tk, tv;
+  int rc = get_tmap(p.q, p.q_rows_total, p.q_ld, p.q_ld, kTile, &tq); if (rc) return rc;
+  rc = get_tmap(p.k, (int)p.k_rows_total, p.k_ld, p.k_ld, kTile, &tk); if (rc) return rc;
+  rc = get_tmap(p.v, (int)p.v_rows_total, p.v_ld, p.v_ld, kTile, &tv); if (rc) return rc;
+  const int smem = AttnSmem::total(DB);
+  if (attr_smem[dev] < smem) {
+    AHA_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_smem[dev] = smem;
+  }
+  // key-axis split as in op_attention's co-resident case; the merge is always the last arriver's (nobody waits)
+  const int q_tiles = (p.nq_rows + kTile - 1) / kTile;
+  const int ctas = q_tiles * p.n_blocks;
+  const int max_tiles = (klen + kTile - 1) / kTile;
+  int splits = 1;
+  if (ctas < sm_counts[dev] && max_tiles > 1) {
+    splits = sm_counts[dev] / ctas;
+    if (splits > 8) splits = 8;
+    if (splits > max_tiles) splits = max_tiles;
+    const int per = (max_tiles + splits - 1) / splits;
+    splits = (max_tiles + per - 1) / per;       // no empty splits
+  }
+  if (splits > 1) {
+    const size_t need = (size_t)ctas * splits * ((size_t)kTile * p.d_pad + 2 * kTile) * sizeof(float);
+    if (need > kNoAllocPartialBytes || ctas > kNoAllocCounters) {
+      aha_set_error("ValueError: aha_attention_noalloc: this problem needs " + std::to_string(need) + " bytes of key-split scratch for " +
+                    std::to_string(ctas) + " (query tile, kv head) groups; the built-in array holds " +
+                    std::to_string(kNoAllocPartialBytes) + " bytes and " + std::to_string(kNoAllocCounters) +
+                    " groups - use aha_attention");
+      return AHA_ERR_VALUE;
+    }
+    int* counters = reinterpret_cast<int*>(scratch_dev[dev] + kNoAllocPartialBytes);
+    AHA_CUDA(cudaMemsetAsync(counters, 0, (size_t)ctas * sizeof(int), st));     // must start at zero, whatever the last call left
+    p.merge_last = 1;
+    p.ws_partial = reinterpret_cast<float*>(scratch_dev[dev]);
+    p.ws_pcounters = counters;
+    p.ws_counters = nullptr; p.ws_zero = nullptr; p.ws_zero_n = 0;
+    p.kv_prefetch = 3;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(q_tiles, p.n_blocks, splits);
+  cfg.blockDim = dim3(kAttnThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cfg.attrs = nullptr; cfg.numAttrs = 0;        // (no programmatic launch: the kernel follows a memset)
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_kernel, tq, tk, tv, p, splits));
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}

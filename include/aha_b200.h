@@ -198,6 +198,16 @@ int aha_rope_table(int pos0, int q, int head_dim, float theta, void* cos_out, vo
  * [nq, heads*d]; allowed(i,j) <=> j <= off + i (pass off >= klen for no mask).  Used by the parity tests. */
 int aha_attention(const void* q, const void* k, const void* v, void* out, int heads, int kv_heads, int nq, int klen,
                   int head_dim, int off, float scale, void* stream);
+/* aha_attention for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments, same
+ * kernel and results as aha_attention; the key-split scratch (fp32 partials + arrival counters) is a fixed device array
+ * inside the library (8 MiB + 4 KiB, held by every GPU that loads the library until exit), so the call performs no
+ * cudaMalloc / cudaFree / allocating library call.  Limit: (query tiles x kv_heads x key splits) x (128 x head_dim + 256)
+ * x 4 bytes <= 8 MiB and at most 1024 (query tile, kv head) groups - ValueError beyond that (use aha_attention).  All
+ * calls share the one array, which keeps the previous call's contents (the counters are cleared on `stream` before every
+ * launch): calls that overlap on the GPU - other streams, other host threads - race on it and must be serialised. */
+int aha_attention_noalloc(const void* q, const void* k, const void* v, void* out, int heads, int kv_heads, int nq, int klen,
+                          int head_dim, int off, float scale, void* stream);
 
 #ifdef __cplusplus
 }
