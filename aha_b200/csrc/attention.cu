@@ -288,7 +288,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         mbar_wait(&s_full[it & 1], (it >> 1) & 1);
         tc_fence_after();
         dbg_stamp(ts, 3 + 2 * min(it, 1));
-        if (it == 2) { dbg_stamp(ts, 8); }
         const int col0 = half * 64;
         const uint32_t s_addr = lane_addr + ((it & 1) ? kColS1 : kColS0) + col0;
         uint32_t sv[64];
@@ -311,9 +310,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               if (!((vm >> t) & 1u)) sv[c * 32 + t] = 0xff800000u;   // -inf
           }
         }
-        float tmax = -INFINITY;
+        // four independent maximum chains (one dependent chain of 32 three-input maxima was ~260 cycles per tile, with both
+        // warps of the scheduler in it at the same time)
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-        for (int t = 0; t < 64; ++t) tmax = fmaxf(tmax, __uint_as_float(sv[t]));
+        for (int t = 0; t < 16; ++t) {
+          mx0 = fmaxf(mx0, __uint_as_float(sv[t]));
+          mx1 = fmaxf(mx1, __uint_as_float(sv[16 + t]));
+          mx2 = fmaxf(mx2, __uint_as_float(sv[32 + t]));
+          mx3 = fmaxf(mx3, __uint_as_float(sv[48 + t]));
+        }
+        float tmax = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
         {
           // row maximum over both halves: the two threads of a row then take identical rescale decisions.  The slots
           // alternate with the tile parity; the pair barrier of tile it + 1 orders their reuse at tile it + 2.
@@ -323,16 +330,18 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           tmax = fmaxf(tmax, x[(half ^ 1) * 128 + row]);
         }
         tmax *= sl2;                                 // scale > 0: max commutes with the scaling
+        // one compare decides (m_used = -inf: -inf + 8 = -inf, so any finite tmax passes; tmax = -inf never does); the whole
+        // slow path sits behind one warp vote
+        const bool rescale = tmax > m_used + kRescaleThreshold;
         float alpha = 1.f;
-        bool rescale = false;
-        if (tmax > m_used + kRescaleThreshold || (m_used == -INFINITY && tmax > -INFINITY)) {
+        if (__any_sync(0xffffffffu, rescale)) {
+        if (rescale) {
           alpha = (m_used == -INFINITY) ? 0.f : ex2_approx(m_used - tmax);
           m_used = tmax;
-          rescale = true;
         }
         // (P(it) overwrites the first half of S(it) in tensor memory: both threads of the row have their scores in registers
         // - the pair barrier above - and the P.V product that read P(it - 2) from these columns ran before Q.K^T(it) did)
-        if (it > 0 && __any_sync(0xffffffffu, rescale)) {
+        if (it > 0) {
           // O may only be rescaled between two P.V products: wait for the previous one (the MMAs complete in order) ...
           mbar_wait(&pv_done[(it - 1) & 1], ((it - 1) >> 1) & 1);
           tc_fence_after();
@@ -348,6 +357,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           tmem_st_wait();
         }
         l_sum *= alpha;
+        }
         // probabilities -> bf16 -> swizzled K-major P tile
         const float mref = (m_used == -INFINITY) ? 0.f : m_used;
         float acc_l = 0.f;
@@ -369,8 +379,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tc_fence_before();
         mbar_arrive(&p_full[it & 1]);
         dbg_stamp(ts, 4 + 2 * min(it, 1));
-        if (it == 2) { dbg_stamp(ts, 9); }
-        if (it == 1) { dbg_stamp(ts, 10); }
       }
       {
         // row sum = half 0's partial + half 1's partial, added in that order by both threads
