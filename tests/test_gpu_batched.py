@@ -124,6 +124,49 @@ def test_attention_long_keys_last_arriver_merge(cuda, nq, klen, off):
     assert (outs[0].float() - ref).abs().max().item() <= 2e-2
 
 
+@pytest.mark.parametrize("heads,kvh,nq,klen,d,off", [
+    (64, 64, 729, 729, 80, 100000),     # whole-group mode: 384 (head, query tile) groups, ragged last key tile, all visible
+    (256, 256, 729, 729, 80, 100000),   # ten groups per CTA: every pipeline runs across the group boundaries
+    (60, 60, 700, 600, 128, 0),         # causal, head_dim 128
+    (160, 160, 260, 77, 64, 100000),    # one key tile per group: Q.K^T of the next group is issued before this group's P.V
+    (28, 4, 392, 8192, 128, 8192),      # stream-K mode: 88 groups x 64 key tiles over 148 CTAs, groups shared by up to 3 CTAs
+    (28, 4, 392, 2500, 128, 2500 - 392),  # stream-K with the causal limit inside the last tiles
+    (14, 2, 520, 3000, 64, 3000),
+])
+def test_attention_persistent_kernel(cuda, monkeypatch, heads, kvh, nq, klen, d, off):
+    """The persistent kernel (attention_persistent.cu) against fp32 torch and against the one-CTA-per-tile kernel
+    (AHA_ATTN_PERSIST=0) on the same inputs; twice, for the self-resetting counters of the stream-K merge."""
+    torch.manual_seed(29)
+    G = heads // kvh
+    q = torch.randn(heads, nq, d, device=cuda).bfloat16()
+    k = torch.randn(kvh, klen, d, device=cuda).bfloat16()
+    v = torch.randn(kvh, klen, d, device=cuda).bfloat16()
+    scale = d ** -0.5
+    qg = q.view(kvh, G, nq, d).permute(0, 2, 1, 3).contiguous()
+
+    def run():
+        out = torch.full((nq, heads * d), float("nan"), dtype=torch.bfloat16, device=cuda)
+        _lib.check(_lib.load().aha_attention(_lib.ptr(qg), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), heads, kvh, nq, klen, d,
+                                             off, scale, _lib.stream_ptr()))
+        torch.cuda.synchronize()
+        return out
+
+    monkeypatch.setenv("AHA_ATTN_PERSIST", "1")
+    a, b = run(), run()
+    monkeypatch.setenv("AHA_ATTN_PERSIST", "0")
+    c = run()
+    assert torch.equal(a, b)
+    assert not torch.isnan(a.float()).any()
+    assert (a.float() - c.float()).abs().max().item() <= 1e-2
+    step = max(1, heads // 8)                                   # fp32 reference on a subset of the heads (memory)
+    for h in range(0, heads, step):
+        s = (q[h].float() @ k[h // G].float().t()) * scale
+        allowed = torch.arange(klen, device=cuda)[None, :] <= (off + torch.arange(nq, device=cuda)[:, None])
+        s = s.masked_fill(~allowed, float("-inf"))
+        ref = torch.softmax(s, -1) @ v[h // G].float()
+        assert (a[:, h * d:(h + 1) * d].float() - ref).abs().max().item() <= 2e-2, h
+
+
 @pytest.fixture(scope="module")
 def wide(cuda):
     cfg = A.config_preset("7b")
