@@ -223,7 +223,7 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
           const int s = n % kStages;
           const uint32_t ph = (n / kStages) & 1;
           if (p.kv_prefetch) prefetch_next();
-          mbar_wait(&empty[s], ph ^ 1);
+          mbar_wait_relaxed(&empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&full[s], stage_bytes);
           for (int b = 0; b < DB; ++b)
             tma_load_2d(ring + s * stage_bytes + b * kAtomBytes, tm, &full[s], col + b * 64, row0 + (it.kt0 + t) * kTile);
@@ -237,47 +237,69 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
       const uint32_t idesc_qk = make_idesc_bf16_f32(kTile, kTile);
       const uint32_t idesc_pv = make_idesc_bf16_f32_bmn(kTile, (uint32_t)p.d_pad);
       const int ksteps = p.d_pad >> 4;
+      // The chain P(n) ready -> P.V(n) -> Q.K^T(n + 2) (its score buffer is the one P(n) sits in) -> S(n + 2) ready must be
+      // shorter than the softmax of tile n + 1, or the softmax warps wait for scores (measured: 20 % of their time when
+      // this thread found out about K(n + 2) / V(n) and built its descriptors AFTER P(n) had arrived).  So everything that
+      // does not depend on P(n) happens before the wait for it; behind the wait there are only the MMA and commit issues.
       int qi = 0, qt_in = 0, nq = 0;          // the next Q.K^T: item, tile inside the item, global tile index
-      auto issue_qk = [&]() {
-        if (qt_in == 0) { mbar_wait(&q_full[qi & 1], (qi >> 1) & 1); }
-        const int s = nq % kStages;
-        mbar_wait(&k_full[s], (nq / kStages) & 1);
-        tc_fence_after();
-        const uint32_t ka = smem_u32(sK + s * stage_bytes);
-        const uint32_t qa = tmem_base + kColQ + (uint32_t)(qi & 1) * 64u;
-        for (int ks = 0; ks < ksteps; ++ks) {
-          const uint32_t o = (uint32_t)(ks >> 2) * kAtomBytes + (uint32_t)(ks & 3) * 32;
-          umma_f16_ts(tmem_base + ((nq & 1) ? kColS1 : kColS0), qa + (uint32_t)ks * 8u, make_kmajor_sw128_desc(ka + o),
-                      idesc_qk, ks != 0);
+      uint32_t qk_ka = 0, qk_qa = 0; int qk_s = 0;
+      auto qk_prepare = [&]() {
+        qk_s = nq % kStages;
+        mbar_wait(&k_full[qk_s], (nq / kStages) & 1);
+        qk_ka = smem_u32(sK + qk_s * stage_bytes);
+        qk_qa = tmem_base + kColQ + (uint32_t)(qi & 1) * 64u;
+      };
+      auto qk_fire = [&]() {
+        // (Q of a new item: loaded an item ahead, so this wait normally falls through.  It cannot move in front of P.V(n): with
+        // one-tile items Q(i + 2) is loaded after the epilogue of item i, which needs P.V(n) itself)
+        if (qt_in == 0) { mbar_wait(&q_full[qi & 1], (qi >> 1) & 1); tc_fence_after(); }
+        const uint64_t d0 = make_kmajor_sw128_desc(qk_ka);
+        const uint32_t sd = tmem_base + ((nq & 1) ? kColS1 : kColS0);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          if (ks < ksteps) {
+            // 64-column atom ks >> 2 (kAtomBytes apart), 32 bytes per K = 16 step inside it; the address field counts 16 B
+            const uint64_t o = (uint64_t)((ks >> 2) * (kAtomBytes >> 4) + (ks & 3) * 2);
+            umma_f16_ts(sd, qk_qa + (uint32_t)ks * 8u, d0 + o, idesc_qk, ks != 0);
+          }
         }
-        umma_commit(&k_empty[s]);      // the K stage is free once these MMAs have read it
+        umma_commit(&k_empty[qk_s]);      // the K stage is free once these MMAs have read it
         umma_commit(&s_full[nq & 1]);
         ++nq;
         if (++qt_in == items[qi].nkt) { qt_in = 0; ++qi; }
       };
-      issue_qk();
+      qk_prepare(); tc_fence_after(); qk_fire();                              // S(0)
+      if (qi < n_items) { qk_prepare(); tc_fence_after(); qk_fire(); }        // S(1)
       int np = 0;
+      long long m_pre = 0, m_pwait = 0, m_fire = 0;   // bring-up: cycles in the early waits / waiting for P / issuing
       for (int pi = 0; pi < n_items; ++pi) {
         const int nkt = items[pi].nkt;
         for (int t = 0; t < nkt; ++t, ++np) {
-          if (qi < n_items) issue_qk();          // scores of the next tile (possibly the next item's first) before this P.V
           const int s = np % kStages;
+          const long long c0 = ts ? clock64() : 0;
           mbar_wait(&v_full[s], (np / kStages) & 1);
-          mbar_wait(&p_full[np & 1], (np >> 1) & 1);
           if (t == 0 && pi > 0) mbar_wait(o_free, (pi - 1) & 1);    // the previous item's O has left tensor memory
-          tc_fence_after();
-          const uint32_t va = smem_u32(sV + s * stage_bytes);
+          const bool more = qi < n_items;
+          if (more) qk_prepare();                                   // K(n + 2) (and Q of a new item) are there
+          // V tile is MN-major: 64-column blocks kAtomBytes apart (LBO), 8-key groups 1024 B apart (SBO); one K = 16 step
+          // (16 keys) is 2048 bytes further
+          const uint64_t dv0 = make_mnmajor_sw128_desc(smem_u32(sV + s * stage_bytes), kAtomBytes, 1024);
           const uint32_t pt = tmem_base + ((np & 1) ? kColS1 : kColS0);     // P(n) sits in the first 64 columns of S(n)
-          for (int ks = 0; ks < kTile / 16; ++ks) {
-            // V tile is MN-major: 64-column blocks kAtomBytes apart (LBO), 8-key groups 1024 B apart (SBO)
-            const uint64_t db = make_mnmajor_sw128_desc(va + (uint32_t)ks * 2048, kAtomBytes, 1024);
-            umma_f16_ts(tmem_base + kColO, pt + (uint32_t)ks * 8u, db, idesc_pv, (t | ks) != 0);
-          }
+          const long long c1 = ts ? clock64() : 0;
+          mbar_wait(&p_full[np & 1], (np >> 1) & 1);
+          const long long c2 = ts ? clock64() : 0;
+          tc_fence_after();
+#pragma unroll
+          for (int ks = 0; ks < kTile / 16; ++ks)
+            umma_f16_ts(tmem_base + kColO, pt + (uint32_t)ks * 8u, dv0 + (uint64_t)(ks * (2048 >> 4)), idesc_pv, (t | ks) != 0);
           umma_commit(&v_empty[s]);
           umma_commit(&pv_done[np & 1]);
           if (t == nkt - 1) umma_commit(o_full);
+          if (more) qk_fire();                                      // S(n + 2): executes behind P.V(n) (issue order)
+          if (ts) { const long long c3 = clock64(); m_pre += c1 - c0; m_pwait += c2 - c1; m_fire += c3 - c2; }
         }
       }
+      if (ts) { ts[19] = (unsigned long long)m_pre; ts[20] = (unsigned long long)m_pwait; ts[21] = (unsigned long long)m_fire; }
     }
   } else if (warp >= 4 && warp < 12) {
     // ===================== online softmax =====================
@@ -290,6 +312,7 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
     const float sl2 = p.scale * 1.4426950408889634f;
     const int col0 = half * 64;
     unsigned long long* ts1 = threadIdx.x == 128 ? ts : nullptr;
+    long long t_prev = 0, acc_wait = 0, acc_work = 0;       // bring-up: cycles waited for scores / spent on tiles (thread 128)
     int n = 0;
     for (int i = 0; i < n_items; ++i) {
       const Item item = items[i];
@@ -301,8 +324,10 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
       for (int t = 0; t < item.nkt; ++t, ++n) {
         const uint32_t s_base = lane_addr + ((n & 1) ? kColS1 : kColS0);
         const int kt = item.kt0 + t;
+        const long long w0 = ts1 ? clock64() : 0;
         mbar_wait(&s_full[n & 1], (n >> 1) & 1);
         tc_fence_after();
+        if (ts1) { const long long w1 = clock64(); acc_wait += w1 - w0; if (t_prev) acc_work += w0 - t_prev; t_prev = w1; }
         if (t == 0 && i < 6) dbg_stamp(ts1, 2 + i);
         uint32_t sv[64];
         tmem_ld_32x32b_x32p(s_base + col0, sv);
@@ -400,6 +425,7 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
       if (half == 0) st[256 + row] = m_used;
       mbar_arrive(&stats_full[b]);
     }
+    if (ts1) { ts1[16] = (unsigned long long)acc_wait; ts1[17] = (unsigned long long)acc_work; ts1[18] = (unsigned long long)n; }
   } else if (warp >= 12) {
     // ===================== Q loader + epilogue: one thread per query row =====================
     const int ew = warp & 3;
@@ -417,15 +443,17 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
       const uint32_t qaddr = lane_addr + kColQ + (uint32_t)(i & 1) * 64u;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        uint32_t qv[32];
+        uint32_t qa[16], qb[16];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          uint4 u = make_uint4(0u, 0u, 0u, 0u);
+        for (int c = 0; c < 4; ++c) {
+          uint4 u = make_uint4(0u, 0u, 0u, 0u), w = make_uint4(0u, 0u, 0u, 0u);
           if (rv && h * 64 + c * 8 < p.d_pad) u = *reinterpret_cast<const uint4*>(qsrc + h * 64 + c * 8);
-          qv[4 * c] = u.x; qv[4 * c + 1] = u.y; qv[4 * c + 2] = u.z; qv[4 * c + 3] = u.w;
+          if (rv && h * 64 + 32 + c * 8 < p.d_pad) w = *reinterpret_cast<const uint4*>(qsrc + h * 64 + 32 + c * 8);
+          qa[4 * c] = u.x; qa[4 * c + 1] = u.y; qa[4 * c + 2] = u.z; qa[4 * c + 3] = u.w;
+          qb[4 * c] = w.x; qb[4 * c + 1] = w.y; qb[4 * c + 2] = w.z; qb[4 * c + 3] = w.w;
         }
-        tmem_st_32x32b_x16(qaddr + h * 32, *reinterpret_cast<uint32_t(*)[16]>(&qv[0]));
-        tmem_st_32x32b_x16(qaddr + h * 32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&qv[16]));
+        tmem_st_32x32b_x16(qaddr + h * 32, qa);
+        tmem_st_32x32b_x16(qaddr + h * 32 + 16, qb);
       }
       tmem_st_wait();
       tc_fence_before();
@@ -441,7 +469,7 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
       const bool row_valid = m < p.nq_rows;
       const int tok = m / p.group;
       const int b = i & 1;
-      mbar_wait(&stats_full[b], (i >> 1) & 1);
+      mbar_wait_relaxed(&stats_full[b], (i >> 1) & 1, 400);
       if (i == 2) dbg_stamp(ts2, 15);
       const float* st = stats + b * 384;
       const float l_sum = st[row] + st[128 + row];      // half 0's partial + half 1's, in that order
@@ -454,26 +482,32 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
       const bool vec_ok = (p.d & 7) == 0 && (p.out_ld & 7) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
       if (item.parts == 1) {
         const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
+        // 32 columns per tensor-memory round trip (next to the running MMAs, which read P and Q from tensor memory, one
+        // tcgen05.ld round trip is ~300 cycles; O - and with it the next item's first P.V - stays locked until the last one)
 #pragma unroll 1
-        for (int cc = 0; cc < p.d_pad; cc += 16) {
-          uint32_t r[16];
-          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+        for (int c0 = 0; c0 < p.d_pad; c0 += 32) {
+          uint32_t r[32];
+          const int ncol = min(32, p.d_pad - c0);          // 16 or 32
+          if (ncol == 32) tmem_ld_32x32b_x32p(lane_addr + kColO + c0, r);
+          else tmem_ld_32x32b_x16p(lane_addr + kColO + c0, r);
           tmem_ld_wait();
-          if (cc + 16 >= p.d_pad) { tc_fence_before(); mbar_arrive(o_free); }   // O is in registers: the next item's P.V may start
+          if (c0 + 32 >= p.d_pad) { tc_fence_before(); mbar_arrive(o_free); }   // O is in registers: the next item's P.V may start
           if (row_valid) {
-            float v[16];
 #pragma unroll
-            for (int u = 0; u < 16; ++u) v[u] = __uint_as_float(r[u]) * inv;
+            for (int g = 0; g < 4; ++g) {
+              const int c8 = c0 + g * 8;
+              if (g * 8 < ncol) {
+                float v[8];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const int c8 = cc + h * 8;
-              if (vec_ok && c8 + 8 <= p.d) {
-                st_v4(orow + c8, make_uint4(pack_bf16x2(v[8 * h], v[8 * h + 1]), pack_bf16x2(v[8 * h + 2], v[8 * h + 3]),
-                                            pack_bf16x2(v[8 * h + 4], v[8 * h + 5]), pack_bf16x2(v[8 * h + 6], v[8 * h + 7])));
-              } else {
-#pragma unroll 4
-                for (int u = 0; u < 8; ++u)
-                  if (c8 + u < p.d) orow[c8 + u] = f2b(v[8 * h + u]);
+                for (int u = 0; u < 8; ++u) v[u] = __uint_as_float(r[g * 8 + u]) * inv;
+                if (vec_ok && c8 + 8 <= p.d) {
+                  st_v4(orow + c8, make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                                              pack_bf16x2(v[6], v[7])));
+                } else {
+#pragma unroll
+                  for (int u = 0; u < 8; ++u)
+                    if (c8 + u < p.d) orow[c8 + u] = f2b(v[u]);
+                }
               }
             }
           }
@@ -485,14 +519,17 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
         float* grp = p.ws_partial + (size_t)item.group_lin * kMaxParts * cta_floats;
         float* mine = grp + (size_t)item.part * cta_floats;
 #pragma unroll 1
-        for (int cc = 0; cc < p.d_pad; cc += 16) {
-          uint32_t r[16];
-          tmem_ld_32x32b_x16(lane_addr + kColO + cc, r);
+        for (int c0 = 0; c0 < p.d_pad; c0 += 32) {
+          uint32_t r[32];
+          const int ncol = min(32, p.d_pad - c0);
+          if (ncol == 32) tmem_ld_32x32b_x32p(lane_addr + kColO + c0, r);
+          else tmem_ld_32x32b_x16p(lane_addr + kColO + c0, r);
           tmem_ld_wait();
-          if (cc + 16 >= p.d_pad) { tc_fence_before(); mbar_arrive(o_free); }
-          float* dst = mine + (size_t)cc * kTile + row;      // a warp's store of one column is one 128-byte segment
+          if (c0 + 32 >= p.d_pad) { tc_fence_before(); mbar_arrive(o_free); }
+          float* dst = mine + (size_t)c0 * kTile + row;      // a warp's store of one column is one 128-byte segment
 #pragma unroll
-          for (int u = 0; u < 16; ++u) __stcg(dst + (size_t)u * kTile, __uint_as_float(r[u]));
+          for (int u = 0; u < 32; ++u)
+            if (u < ncol) __stcg(dst + (size_t)u * kTile, __uint_as_float(r[u]));
         }
         __stcg(mine + (size_t)kTile * p.d_pad + row, m_used);
         __stcg(mine + (size_t)kTile * p.d_pad + kTile + row, l_sum);
@@ -584,10 +621,10 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
 }  // namespace
 
 static unsigned long long* g_pattn_ts = nullptr;
-extern "C" int aha_debug_attention_persistent_timeline(unsigned long long* out16) {
+extern "C" int aha_debug_attention_persistent_timeline(unsigned long long* out32) {
   if (!g_pattn_ts) { aha_set_error("ValueError: run with AHA_TS=2"); return AHA_ERR_VALUE; }
   AHA_CUDA(cudaDeviceSynchronize());
-  AHA_CUDA(cudaMemcpy(out16, g_pattn_ts, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  AHA_CUDA(cudaMemcpy(out32, g_pattn_ts, 32 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return AHA_OK;
 }
 
@@ -664,7 +701,8 @@ int op_attention_persistent(const AttnProblem& p_in, cudaStream_t st) {
   static const bool want_ts = getenv("AHA_TS") && atoi(getenv("AHA_TS")) == 2;
   p.dbg_ts = nullptr;
   if (want_ts) {
-    if (!g_pattn_ts) { AHA_CUDA(cudaMalloc(&g_pattn_ts, 16 * sizeof(unsigned long long))); AHA_CUDA(cudaMemset(g_pattn_ts, 0, 128)); }
+    if (!g_pattn_ts) { AHA_CUDA(cudaMalloc(&g_pattn_ts, 32 * sizeof(unsigned long long))); }
+    AHA_CUDA(cudaMemsetAsync(g_pattn_ts, 0, 256, st)); { }
     p.dbg_ts = g_pattn_ts;
   }
   cudaLaunchConfig_t cfg{};

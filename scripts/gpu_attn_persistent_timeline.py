@@ -17,8 +17,11 @@ for which, (heads, kvh, nq, klen, d, off) in (("vision", (512, 512, 729, 729, 80
         _lib.check(lib.aha_attention(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), heads, kvh, nq, klen, d, off, d ** -0.5,
                                      _lib.stream_ptr()))
     torch.cuda.synchronize()
-    a = (ctypes.c_ulonglong * 16)()
+    a = (ctypes.c_ulonglong * 32)()
     _lib.check(lib.aha_debug_attention_persistent_timeline(a))
     t = list(a)
     names = ["ready", "pdl"] + [f"S0 of item {i}" for i in range(6)] + [f"epilogue {i} done" for i in range(6)] + ["o_full(2) seen", "stats(2) seen"]
-    print(which, {n: x - t[0] for n, x in zip(names, t) if x})
+    print(which, {n: x - t[0] for n, x in zip(names, t[:16]) if x})
+    n = max(1, t[18])
+    print(f"   per tile ({n} tiles): softmax thread 128 waits {t[16] / n:.0f} cycles for scores, works {t[17] / n:.0f}; MMA thread: early waits {t[19] / n:.0f}, "
+          f"waits for P {t[20] / n:.0f}, issues P.V + Q.K^T {t[21] / n:.0f}")
