@@ -75,49 +75,61 @@ __device__ __noinline__ uint32_t visible_mask32(const AttnSeg& seg, int p0, int 
   return vm;
 }
 
-// This CTA's work list.  mode 0: groups [c NG / G, (c + 1) NG / G), whole key axes.  mode 1: units [c U / G, (c + 1) U / G)
-// of the (group, key tile) sequence; a group cut by a range boundary is shared with the neighbouring CTAs.
+// This CTA's work list.  Both decompositions keep the CTAs that run AT THE SAME TIME on neighbouring data, like the wave
+// order of a plain grid does: the tower's q/k/v buffer (161 MB for 32 frames) and the KV windows of eight streams (134 MB
+// per layer) are larger than the L2, and every K / V tile is wanted by all query tiles of its head.  (Contiguous group
+// ranges per CTA had 148 heads from all over the buffer in flight: 712 MB of DRAM reads per launch instead of 179 MB.)
+//   mode 0: groups c, c + G, c + 2 G, ... (G = grid size): the 148 groups in flight are ~25 neighbouring heads, the six query
+//           tiles of a head run side by side and share its K / V through the L2.
+//   mode 1: the CTAs form q_tiles teams (team = c mod q_tiles takes query tile `team` of every (segment, kv head)); inside a
+//           team the (segment, kv head, key tile) units are dealt as equal contiguous ranges (stream-K).  Rank r of every team
+//           walks the same keys at the same time, so a K / V tile comes from DRAM once; a (segment, kv head) cut by a range
+//           boundary is shared with the neighbouring ranks and merged by its last part.
 __device__ __forceinline__ int build_items(const AttnProblem& p, const AttnPersistPlan& pl, Item* items, int lane) {
   const int G = (int)gridDim.x, c = (int)blockIdx.x;
   int count = 0;
   if (pl.mode == 0) {
-    const int g0 = (int)((long long)c * pl.n_groups / G), g1 = (int)((long long)(c + 1) * pl.n_groups / G);
-    count = min(g1 - g0, kMaxItems);
+    count = c < pl.n_groups ? min((pl.n_groups - 1 - c) / G + 1, kMaxItems) : 0;
     for (int j = lane; j < count; j += 32) {
-      const int g = g0 + j;
+      const int g = c + j * G;
       const int seg = g / pl.gps, rem = g - seg * pl.gps;
       const int blk = rem / pl.q_tiles, qt = rem - blk * pl.q_tiles;
       Item it{seg, blk, qt, 0, (p.segs[seg].klen + kTile - 1) / kTile, 1, 0, g};
       items[j] = it;
     }
   } else {
+    const int R = G / pl.q_tiles, team = c % pl.q_tiles, rank = c / pl.q_tiles;
     const long long U = pl.units;
-    const int u0 = (int)((long long)c * U / G), u1 = (int)((long long)(c + 1) * U / G);
-    if (u0 < u1) {
-      int s0 = 0;
-      while (s0 + 1 < p.n_segs && pl.unit_base[s0 + 1] <= u0) ++s0;
-      const int T0 = (p.segs[s0].klen + kTile - 1) / kTile;
-      const int g_first = s0 * pl.gps + (u0 - pl.unit_base[s0]) / T0;
-      for (int r = 0; r < kMaxItems / 32; ++r) {
-        const int j = r * 32 + lane;
-        const int g = g_first + j;
-        bool valid = g < pl.n_groups;
-        Item it{0, 0, 0, 0, 0, 1, 0, g};
-        if (valid) {
-          const int seg = g / pl.gps, rem = g - seg * pl.gps;
-          const int T = (p.segs[seg].klen + kTile - 1) / kTile;
-          const int gs = pl.unit_base[seg] + rem * T, ge = gs + T;
-          valid = gs < u1;
+    if (rank < R) {
+      const int u0 = (int)((long long)rank * U / R), u1 = (int)((long long)(rank + 1) * U / R);
+      if (u0 < u1) {
+        int s0 = 0;
+        while (s0 + 1 < p.n_segs && pl.unit_base[s0 + 1] <= u0) ++s0;
+        const int T0 = (p.segs[s0].klen + kTile - 1) / kTile;
+        const int sg_first = s0 * p.n_blocks + (u0 - pl.unit_base[s0]) / T0;       // (segment, kv head) pairs in unit order
+        const int n_sg = p.n_segs * p.n_blocks;
+        for (int r = 0; r < kMaxItems / 32; ++r) {
+          const int j = r * 32 + lane;
+          const int sg = sg_first + j;
+          bool valid = sg < n_sg;
+          Item it{0, 0, 0, 0, 0, 1, 0, 0};
           if (valid) {
-            const int a = max(gs, u0), b = min(ge, u1);
-            const int first_cta = (int)(((long long)(gs + 1) * G + U - 1) / U) - 1;
-            const int last_cta = (int)(((long long)ge * G + U - 1) / U) - 1;
-            it.seg = seg; it.blk = rem / pl.q_tiles; it.qt = rem - it.blk * pl.q_tiles;
-            it.kt0 = a - gs; it.nkt = b - a; it.parts = last_cta - first_cta + 1; it.part = c - first_cta;
-            items[j] = it;
+            const int seg = sg / p.n_blocks, blk = sg - seg * p.n_blocks;
+            const int T = (p.segs[seg].klen + kTile - 1) / kTile;
+            const int gs = pl.unit_base[seg] + blk * T, ge = gs + T;
+            valid = gs < u1;
+            if (valid) {
+              const int a = max(gs, u0), b = min(ge, u1);
+              const int first_rank = (int)(((long long)(gs + 1) * R + U - 1) / U) - 1;
+              const int last_rank = (int)(((long long)ge * R + U - 1) / U) - 1;
+              it.seg = seg; it.blk = blk; it.qt = team;
+              it.kt0 = a - gs; it.nkt = b - a; it.parts = last_rank - first_rank + 1; it.part = rank - first_rank;
+              it.group_lin = sg * pl.q_tiles + team;
+              items[j] = it;
+            }
           }
+          count += __popc(__ballot_sync(0xffffffffu, valid));
         }
-        count += __popc(__ballot_sync(0xffffffffu, valid));
       }
     }
   }
@@ -652,7 +664,7 @@ int op_attention_persistent(const AttnProblem& p_in, cudaStream_t st) {
     max_tiles = T > max_tiles ? T : max_tiles;
     min_tiles = T < min_tiles ? T : min_tiles;
     pl.unit_base[i] = (int)units;
-    units += (long long)pl.gps * T;
+    units += (long long)p_in.n_blocks * T;      // per team (one query tile of every (segment, kv head))
   }
   pl.unit_base[p_in.n_segs] = (int)units;
   if (units >= (1ll << 30)) return 0;
@@ -664,11 +676,13 @@ int op_attention_persistent(const AttnProblem& p_in, cudaStream_t st) {
     grid = pl.n_groups < sm_count ? pl.n_groups : sm_count;
     if ((pl.n_groups + grid - 1) / grid > kMaxItems) return 0;
     pl.mode = 0;
-  } else if (!p_in.no_split && (max_tiles >= 16 || force_mode == 1) && units >= 2ll * sm_count) {
-    // few groups with long key axes: equal unit ranges (stream-K)
+  } else if (!p_in.no_split && (max_tiles >= 16 || force_mode == 1) && pl.q_tiles <= sm_count / 4 &&
+             units * pl.q_tiles >= 2ll * sm_count) {
+    // few groups with long key axes: teams of CTAs, equal unit ranges inside a team (stream-K)
     grid = sm_count;
-    const int L = (int)(units / grid);                    // shortest range
-    const int Lmax = (int)((units + grid - 1) / grid);    // longest range
+    const int R = grid / pl.q_tiles;                      // ranks per team
+    const int L = (int)(units / R);                       // shortest range
+    const int Lmax = (int)((units + R - 1) / R);          // longest range
     if (L < 1) return 0;
     const int parts = (max_tiles - 1 + L - 1) / L + 1;
     if (parts > kMaxParts) return 0;

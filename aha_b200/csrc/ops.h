@@ -75,11 +75,12 @@ int op_attention(const AttnProblem& p, cudaStream_t st);
 // attention_persistent.cu: work decomposition of the persistent kernel (filled in by op_attention_persistent)
 struct AttnPersistPlan {
   int mode;          // 0: every CTA takes a contiguous range of whole (segment, block, query tile) groups;
-                     // 1: stream-K - equal contiguous ranges of (group, key tile) units, split groups merged by the last part
+                     // 1: stream-K - one team of CTAs per query tile, equal contiguous ranges of (segment, kv head, key tile)
+                     //    units inside a team, split groups merged by the last part
   int q_tiles;       // query tiles per (segment, block)
   int gps;           // groups per segment = n_blocks * q_tiles
   int n_groups;      // n_segs * gps
-  int units;         // mode 1: key tiles summed over all groups
+  int units;         // mode 1: key tiles summed over all (segment, kv head) pairs = the units of ONE team (query tile)
   int unit_base[33]; // mode 1: first unit of segment s
 };
 // returns 1 when the launch was taken (enqueued), 0 when this shape stays with attention.cu, < 0 on errors
