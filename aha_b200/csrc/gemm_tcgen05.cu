@@ -796,7 +796,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 // ---------------------------------------------------------------------------------------------------------------------
 template <int BN>
 struct PCfg {
-  static constexpr int kStages = 3;
+  // 128 x 192 tiles consume a k-block in 384 tensor-pipe cycles: three stages are 0.6 us of look-ahead, less than an L2
+  // round trip under load (the tower's qkv GEMM ran at 0.57 of the sustained peak where the 256-wide fc2 reaches 0.99)
+  static constexpr int kStages = BN <= 192 ? 4 : 3;
   static constexpr int kABytes = kBlockM * kBlockK * 2;
   static constexpr int kBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;

@@ -65,3 +65,15 @@ if os.environ.get("AHA_TS") == "1":
         acc, ex = (a[:, 0] - t0) / 1e3, (a[:, 1] - t0) / 1e3
         q = lambda v: [round(float(x), 2) for x in np.percentile(v, [0, 25, 50, 75, 100])]
         print(f"gemm grid.x={gx[i]} splits={gz[i]} ({len(a)} CTAs) us after the first accumulator: accum done min/q1/med/q3/max {q(acc)}  exit {q(ex)}")
+
+if os.environ.get("AHA_TS") == "2":
+    import ctypes
+    lib = A._lib.load()
+    a = (ctypes.c_ulonglong * 32)()
+    A._lib.check(lib.aha_debug_attention_persistent_timeline(a))
+    t = list(a)
+    names = ["ready", "pdl"] + [f"S0 of item {i}" for i in range(6)] + [f"epilogue {i} done" for i in range(6)] + ["o_full(2) seen", "stats(2) seen"]
+    print("persistent attention CTA 0, cycles:", {k: x - t[0] for k, x in zip(names, t[:16]) if x})
+    nt = max(1, t[18])
+    print(f"   per tile ({nt} tiles): softmax thread 128 waits {t[16] / nt:.0f} cycles for scores, works {t[17] / nt:.0f}; MMA thread: early waits "
+          f"{t[19] / nt:.0f}, waits for P {t[20] / nt:.0f}, issues P.V + Q.K^T {t[21] / nt:.0f}")
