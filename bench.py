@@ -511,14 +511,14 @@ def roofline_leg(wl, lib, K, peaks, single_stream):
                                    launches=tall["launches"], ms_per_frame=tall["ms"] / (n * ns))
     if va["ms"] > 0 and va["launches"]:
         tf = va["flops"] / (va["ms"] / 1e3) / 1e12
-        roof["vision_attention"] = dict(bound="tensor", kernel="attention_kernel (SigLIP: 729 x 729 x 72, 16 heads x 32 frames per launch)",
+        roof["vision_attention"] = dict(bound="tensor", kernel="attention_persistent_kernel (SigLIP: 729 x 729 x 72, 16 heads x 32 frames per launch; attention_kernel for batches under two waves)",
                                         achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s", frac=tf / peaks["tf_sustained"],
                                         launches=va["launches"], avg_launch_us=va["ms"] * 1e3 / va["launches"],
                                         ms_per_frame=va["ms"] / (n * ns))
     if ca["ms"] > 0 and ca["launches"]:
         tf = ca["flops"] / (ca["ms"] / 1e3) / 1e12
         roof["chunk_attention"] = dict(bound="tensor" if not single_stream else "latency",
-                                       kernel=f"attention_kernel (49-token frame chunks x 7 query heads per kv head of {ns} stream(s) "
+                                       kernel=f"{'attention_persistent_kernel' if ns > 1 else 'attention_kernel'} (49-token frame chunks x 7 query heads per kv head of {ns} stream(s) "
                                               f"against {wl.window} cached keys, one launch per layer)",
                                        launches=ca["launches"], avg_launch_us=ca["ms"] * 1e3 / ca["launches"],
                                        achieved=tf, peak=peaks["tf_sustained"], unit="TFLOP/s", frac=tf / peaks["tf_sustained"],
