@@ -55,6 +55,7 @@ SIGNATURES = {
     "aha_find_ticks": (c_int, [P, c_int, c_int, c_double, c_int, P, P, c_int, P, P, P, P]),
     "aha_greedy_pick": (c_int, [P, c_int, P, c_int, c_float, P, P, P]),
     "aha_fuse_scores": (c_int, [P, P, P, c_longlong, c_double, c_double, c_double, c_double, P, P]),
+    "aha_knapsack_words": (c_int, [c_int]),
     "aha_knapsack_select": (c_int, [P, P, P, c_int, c_int, c_int, c_double, c_double, c_double, P, P, P]),
     "aha_highlight_mask": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P]),
     "aha_gemm_bf16": (c_int, [P, c_int, c_int, P, c_int, c_int, c_int, P, c_int, c_int, c_int, c_int, P, P, c_int, c_int,

@@ -4,8 +4,8 @@
 //   fuse_scores        test/grid_search.py:58-65 (and :95-104): alpha*inf + beta*rel, minus (unc - thr)*eps when unc >= thr
 //   knapsack_select    test/highlight_generator.py:8-37: 0/1 knapsack, every frame costs 1, value = inf*alpha + rel*beta +
 //                      unc*epsilon; the DP recurrence and the backtracking rule `dp[i][c] != dp[i-1][c]` are evaluated
-//                      exactly (one warp per stream: lane j owns budget j, a 32-bit decision word per frame replaces the
-//                      (n+1) x (budget+1) table)
+//                      exactly (one warp per stream: lane j owns the budgets j + 32 w, W 32-bit decision words per frame
+//                      replace the (n+1) x (budget+1) table; any budget up to 1023)
 //   highlight_mask     test/highlight_generator.py:76-86: every selected frame widened to [gt - half, gt + half] clipped
 //                      to [0, last_frame]
 #include "ops.h"
@@ -24,23 +24,35 @@ __global__ void fuse_scores_kernel(const double* __restrict__ inf, const double*
   }
 }
 
-// one warp per stream; lane j holds dp[i][j] for budget j (j <= budget <= 31)
+// one warp per stream; lane j holds dp[i][b] for the budgets b = j + 32 w, w < W (W decision words per frame: bit j of word w
+// says dp[i][j + 32 w] != dp[i-1][j + 32 w]).  dp[i-1][b-1] sits in the lane below, or - for lane 0 - in lane 31 of word w - 1.
+template <int W>
 __global__ void knapsack_kernel(const double* __restrict__ inf, const double* __restrict__ rel,
                                 const double* __restrict__ unc, int n_streams, int T, int budget, double alpha, double beta,
                                 double eps, uint32_t* __restrict__ bits, uint8_t* __restrict__ selected) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= n_streams) return;
   const size_t base = (size_t)warp * T;
-  double dp = 0.0;   // dp[0][j] = 0
+  double dp[W];
+#pragma unroll
+  for (int w = 0; w < W; ++w) dp[w] = 0.0;   // dp[0][b] = 0
   for (int i = 0; i < T; ++i) {
     const double value = __dadd_rn(__dadd_rn(__dmul_rn(inf[base + i], alpha), __dmul_rn(rel[base + i], beta)),
                                    __dmul_rn(unc[base + i], eps));
-    const double left = __shfl_up_sync(0xffffffffu, dp, 1);            // dp[i-1][j-1]
-    double nd = dp;
-    if (lane >= 1 && lane <= budget) nd = fmax(dp, __dadd_rn(left, value));   // cost 1 <= j
-    const uint32_t word = __ballot_sync(0xffffffffu, nd != dp);        // bit j: dp[i][j] != dp[i-1][j]
-    if (lane == 0) bits[base + i] = word;
-    dp = nd;
+    double carry = 0.0;                                                  // dp[i-1][32 w - 1] for lane 0
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const double up = __shfl_up_sync(0xffffffffu, dp[w], 1);
+      const double top = __shfl_sync(0xffffffffu, dp[w], 31);
+      const double left = lane == 0 ? carry : up;                        // dp[i-1][b-1]
+      const int bud = lane + 32 * w;
+      double nd = dp[w];
+      if (bud >= 1 && bud <= budget) nd = fmax(dp[w], __dadd_rn(left, value));   // cost 1 <= b
+      const uint32_t word = __ballot_sync(0xffffffffu, nd != dp[w]);     // bit j: dp[i][b] != dp[i-1][b]
+      if (lane == 0) bits[(base + i) * W + w] = word;
+      carry = top;
+      dp[w] = nd;
+    }
   }
   __syncwarp();
   // backtracking (sequential, lane 0); the other lanes clear the output first
@@ -49,9 +61,17 @@ __global__ void knapsack_kernel(const double* __restrict__ inf, const double* __
   if (lane == 0) {
     int rc = budget;
     for (int i = T - 1; i >= 0; --i) {
-      if ((bits[base + i] >> rc) & 1u) { selected[base + i] = 1; --rc; }
+      if ((bits[(base + i) * W + (rc >> 5)] >> (rc & 31)) & 1u) { selected[base + i] = 1; --rc; }
     }
   }
+}
+
+template <int W>
+void launch_knapsack(const double* inf, const double* rel, const double* unc, int n_streams, int T, int budget, double alpha,
+                     double beta, double eps, uint32_t* bits, uint8_t* selected, cudaStream_t st) {
+  const int warps_per_block = 4;
+  knapsack_kernel<W><<<(n_streams + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
+      inf, rel, unc, n_streams, T, budget, alpha, beta, eps, bits, selected);
 }
 
 __global__ void highlight_mask_kernel(const uint8_t* __restrict__ selected, const int32_t* __restrict__ gt_frames, int T,
@@ -70,6 +90,12 @@ __global__ void highlight_mask_kernel(const uint8_t* __restrict__ selected, cons
 
 extern "C" {
 
+int aha_knapsack_words(int max_duration) {
+  int w = 1;
+  while (w * 32 < max_duration + 1 && w < 32) w *= 2;
+  return w;
+}
+
 int aha_fuse_scores(const double* inf, const double* rel, const double* unc, long long n, double alpha, double beta,
                     double epsilon, double uncertainty_threshold, double* out, void* stream) {
   AHA_REQUIRE(inf && rel && unc && out && n > 0, "aha_fuse_scores: bad arguments");
@@ -85,10 +111,17 @@ int aha_knapsack_select(const double* inf, const double* rel, const double* unc,
                         double alpha, double beta, double epsilon, uint32_t* scratch_bits, uint8_t* selected,
                         void* stream) {
   AHA_REQUIRE(inf && rel && unc && scratch_bits && selected && n_streams > 0 && T > 0, "aha_knapsack_select: bad arguments");
-  AHA_REQUIRE(max_duration >= 0 && max_duration <= 31, "aha_knapsack_select: max_duration must be in [0, 31]");
-  const int warps_per_block = 4;
-  knapsack_kernel<<<(n_streams + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, (cudaStream_t)stream>>>(
-      inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected);
+  AHA_REQUIRE(max_duration >= 0 && max_duration <= 1023, "aha_knapsack_select: max_duration must be in [0, 1023]");
+  // W = decision words per frame (aha_knapsack_words): the smallest of 1, 2, 4, 8, 16, 32 that holds max_duration + 1 bits
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (aha_knapsack_words(max_duration)) {
+    case 1: launch_knapsack<1>(inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected, st); break;
+    case 2: launch_knapsack<2>(inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected, st); break;
+    case 4: launch_knapsack<4>(inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected, st); break;
+    case 8: launch_knapsack<8>(inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected, st); break;
+    case 16: launch_knapsack<16>(inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected, st); break;
+    default: launch_knapsack<32>(inf, rel, unc, n_streams, T, max_duration, alpha, beta, epsilon, scratch_bits, selected, st); break;
+  }
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;

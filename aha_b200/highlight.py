@@ -54,7 +54,7 @@ def knapsack_select_batched(informative: torch.Tensor, relevance: torch.Tensor, 
             raise TypeError("scores must be [N, T] float64 CUDA tensors")
     inf, rel, unc = informative.contiguous(), relevance.contiguous(), uncertainty.contiguous()
     n, T = inf.shape
-    bits = torch.empty(n, T, dtype=torch.int32, device=inf.device)
+    bits = torch.empty(n, T, _lib.load().aha_knapsack_words(int(max_duration)), dtype=torch.int32, device=inf.device)
     sel = torch.empty(n, T, dtype=torch.uint8, device=inf.device)
     _lib.check(_lib.load().aha_knapsack_select(_lib.ptr(inf), _lib.ptr(rel), _lib.ptr(unc), n, T, int(max_duration),
                                                float(alpha), float(beta), float(epsilon), _lib.ptr(bits), _lib.ptr(sel),

@@ -158,12 +158,14 @@ int aha_greedy_pick(const float* logits, int vocab, const long long* generated_i
 /* ---- score fusion and highlight selection, float64, bit-identical to the reference's Python ----
  * aha_fuse_scores: test/grid_search.py:58-65  out = alpha*inf + beta*rel - (unc >= thr ? (unc - thr)*epsilon : 0), n values.
  * aha_knapsack_select: test/highlight_generator.py:8-37 (knapsack_selection), inf/rel/unc [n_streams, T]; every frame
- *   costs 1, value = inf*alpha + rel*beta + unc*epsilon, budget max_duration <= 31; selected[n_streams, T] gets 0/1,
- *   scratch_bits [n_streams, T] is caller-allocated work space.
+ *   costs 1, value = inf*alpha + rel*beta + unc*epsilon, budget max_duration <= 1023; selected[n_streams, T] gets 0/1,
+ *   scratch_bits [n_streams, T, aha_knapsack_words(max_duration)] uint32 is caller-allocated work space (one word per
+ *   frame up to a budget of 31 - the reference's driver uses 20).
  * aha_highlight_mask: test/highlight_generator.py:76-86; mask [n_streams, last_frame + 1] = union over selected frames i
  *   of [gt_frames[i] - half_width, gt_frames[i] + half_width] clipped to [0, last_frame]. */
 int aha_fuse_scores(const double* inf, const double* rel, const double* unc, long long n, double alpha, double beta,
                     double epsilon, double uncertainty_threshold, double* out, void* stream);
+int aha_knapsack_words(int max_duration);
 int aha_knapsack_select(const double* inf, const double* rel, const double* unc, int n_streams, int T, int max_duration,
                         double alpha, double beta, double epsilon, uint32_t* scratch_bits, uint8_t* selected,
                         void* stream);

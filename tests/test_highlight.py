@@ -72,10 +72,30 @@ def test_cuda_highlight_pipeline_vs_oracle(cuda):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("budget", [31, 32, 33, 40, 64, 100, 250])
+def test_cuda_knapsack_large_budgets(cuda, budget):
+    """Budgets beyond one decision word per frame (the reference's knapsack_selection takes any budget; its driver uses
+    20): several 32-bit words per frame, dp[b - 1] of lane 0 carried over from lane 31 of the word below.  Values with
+    mixed signs, so that fewer than `budget` frames may be worth taking; T both above and below the budget."""
+    import aha_b200 as A
+    g = np.random.default_rng(100 + budget)
+    for T in (budget + 57, max(8, budget - 9)):
+        n = 5
+        inf = (g.random((n, T)) - 0.4).astype(np.float32).astype(np.float64)
+        rel = (g.random((n, T)) - 0.5).astype(np.float32).astype(np.float64)
+        unc = (g.random((n, T)) * 0.3).astype(np.float32).astype(np.float64)
+        sel = A.knapsack_select_batched(*(torch.from_numpy(x).to(cuda) for x in (inf, rel, unc)), budget, 0.7, 0.6, -1.5)
+        for s_ in range(n):
+            fr = [dict(idx=i, informative_score=float(inf[s_, i]), relevance_score=float(rel[s_, i]),
+                       uncertainty_score=float(unc[s_, i])) for i in range(T)]
+            assert set(np.nonzero(sel[s_].cpu().numpy())[0].tolist()) == o.knapsack_selection(fr, budget, 0.7, 0.6, -1.5), (T, s_)
+
+
+@pytest.mark.gpu
 def test_cuda_knapsack_errors(cuda):
     import aha_b200 as A
     x = torch.zeros(1, 8, dtype=torch.float64, device=cuda)
     with pytest.raises(ValueError, match="max_duration"):
-        A.knapsack_select_batched(x, x, x, 40, 1.0, 1.0, 1.0)
+        A.knapsack_select_batched(x, x, x, 1024, 1.0, 1.0, 1.0)
     with pytest.raises(TypeError):
         A.knapsack_select_batched(x.float(), x, x, 4, 1.0, 1.0, 1.0)
