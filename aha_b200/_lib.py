@@ -36,6 +36,7 @@ SIGNATURES = {
     "aha_set_sm_sharing": (c_int, [c_int]),
     "aha_debug_attention_timeline": (c_int, [POINTER(c_ulonglong)]),
     "aha_debug_attention_persistent_timeline": (c_int, [POINTER(c_ulonglong)]),
+    "aha_attention_persistent_launch_count": (c_ulonglong, []),
     "aha_debug_gemm_timeline": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_ulonglong)]),
     "aha_debug_gemm_tails": (c_int, [c_int, POINTER(c_ulonglong)]),
     "aha_profile_gemm": (c_int, [c_int]),

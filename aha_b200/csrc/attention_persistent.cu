@@ -632,6 +632,8 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_k, const __
 
 }  // namespace
 
+static unsigned long long g_pattn_launches = 0;
+extern "C" unsigned long long aha_attention_persistent_launch_count(void) { return g_pattn_launches; }
 static unsigned long long* g_pattn_ts = nullptr;
 extern "C" int aha_debug_attention_persistent_timeline(unsigned long long* out32) {
   if (!g_pattn_ts) { aha_set_error("ValueError: run with AHA_TS=2"); return AHA_ERR_VALUE; }
@@ -732,6 +734,7 @@ int op_attention_persistent(const AttnProblem& p_in, cudaStream_t st) {
   ProfSlot* slot = prof_begin(pl.mode == 0 ? 3 : 4, st);
   AHA_CUDA(cudaLaunchKernelEx(&cfg, attention_persistent_kernel, tk, tv, p, pl));
   ++g_aha_launch_count;
+  ++g_pattn_launches;
   if (slot) {
     double flops = 0, bytes = 0;
     for (int i = 0; i < p.n_segs; ++i) {

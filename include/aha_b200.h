@@ -76,7 +76,9 @@ int aha_set_sm_sharing(int shared);
 /* Bring-up aids (AHA_TS=1 in the environment): SM-cycle phase stamps of CTA (0,0,0) of the most recent attention launch /
  * of the most recent GEMM launch per (grid.x, grid.z) class.  Not part of the reference-facing surface. */
 int aha_debug_attention_timeline(unsigned long long* out16);
-int aha_debug_attention_persistent_timeline(unsigned long long* out32);   /* AHA_TS=2: CTA 0 of the persistent kernel */
+int aha_debug_attention_persistent_timeline(unsigned long long* out32);
+/* launches of the persistent attention kernel so far (tests check which kernel a shape runs on) */
+unsigned long long aha_attention_persistent_launch_count(void);   /* AHA_TS=2: CTA 0 of the persistent kernel */
 int aha_debug_gemm_timeline(int* n_out, int* grid_x /*[64]*/, int* grid_z /*[64]*/, unsigned long long* out /*[64*16]*/);
 /* AHA_TS=1: (accumulator complete, exit) of every CTA (up to 512) of the most recent launch of timeline slot `slot`, ns */
 int aha_debug_gemm_tails(int slot, unsigned long long* out /*[512*2]*/);

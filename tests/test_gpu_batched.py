@@ -152,9 +152,12 @@ def test_attention_persistent_kernel(cuda, monkeypatch, heads, kvh, nq, klen, d,
         return out
 
     monkeypatch.setenv("AHA_ATTN_PERSIST", "1")
+    n0 = _lib.load().aha_attention_persistent_launch_count()
     a, b = run(), run()
+    assert _lib.load().aha_attention_persistent_launch_count() == n0 + 2
     monkeypatch.setenv("AHA_ATTN_PERSIST", "0")
     c = run()
+    assert _lib.load().aha_attention_persistent_launch_count() == n0 + 2
     assert torch.equal(a, b)
     assert not torch.isnan(a.float()).any()
     assert (a.float() - c.float()).abs().max().item() <= 1e-2
@@ -224,6 +227,43 @@ def test_batched_streams_out_of_phase(cuda, wide):
         for s in range(ns):
             one = model(inputs_embeds=x[s:s + 1].contiguous(), past_key_values=singles[s])
             a, b = out.frame_scores[s], one.frame_scores[0]
+            assert (a[:2] - b[:2]).abs().max().item() <= 2e-2, (t, s, a, b)
+            assert caches[s].get_seq_length() == singles[s].get_seq_length()
+    for s in range(ns):
+        assert torch.equal(caches[s].provenance(0), singles[s].provenance(0))
+
+
+@pytest.mark.parametrize("kind,sinks", [("sliding_window", 0), ("default_sink", 32)])
+def test_batched_long_windows_out_of_phase(cuda, wide, kind, sinks):
+    """Eight streams against windows of 2304 keys at different fill levels (294 ... 2304 keys: growing caches with the causal
+    limit inside the last tiles, a full one whose ring has wrapped, a sink cache that evicts and re-rotates): the batched
+    call runs the PERSISTENT attention kernel in its stream-K mode (one team of CTAs per query tile, segments of different
+    lengths, (stream, head) groups shared by up to four CTAs), the single-stream calls it is compared with the one-CTA-per-
+    tile kernel with co-resident key splits."""
+    cfg, model = wide
+    q, W, ns = cfg.frame_num_tokens, 2304, 8
+    torch.manual_seed(33)
+    caches = [model.new_cache(kind, W, sinks, max_chunk=q + 8) for _ in range(ns)]
+    singles = [model.new_cache(kind, W, sinks, max_chunk=q + 8) for _ in range(ns)]
+    for s in range(ns):
+        for _ in range(6 * (s + 1)):                       # stream 7: 48 chunks = 2352 tokens > W
+            x = (torch.randn(1, q, cfg.hidden_size, device=cuda) * 0.05).bfloat16()
+            model(inputs_embeds=x, past_key_values=caches[s])
+            model(inputs_embeds=x, past_key_values=singles[s])
+    for s in range(ns):
+        assert torch.equal(caches[s].provenance(0), singles[s].provenance(0))
+    count = _lib.load().aha_attention_persistent_launch_count
+    for t in range(3):
+        x = (torch.randn(ns, q, cfg.hidden_size, device=cuda) * 0.05).bfloat16()
+        n0 = count()
+        out = model(inputs_embeds=x, past_key_values=caches)
+        assert count() == n0 + cfg.num_hidden_layers, "the batched call must run the persistent kernel"
+        for s in range(ns):
+            n1 = count()
+            one = model(inputs_embeds=x[s:s + 1].contiguous(), past_key_values=singles[s])
+            assert count() == n1, "a single stream at this window stays on the one-CTA-per-tile kernel"
+            a, b = out.frame_scores[s], one.frame_scores[0]
+            assert not torch.isnan(a).any()
             assert (a[:2] - b[:2]).abs().max().item() <= 2e-2, (t, s, a, b)
             assert caches[s].get_seq_length() == singles[s].get_seq_length()
     for s in range(ns):
