@@ -3,12 +3,13 @@
 //   * SigLIP self-attention of a vision batch (siglip_encoder.py:197-239): thousands of (frame, head, query tile) groups
 //     of six key tiles each.  One CTA per group spent more than a third of its life outside the key loop (barrier set-up,
 //     tensor-memory allocation, the Q -> K -> first-score latency chain, the output epilogue, the launch gap to the next
-//     CTA); here a CTA walks a contiguous range of groups and every pipeline - K/V ring, score buffers, Q, output - runs
-//     across the group boundaries.
+//     CTA); here a CTA walks over many groups (dealt round-robin, see build_items) and every pipeline - K/V ring, score
+//     buffers, Q, output - runs across the group boundaries.
 //   * frame chunks of several streams against long KV windows (transformers 4.49 Qwen2Attention called at
 //     video_head_live_llava_qwen.py:160-169; BASELINE config 3: 8 streams x 4 kv heads x 3 query tiles x 64 key tiles):
-//     the (group, key tile) units are dealt to the CTAs as equal contiguous ranges (stream-K), so every SM gets the same
-//     number of key tiles; a group shared by several CTAs is merged by the last part to arrive, in part order.
+//     one team of CTAs per query tile; inside a team the (stream, kv head, key tile) units are dealt as equal contiguous
+//     ranges (stream-K), so every SM gets the same number of key tiles; a (stream, head) shared by several CTAs is merged by
+//     the last part to arrive, in part order.
 //
 // CTA = 512 threads, one per SM, tensor memory: S0 | S1 | O | Q0 | Q1 (512 columns).
 //   warp 0      TMA producer of the K ring, warp 3 of the V ring (three stages of 128 keys each), L2 prefetch hints
