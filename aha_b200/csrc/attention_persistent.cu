@@ -13,8 +13,9 @@
 //
 // CTA = 512 threads, one per SM, tensor memory: S0 | S1 | O | Q0 | Q1 (512 columns).
 //   warp 0      TMA producer of the K ring, warp 3 of the V ring (three stages of 128 keys each), L2 prefetch hints
-//   warp 1      MMA issuer: S(n+1) = Q.K^T is issued before O += P(n).V, also across item boundaries; Q and P are
-//               tensor-memory operands (P(n) overwrites the first 64 columns of S(n))
+//   warp 1      MMA issuer: two score tiles ahead - as soon as P(n) arrives it issues O += P(n).V and S(n+2) = Q.K^T back to
+//               back, also across item boundaries; Q and P are tensor-memory operands (P(n) overwrites the first 64
+//               columns of S(n))
 //   warp 2      tensor-memory allocation, builds this CTA's work list in shared memory
 //   warps 4-11  online softmax, two threads per query row (64 key columns each); they never touch O except for the rare
 //               lazy rescale, and go straight on to the next item's first scores
