@@ -69,10 +69,16 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return y;
 }
 __device__ __forceinline__ float fast_silu(float x) { return x * rcp_approx(1.f + __expf(-x)); }
+// gelu_tanh(x) = 0.5 x (1 + tanh(u)) = x * sigmoid(2u), u = sqrt(2/pi) (x + 0.044715 x^3): one ex2, one rcp and five FP
+// operations per element (the tanh form spent eleven; the fc1 GEMM of the SigLIP tower is co-limited by its epilogue).
+// Relative error ~1e-7.  Launch time of fc1 relative to fc2 (same FLOPs, no activation) by ncu: 1.26 with the tanh form,
+// 1.17 with this one - and 1.17 with tanh.approx.f32, which would save the second MUFU but is only good to 5e-4 absolute,
+// ten bf16 steps of the small negative outputs: not used.
 __device__ __forceinline__ float fast_gelu_tanh(float x) {
-  const float u = 0.79788456080286535588f * (x + 0.044715f * x * x * x);
-  const float t = 1.f - 2.f * rcp_approx(1.f + __expf(2.f * u));   // tanh(u)
-  return 0.5f * x * (1.f + t);
+  const float w = x * fmaf(0.044715f * -2.3022082f, x * x, -2.3022082f);   // -2u * log2(e)
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(w));
+  return x * rcp_approx(1.f + e);
 }
 __device__ __forceinline__ float fast_gelu_erf(float x) {
   // erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7)
@@ -380,7 +386,8 @@ __device__ __forceinline__ void epi_tall16(const GemmParams& p, int token, int f
 // segments of the output (and of the residual it adds): fully coalesced HBM traffic.
 template <int BN, int kAct>
 __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t taddr, uint8_t* stage_warp, int a0, int b0,
-                                                int ew, int lane, uint64_t* release_bar = nullptr) {
+                                                int ew, int lane, uint64_t* release_bar = nullptr,
+                                                uint32_t release_cluster_addr = 0) {
   constexpr int kPitch = BN * 2 + 16;
   constexpr int kOutCols = (kAct == GEMM_ACT_SILU_MUL) ? BN / 2 : BN;    // SiLU*mul halves the feature count
   uint8_t* my = stage_warp + lane * kPitch;
@@ -437,6 +444,11 @@ __device__ __forceinline__ void epi_tall_staged(const GemmParams& p, uint32_t ta
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(release_bar);
+  }
+  if (release_cluster_addr) {   // CTA-pair kernel: the accumulator's "drained" barrier lives in the leader CTA
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive_cluster(release_cluster_addr);
   }
   __syncwarp();
   constexpr int kChunksPerRow = kOutCols / 8;
@@ -1490,6 +1502,134 @@ gemm_swap_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The persistent tall GEMM on CTA PAIRS (tcgen05.mma.cta_group::2, M = 256): the two SMs of a TPC take two neighbouring
+// 128-row blocks and the same BN columns.  Every CTA loads its own 128 activation rows (16 KB) and only HALF of the BN
+// weight rows of a k-block; the tensor cores read the other half from the partner's shared memory.  Per CTA and k-block
+// that is 32 KB instead of 48 KB at BN = 256 (28 instead of 40 KB at BN = 192): a third less L2 -> SM traffic and
+// shared-memory fill for the same MMA work, and room for a fourth (BN = 256) / fifth (BN = 192) operand stage.  Same
+// two-accumulator pipeline and the same epilogue as the single-CTA kernel; TMA completions of both CTAs are counted by the
+// leader's full barrier, tcgen05.commit multicasts "stage free" and "accumulator full" to both CTAs, both CTAs' epilogue
+// warps release an accumulator on the leader's barrier.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int BN>
+struct TPairCfg {
+  static constexpr int kStages = BN <= 192 ? 5 : 4;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBHalfRows = BN / 2;
+  static constexpr int kBBytes = kBHalfRows * kBlockK * 2;          // this CTA's half of the weight rows
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kEpiWarps = 8;
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
+  static constexpr int kEpiBN = BN / 2;
+  static constexpr int kEpiWarpBytes = 32 * (kEpiBN * 2 + 16);
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiWarpBytes + 1024 + 256;
+  static_assert(kBBytes % 1024 == 0 && kSmemBytes <= 232448, "tile shape");
+};
+
+template <int BN, int kAct>
+__global__ void __launch_bounds__(TPairCfg<BN>::kThreads, 1)
+gemm_tall_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                      const GemmParams p, const int tiles_mp, const int tiles_n) {
+  using C = TPairCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + C::kStages * C::kABytes;
+  uint8_t* smem_epi = smem + C::kStages * C::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_epi + C::kEpiWarps * C::kEpiWarpBytes);   // used in the leader only
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tmem_full = empty_bar + C::kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;             // [2], counted in the leader only (both CTAs' epilogue warps arrive)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();           // 0 = leader
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  const int n_tiles = tiles_mp * tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 2 * C::kEpiWarps); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc_pair<512>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();        // both CTAs' barriers are initialised before any remote arrival / TMA completion can reach them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();   // activations, residuals and the output buffer belong to earlier kernels until here
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs): own activation rows + own half of the weight rows, counted by the leader's barrier =====
+    if (lane == 0) {
+      const uint64_t pol_a = l2_policy_evict_first(), pol_b = l2_policy_evict_last();
+      uint32_t it = 0;
+      for (int t = cluster_id; t < n_tiles; t += n_clusters) {
+        const int a0 = ((t / tiles_n) * 2 + (int)rank) * kBlockM;
+        const int b0 = (t % tiles_n) * BN + (int)rank * C::kBHalfRows;
+        for (int kb = 0; kb < kb_total; ++kb, ++it) {
+          const int s = it % C::kStages;
+          mbar_wait(&empty_bar[s], ((it / C::kStages) & 1) ^ 1);
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[s], 2u * (uint32_t)C::kStageBytes);     // both CTAs' bytes
+          tma_load_2d_pair_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kb * kBlockK, a0, pol_a);
+          tma_load_2d_pair_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, b0, pol_b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: the leader's elected lane drives the tensor cores of both SMs =====
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16_f32(2 * kBlockM, BN);
+      uint32_t it = 0, tl = 0;
+      for (int t = cluster_id; t < n_tiles; t += n_clusters, ++tl) {
+        const uint32_t buf = tl & 1;
+        mbar_wait(&tmem_empty[buf], ((tl >> 1) & 1) ^ 1);      // both CTAs' epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * BN;
+        for (int kb = 0; kb < kb_total; ++kb, ++it) {
+          const int s = it % C::kStages;
+          mbar_wait(&full_bar[s], (it / C::kStages) & 1);
+          tc_fence_after();
+          const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + s * C::kABytes));
+          const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + s * C::kBBytes));
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma_f16_ss_pair(tacc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          umma_commit_pair(&empty_bar[s], 0b11);    // frees the stage in both CTAs
+        }
+        umma_commit_pair(&tmem_full[buf], 0b11);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue (both CTAs): warp (w & 3) owns TMEM lanes 32*(w&3) .. +31 of both accumulators, column half (w - 4) / 4 =====
+    const int ew = warp & 3, half = (warp - 4) >> 2;
+    uint32_t tl = 0;
+    for (int t = cluster_id; t < n_tiles; t += n_clusters, ++tl) {
+      const int a0 = ((t / tiles_n) * 2 + (int)rank) * kBlockM, b0 = (t % tiles_n) * BN;
+      const uint32_t buf = tl & 1;
+      mbar_wait(&tmem_full[buf], (tl >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * BN + half * C::kEpiBN + ((uint32_t)(ew * 32) << 16);
+      epi_tall_staged<C::kEpiBN, kAct>(p, taddr, smem_epi + (warp - 4) * C::kEpiWarpBytes, a0, b0 + half * C::kEpiBN, ew, lane,
+                                       nullptr, mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+    }
+    tc_fence_before();
+  }
+
+  __syncwarp();
+  cluster_sync_all();      // the partner's tensor-core reads of this CTA's shared memory / writes to its TMEM are over
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<512>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // =====================================================================================
@@ -1680,6 +1820,46 @@ int dispatch_persistent(int act, const CUtensorMap& ta, const CUtensorMap& tb, c
     case GEMM_ACT_GELU_ERF: return launch_persistent<BN, GEMM_ACT_GELU_ERF>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
     case GEMM_ACT_SILU_MUL: return launch_persistent<BN, GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
     default: return launch_persistent<BN, GEMM_ACT_NONE>(ta, tb, p, tiles_m, tiles_n, sm_count, st);
+  }
+}
+}  // namespace
+
+namespace {
+template <int BN, int kAct>
+int launch_tall_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_mp, int tiles_n, int sm_count,
+                     cudaStream_t stream) {
+  using C = TPairCfg<BN>;
+  static bool attr_done[16] = {false};     // function attributes are per device
+  int dev = 0;
+  AHA_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 16 && !attr_done[dev]) {
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tall_pair_kernel<BN, kAct>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_tall_pair_kernel<BN, kAct>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_done[dev] = true;
+  }
+  const int n_clusters = std::min(tiles_mp * tiles_n, sm_count / 2);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * n_clusters); cfg.blockDim = dim3(C::kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 2 : 1;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_tall_pair_kernel<BN, kAct>, ta, tb, p, tiles_mp, tiles_n));
+  ++g_aha_launch_count;
+  AHA_CHECK_LAUNCH();
+  return AHA_OK;
+}
+template <int BN>
+int dispatch_tall_pair(int act, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_mp, int tiles_n,
+                       int sm_count, cudaStream_t st) {
+  switch (act) {
+    case GEMM_ACT_GELU_TANH: return launch_tall_pair<BN, GEMM_ACT_GELU_TANH>(ta, tb, p, tiles_mp, tiles_n, sm_count, st);
+    case GEMM_ACT_GELU_ERF: return launch_tall_pair<BN, GEMM_ACT_GELU_ERF>(ta, tb, p, tiles_mp, tiles_n, sm_count, st);
+    case GEMM_ACT_SILU_MUL: return launch_tall_pair<BN, GEMM_ACT_SILU_MUL>(ta, tb, p, tiles_mp, tiles_n, sm_count, st);
+    default: return launch_tall_pair<BN, GEMM_ACT_NONE>(ta, tb, p, tiles_mp, tiles_n, sm_count, st);
   }
 }
 }  // namespace
@@ -1998,9 +2178,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     // While another stream shares the SMs (vision under the decoder) the one-shot kernel is used instead: a persistent CTA
     // holds its SM for the whole GEMM and the decoder's grids queue behind it (measured 4.80 vs 4.53 ms per frame; the
     // 128-column persistent variant, which leaves room for a decoder CTA on paper, measured 4.77).
-    const bool forced = c.force_bn == 192 || c.force_bn == 256 || c.force_bn == 1128;
+    const bool forced = c.force_bn == 192 || c.force_bn == 256 || c.force_bn == 1128 || c.force_bn == 2192 || c.force_bn == 2256;
     if (!swap && persist && !c.out_f32 && c.force_splits <= 1 && (forced || (c.force_bn == 0 && !g_sm_shared))) {
-      int pbn = c.force_bn == 1128 ? 128 : c.force_bn;   // 1128: the persistent 128-column variant (tests / experiments)
+      int pbn = c.force_bn == 1128 ? 128 : c.force_bn >= 2000 ? c.force_bn - 2000 : c.force_bn;   // 1128: the persistent 128-column variant, 2192 / 2256: CTA pairs (tests / experiments)
       if (pbn == 0) {      // fewer wasted columns wins; ties go to the wider tile
         const int w256 = (p.Nb + 255) / 256 * 256, w192 = (p.Nb + 191) / 192 * 192;
         pbn = w192 < w256 ? 192 : 256;
@@ -2012,8 +2192,15 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
         p.splits = 1; p.kb_per_split = (p.K + kBlockK - 1) / kBlockK; p.dbg = 0; p.dbg_ts = gemm_ts_slot(dim3(148, 1, 1));
         CUtensorMap ta, tb;
         int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
-        rc = get_tmap(b, p.Nb, p.K, ldb, pbn, &tb); if (rc) return rc;
+        // CTA pairs (cta_group::2) for the 192- and 256-column tiles: AHA_TALL_PAIR=1, or force_bn 2192 / 2256 (tests)
+        static const int tall_pair = getenv("AHA_TALL_PAIR") ? atoi(getenv("AHA_TALL_PAIR")) : 1;
+        const bool pair = (tall_pair || c.force_bn == 2192 || c.force_bn == 2256) && pbn != 128;
+        rc = get_tmap(b, p.Nb, p.K, ldb, pair ? pbn / 2 : pbn, &tb); if (rc) return rc;
         ProfSlot* slot = prof_begin(1, stream);
+        if (pair)
+          rc = pbn == 192 ? dispatch_tall_pair<192>(c.act, ta, tb, p, (tm + 1) / 2, tn, w->sm_count, stream)
+                          : dispatch_tall_pair<256>(c.act, ta, tb, p, (tm + 1) / 2, tn, w->sm_count, stream);
+        else
         rc = pbn == 128 ? dispatch_persistent<128>(c.act, ta, tb, p, tm, tn, w->sm_count, stream)
            : pbn == 192 ? dispatch_persistent<192>(c.act, ta, tb, p, tm, tn, w->sm_count, stream)
                         : dispatch_persistent<256>(c.act, ta, tb, p, tm, tn, w->sm_count, stream);

@@ -169,10 +169,13 @@ def test_gemm_vs_torch(cuda, T, F_, K, act):
 
 @pytest.mark.parametrize("T,F_,K,act,bn", [(5832, 3840, 1152, 0, 0), (5832, 4304, 1152, 1, 0), (5832, 1152, 4304, 0, 0),
                                           (5000, 1152, 1152, 2, 256), (3001, 520, 200, 0, 192), (5832, 4304, 1152, 1, 1128),
-                                          (3001, 520, 200, 2, 1128)])
+                                          (3001, 520, 200, 2, 1128),
+                                          # CTA pairs (tcgen05.mma.cta_group::2): odd number of 128-row blocks, ragged columns
+                                          (5832, 3456, 1152, 0, 2192), (5832, 4304, 1152, 1, 2256), (5832, 1152, 4304, 0, 2256),
+                                          (3001, 520, 200, 2, 2192), (2945, 1000, 328, 0, 2256), (23328, 1152, 1152, 0, 2192)])
 def test_gemm_persistent_tall(cuda, T, F_, K, act, bn):
     """The persistent 128 x {192, 256} kernel (two TMEM accumulators): bias, activation and an in-place residual, ragged
-    token / feature / K tails."""
+    token / feature / K tails.  bn = 1128: the 128-column variant; 2192 / 2256: the same tiles on CTA pairs."""
     torch.manual_seed(8)
     x = (torch.randn(T, K, device=cuda) * 0.5).bfloat16()
     w = (torch.randn(F_, K, device=cuda) / K ** 0.5).bfloat16()
