@@ -947,12 +947,14 @@ constexpr int kPsBN = 208;
 // BN = 112: four token tiles - the matrices with 28 / 36 feature tiles (o_proj, down, qkv) then have 112 / 144 work items
 // WITHOUT splitting K, i.e. without parking and merging partial tiles (in the step those merges cost more than the main
 // loops they balanced: o_proj 35 us, down 69 us, qkv 28 us split 2 ways).
-template <int BN>
+template <int BN, bool kPair = false>
 struct PSCfgT {
   static constexpr int kABytes = kBlockM * kBlockK * 2;
-  static constexpr int kBBytes = BN * kBlockK * 2;
+  // kPair: the CTA loads only its half of the token rows, the tensor cores read the other half from the partner CTA
+  static constexpr int kBRows = kPair ? BN / 2 : BN;
+  static constexpr int kBBytes = kBRows * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BN > 128 ? 5 : 7;
+  static constexpr int kStages = kPair ? (BN > 128 ? 7 : 9) : (BN > 128 ? 5 : 7);
   static constexpr int kEpiWarps = 8;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kEpiWarpBytes = 1280;
@@ -980,11 +982,11 @@ __device__ __forceinline__ void reduce_splits_dyn(const float* pp, size_t stride
   }
 }
 
-template <int kAct, int BN>
-__global__ void __launch_bounds__(PSCfgT<BN>::kThreads, 1)
+template <int kAct, int BN, bool kPair>
+__global__ void __launch_bounds__(PSCfgT<BN, kPair>::kThreads, 1)
 gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                             const GemmParams p, const int tiles_a, const int tiles_b) {
-  using C = PSCfgT<BN>;
+  using C = PSCfgT<BN, kPair>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ float sq_red[2][2][4][16];      // [epilogue group][chunk parity][warp][token]
   __shared__ int last_flag[2];
@@ -1001,6 +1003,11 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_total = (p.K + kBlockK - 1) / kBlockK;
+  // kPair: the two CTAs of a cluster (one TPC) take two neighbouring feature tiles and the SAME token tile; `tiles_a` then
+  // counts PAIRS of feature tiles, work items are dealt to clusters, the leader (rank 0) issues tcgen05.mma.cta_group::2.
+  const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+  const int wg_id = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;        // work-group (CTA or CTA pair) index
+  const int wg_n = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   // Work items of this CTA, in order.  Two decompositions:
   //  * fixed split (p.sk_ranks == 0): item -> (feature tile, split, token tile), token tile fastest (the readers of one
   //    weight tile are neighbours), items dealt round-robin over the CTAs;
@@ -1013,7 +1020,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
   struct Item { int a0, b0, kb0, kb1, tile_lin, split, nsplit; };
   const int sk_R = p.sk_ranks;
   const long long sk_U = (long long)tiles_a * kb_total;
-  const int sk_r = blockIdx.x / tiles_b, sk_tb = blockIdx.x % tiles_b;
+  const int sk_r = wg_id / tiles_b, sk_tb = wg_id % tiles_b;     // (stream-K is not used with pairs)
   const long long sk_u0 = sk_R ? (sk_r * sk_U) / sk_R : 0, sk_u1 = sk_R ? ((sk_r + 1) * sk_U) / sk_R : 0;
   auto sk_rank_of = [&](long long u) { return (int)(((u + 1) * sk_R + sk_U - 1) / sk_U) - 1; };
   auto get_item = [&](int i, Item& it) -> bool {
@@ -1029,11 +1036,11 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       it.split = sk_r - rf; it.nsplit = rl - rf + 1;
       return true;
     }
-    const int g = blockIdx.x + i * gridDim.x;
+    const int g = wg_id + i * wg_n;
     if (g >= tiles_a * tiles_b * p.splits) return false;
     const int tb = g % tiles_b, r = g / tiles_b;
     it.split = r % p.splits; it.nsplit = p.splits;
-    const int f = r / p.splits;
+    const int f = kPair ? 2 * (r / p.splits) + (int)rank : r / p.splits;
     it.a0 = f * kBlockM; it.b0 = tb * BN;
     it.kb0 = it.split * p.kb_per_split; it.kb1 = min(kb_total, it.kb0 + p.kb_per_split);
     it.tile_lin = f * tiles_b + tb;
@@ -1048,20 +1055,30 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     prefetch_tensormap(&tmap_a);
     prefetch_tensormap(&tmap_b);
     for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], C::kEpiWarps); }
+    // (pairs: the leader's tmem_empty barriers collect the epilogue warps of both CTAs, its full barriers the bytes of both)
+    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], kPair ? 2 * C::kEpiWarps : C::kEpiWarps); }
     fence_barrier_init();
     // the weight tiles of the first ring do not depend on any earlier kernel: requested before griddepcontrol.wait (PDL)
-    if (pre > 0) {
+    if (pre > 0 && !kPair) {
       for (int kb = 0; kb < pre; ++kb) {
         mbar_arrive_expect_tx(&full_bar[kb], C::kStageBytes);
         tma_load_2d_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], (first.kb0 + kb) * kBlockK, first.a0, pol_a);
       }
     }
   }
-  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  if (warp == 2) { if (kPair) tmem_alloc_pair<512>(tmem_slot); else tmem_alloc<512>(tmem_slot); }
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all();   // both CTAs' barriers are initialised before a remote arrival / TMA completion can reach them
+  else __syncthreads();
   tc_fence_after();
+  if (kPair && warp == 0 && lane == 0 && pre > 0) {
+    // (pairs: the first ring of weight tiles can only be requested once the LEADER's barriers exist - after the cluster sync,
+    // still before griddepcontrol.wait)
+    for (int kb = 0; kb < pre; ++kb) {
+      if (rank == 0) mbar_arrive_expect_tx(&full_bar[kb], 2u * (uint32_t)C::kStageBytes);
+      tma_load_2d_pair_hint(smem_a + kb * C::kABytes, &tmap_a, &full_bar[kb], (first.kb0 + kb) * kBlockK, first.a0, pol_a);
+    }
+  }
   const uint32_t tmem_base = *tmem_slot;
   pdl_launch_dependents();
 
@@ -1075,7 +1092,15 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         const int a0 = it.a0, b0 = it.b0;
         for (int kb = it.kb0; kb < it.kb1; ++kb, ++cnt) {
           const int s = cnt % C::kStages;
-          if (cnt < (uint32_t)pre) {           // first ring: the weight tile is already on its way
+          if (kPair) {
+            const int bh = b0 + (int)rank * C::kBRows;       // this CTA's half of the token rows
+            if (cnt >= (uint32_t)pre) {
+              mbar_wait(&empty_bar[s], ((cnt / C::kStages) & 1) ^ 1);
+              if (rank == 0) mbar_arrive_expect_tx(&full_bar[s], 2u * (uint32_t)C::kStageBytes);     // both CTAs' bytes
+              tma_load_2d_pair_hint(smem_a + s * C::kABytes, &tmap_a, &full_bar[s], kb * kBlockK, a0, pol_a);
+            }
+            tma_load_2d_pair_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, bh, pol_b);
+          } else if (cnt < (uint32_t)pre) {           // first ring: the weight tile is already on its way
             tma_load_2d_hint(smem_b + s * C::kBBytes, &tmap_b, &full_bar[s], kb * kBlockK, b0, pol_b);
           } else {
             mbar_wait(&empty_bar[s], ((cnt / C::kStages) & 1) ^ 1);
@@ -1088,8 +1113,8 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16_f32(kBlockM, BN);
+    if ((!kPair || rank == 0) && elect_one()) {      // pairs: the leader's elected lane drives the tensor cores of both SMs
+      constexpr uint32_t idesc = make_idesc_bf16_f32(kPair ? 2 * kBlockM : kBlockM, BN);
       uint32_t cnt = 0, tl = 0;
       Item it;
       for (int ii = 0; get_item(ii, it); ++ii, ++tl) {
@@ -1106,10 +1131,13 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
           const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + s * C::kBBytes));
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k)
-            umma_f16_ss(tacc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb != kb0 || k != 0) ? 1u : 0u);
-          umma_commit(&empty_bar[s]);
+            if (kPair) umma_f16_ss_pair(tacc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+            else umma_f16_ss(tacc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+          if (kPair) umma_commit_pair(&empty_bar[s], 0b11);    // frees the stage in both CTAs
+          else umma_commit(&empty_bar[s]);
         }
-        umma_commit(&tmem_full[buf]);
+        if (kPair) umma_commit_pair(&tmem_full[buf], 0b11);
+        else umma_commit(&tmem_full[buf]);
       }
     }
   } else if (warp >= 4) {
@@ -1153,6 +1181,12 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
       const bool staged = swap_staged_ok(p, a0);
       const int ncols = min(BN, p.Nb - b0);
       const int my_end = min(col_end, ncols);
+      if (kPair && a0 >= p.Ma) {     // the partner of an odd last feature tile: zeros in the accumulator, nothing to store
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0));
+        continue;
+      }
       if (nsplit == 1) {
 #pragma unroll 1
         for (int jc = col_begin; jc < my_end; jc += 16) {
@@ -1177,7 +1211,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        if (lane == 0) { if (kPair) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0)); else mbar_arrive(&tmem_empty[buf]); }
       } else {
         constexpr size_t kSplitStride = (size_t)BN * kBlockM;
         float* part = p.ws_partial + ((size_t)tile_lin * p.splits + split) * kSplitStride + i;
@@ -1191,7 +1225,7 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[buf]);     // the accumulator is free: the rest works on the parked copy
+        if (lane == 0) { if (kPair) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[buf]), 0)); else mbar_arrive(&tmem_empty[buf]); }     // the accumulator is free: the rest works on the parked copy
         __threadfence();
         asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
         if (ew == 0 && lane == 0) {
@@ -1230,10 +1264,15 @@ gemm_swap_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
     tc_fence_before();
   }
 
-  __syncthreads();
+  if (kPair) {
+    __syncwarp();
+    cluster_sync_all();    // the partner's tensor-core reads of this CTA's shared memory / writes to its TMEM are over
+  } else {
+    __syncthreads();
+  }
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    if (kPair) tmem_dealloc_pair<512>(tmem_base); else tmem_dealloc<512>(tmem_base);
   }
 }
 
@@ -1865,26 +1904,35 @@ int dispatch_tall_pair(int act, const CUtensorMap& ta, const CUtensorMap& tb, co
 }  // namespace
 
 namespace {
-template <int kAct, int BN>
+template <int kAct, int BN, bool kPair = false>
 int launch_swap_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_a, int tiles_b,
                            int grid_ctas, cudaStream_t stream) {
-  using C = PSCfgT<BN>;
+  using C = PSCfgT<BN, kPair>;
   static bool attr_done[16] = {false};
   int dev = 0;
   AHA_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 16 && !attr_done[dev]) {
-    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct, BN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct, BN, kPair>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    AHA_CUDA(cudaFuncSetAttribute(gemm_swap_persistent_kernel<kAct, BN, kPair>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_done[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid_ctas); cfg.blockDim = dim3(C::kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes; cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = aha_pdl_enabled() ? 1 : 0;
-  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_swap_persistent_kernel<kAct, BN>, ta, tb, p, tiles_a, tiles_b));
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (kPair) {      // (tiles_a counts PAIRS of feature tiles, grid_ctas is even)
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (aha_pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr; cfg.numAttrs = na;
+  AHA_CUDA(cudaLaunchKernelEx(&cfg, gemm_swap_persistent_kernel<kAct, BN, kPair>, ta, tb, p, tiles_a, tiles_b));
   ++g_aha_launch_count;
   AHA_CHECK_LAUNCH();
   return AHA_OK;
@@ -2097,21 +2145,29 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     const int tiles_a = (p.Ma + kBlockM - 1) / kBlockM;
     // token tile width: 208 for the big matrices, 112 where 208-token tiles would leave most SMs without a work item
     static const int bn_env = getenv("AHA_PS_BN") ? atoi(getenv("AHA_PS_BN")) : 0;
+    // CTA pairs (tcgen05.mma.cta_group::2: two feature tiles x one token tile per cluster, each CTA loads half of the token
+    // rows): AHA_PS_PAIR2=1, or force_bn = 2112 / 2208 (tests)
+    static const int pair2_env = getenv("AHA_PS_PAIR2") ? atoi(getenv("AHA_PS_PAIR2")) : 0;
+    const bool pair2 = (pair2_env && c.force_bn == 0 && c.force_splits >= 0) || c.force_bn == 2112 || c.force_bn == 2208;
+    const int wg = pair2 ? w->sm_count / 2 : w->sm_count;                 // work groups: CTAs or CTA pairs
     int bn_tok = kPsBN;
     if (c.force_bn == 112 || c.force_bn == 208) bn_tok = c.force_bn;
+    else if (c.force_bn == 2112 || c.force_bn == 2208) bn_tok = c.force_bn - 2000;
     else if (bn_env == 112 || bn_env == 208) bn_tok = bn_env;
     // (short K only: with 112-token tiles every weight tile is pulled by four CTAs - down (K = 18 944) measured 87 us
     // unsplit on 112-token tiles, at the L2 -> SM bandwidth, against 69 us on 208-token tiles split two ways)
     else if ((long)tiles_a * ((p.Nb + kPsBN - 1) / kPsBN) * 5 <= (long)w->sm_count * 3 && (p.K + kBlockK - 1) / kBlockK <= 96) bn_tok = 112;
     const int tiles_b = (p.Nb + bn_tok - 1) / bn_tok;
-    const int tiles = tiles_a * tiles_b;
+    const int tiles_aw = pair2 ? (tiles_a + 1) / 2 : tiles_a;              // feature tiles (or pairs of them) per token tile
+    const int tiles = (pair2 ? 2 * tiles_aw : tiles_a) * tiles_b;           // workspace tiles (an odd last pair has a dummy partner)
+    const int tiles_w = tiles_aw * tiles_b;                                 // work items before splitting
     const int kb_total = (p.K + kBlockK - 1) / kBlockK;
     if (c.sumsq_tiles) *c.sumsq_tiles = tiles_a;
     static const int use_sk = getenv("AHA_PS_STREAMK") ? atoi(getenv("AHA_PS_STREAMK")) : 0;   // measured slower in the step: opt-in
     // (force_splits = -1 selects it explicitly)
     int splits = c.force_splits, kb_per = kb_total, grid_ctas = 0;
     p.sk_ranks = 0;
-    if (splits == -1 || (splits == 0 && use_sk)) {
+    if (!pair2 && (splits == -1 || (splits == 0 && use_sk))) {
       // stream-K: every CTA carries the same number of k-blocks (see the kernel).  R ranks per token tile.
       const long long U = (long long)tiles_a * kb_total;
       int R = std::max(1, w->sm_count / tiles_b);
@@ -2132,9 +2188,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
         for (int s = 1; s <= max_env && s <= kb_total; ++s) {
           const int kbp = (kb_total + s - 1) / s;
           if ((kb_total + kbp - 1) / kbp != s || (s > 1 && kbp < 8)) continue;
-          const long items = (long)tiles * s;
+          const long items = (long)tiles_w * s;
           // (measured in the batched step: with residual + sum-of-squares epilogues, down runs faster split 2 ways than 5)
-          const long cost = ((items + w->sm_count - 1) / w->sm_count) * (kbp + (s > 1 ? 14 + 6 * s : 2));
+          const long cost = ((items + wg - 1) / wg) * (kbp + (s > 1 ? 14 + 6 * s : 2));
           if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = s; }
         }
       }
@@ -2146,8 +2202,9 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
         kb_per = (kb_total + splits - 1) / splits;
         splits = (kb_total + kb_per - 1) / kb_per;
       }
-      grid_ctas = std::min(tiles * splits, w->sm_count);
+      grid_ctas = pair2 ? 2 * std::min(tiles_w * splits, wg) : std::min(tiles * splits, w->sm_count);
     }
+    if (splits < 1) splits = 1;
     p.splits = splits; p.kb_per_split = kb_per; p.dbg = 0;
     if (splits > 1) {
       GemmSplitScratch sc;
@@ -2156,9 +2213,15 @@ int gemm_bf16(const GemmCall& c, GemmWorkspace* w, cudaStream_t stream) {
     }
     CUtensorMap ta, tb;
     int rc = get_tmap(a, p.Ma, p.K, lda, kBlockM, &ta); if (rc) return rc;
-    rc = get_tmap(b, p.Nb, p.K, ldb, bn_tok, &tb); if (rc) return rc;
+    rc = get_tmap(b, p.Nb, p.K, ldb, pair2 ? bn_tok / 2 : bn_tok, &tb); if (rc) return rc;
     ProfSlot* slot = prof_begin(5, stream);
-    if (bn_tok == 112)
+    if (pair2 && bn_tok == 112)
+      rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL, 112, true>(ta, tb, p, tiles_aw, tiles_b, grid_ctas, stream)
+                                      : launch_swap_persistent<GEMM_ACT_NONE, 112, true>(ta, tb, p, tiles_aw, tiles_b, grid_ctas, stream);
+    else if (pair2)
+      rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL, kPsBN, true>(ta, tb, p, tiles_aw, tiles_b, grid_ctas, stream)
+                                      : launch_swap_persistent<GEMM_ACT_NONE, kPsBN, true>(ta, tb, p, tiles_aw, tiles_b, grid_ctas, stream);
+    else if (bn_tok == 112)
       rc = c.act == GEMM_ACT_SILU_MUL ? launch_swap_persistent<GEMM_ACT_SILU_MUL, 112>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream)
                                       : launch_swap_persistent<GEMM_ACT_NONE, 112>(ta, tb, p, tiles_a, tiles_b, grid_ctas, stream);
     else

@@ -41,9 +41,11 @@ def _gemm(x, w, out, act=0, bias=None, res=None, splits=0, swap=-1, bn=0):
     (392, 3584, 18944, 0, -1),    # stream-K: 296 k-blocks per tile shared by ranges of 112
     (600, 1536, 8960, 3, -1),
 ])
-@pytest.mark.parametrize("bn", [416, 208, 112], ids=["cta_pair", "single_cta_208", "single_cta_112"])
+@pytest.mark.parametrize("bn", [416, 208, 112, 2208, 2112], ids=["cta_pair_416", "single_cta_208", "single_cta_112", "cta_pair_208", "cta_pair_112"])
 def test_gemm_persistent_skinny(cuda, T, F_, K, act, splits, bn):
-    """bn = 416: the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 weight rows x 416 tokens per pair); bn = 208: the
+    """bn = 2208 / 2112: the persistent kernel on CTA pairs (tcgen05.mma.cta_group::2: two feature tiles x one token tile per
+    cluster, two accumulators, each CTA loads half of the token rows); bn = 416: the first CTA-pair kernel (256 weight rows x
+    416 tokens per pair, one accumulator); bn = 208: the
     single-CTA persistent kernel with 128 x 208 tiles (two accumulators), bn = 112: the same with 128 x 112 tiles (small
     matrices: more work items instead of split-K).  splits = -1: stream-K decomposition."""
     torch.manual_seed(21)
